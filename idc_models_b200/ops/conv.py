@@ -1,0 +1,151 @@
+"""Convolution front-end: geometry helpers, the raw bindings to the tcgen05 implicit-GEMM kernels
+(``csrc/umma_conv.cu``) and the plain-PyTorch fp32 statement of the same math (CPU path + oracle).
+
+Activation convention everywhere in this package: NHWC, i.e. a 4-D tensor ``[B, H, W, pitch]``
+whose last dimension may be wider than the logical channel count (``coff``/``channels`` select a
+slice). Conv weights are ``[Cout, KH, KW, Cin]``.
+
+Reference parity: these are the cuDNN calls TensorFlow issues for ``tf.keras`` ``Conv2D`` inside
+``tf.keras.applications`` models (/root/reference/dist_model_tf_vgg.py:119,
+dist_model_tf_dense.py:131, dist_model_tf_mobile.py:119).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+
+ACT_NONE, ACT_RELU, ACT_RELU6 = 0, 1, 2
+
+
+@dataclass(frozen=True)
+class ConvGeom:
+    """Forward geometry of one convolution (Keras semantics resolved to explicit padding)."""
+    h: int
+    w: int
+    cin: int
+    cout: int
+    kh: int
+    kw: int
+    stride: int
+    pad_t: int
+    pad_l: int
+    pad_b: int
+    pad_r: int
+
+    @property
+    def ho(self) -> int:
+        return (self.h + self.pad_t + self.pad_b - self.kh) // self.stride + 1
+
+    @property
+    def wo(self) -> int:
+        return (self.w + self.pad_l + self.pad_r - self.kw) // self.stride + 1
+
+
+def same_padding(size: int, k: int, stride: int) -> tuple[int, int]:
+    """TensorFlow 'SAME' padding (before, after) for one spatial dim."""
+    out = -(-size // stride)
+    total = max((out - 1) * stride + k - size, 0)
+    return total // 2, total - total // 2
+
+
+def geom(h: int, w: int, cin: int, cout: int, k: int, stride: int = 1, padding="same") -> ConvGeom:
+    """padding: 'same' | 'valid' | ((top, bottom), (left, right)) explicit (ZeroPadding2D + VALID)."""
+    if padding == "same":
+        (pt, pb), (pl, pr) = same_padding(h, k, stride), same_padding(w, k, stride)
+    elif padding == "valid":
+        pt = pb = pl = pr = 0
+    else:
+        (pt, pb), (pl, pr) = padding
+    return ConvGeom(h, w, cin, cout, k, k, stride, pt, pl, pb, pr)
+
+
+def _desc(g: ConvGeom, batch: int, x_pitch: int, x_coff: int, y_pitch: int, y_coff: int) -> _lib.ConvDesc:
+    return _lib.ConvDesc(batch, g.h, g.w, g.cin, g.ho, g.wo, g.cout, g.kh, g.kw, g.stride, g.pad_t,
+                         g.pad_l, x_pitch, x_coff, y_pitch, y_coff)
+
+
+def _chk(t: torch.Tensor, dtype, name: str) -> None:
+    if t is None:
+        return
+    if not t.is_cuda or t.dtype != dtype or not t.is_contiguous():
+        raise ValueError(f"{name}: expected a contiguous CUDA {dtype} tensor, got {t.dtype} "
+                         f"{t.device} contiguous={t.is_contiguous()}")
+
+
+def conv_fprop_raw(g: ConvGeom, x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, *, x_coff: int = 0,
+                   y_coff: int = 0, pro_scale=None, pro_shift=None, pro_act: int = ACT_NONE,
+                   epi_scale=None, epi_shift=None, epi_act: int = ACT_NONE, residual=None,
+                   res_coff: int = 0, stat_sum=None, stat_sq=None) -> None:
+    """y[..., y_coff:y_coff+cout] = epi(conv(pro(x[..., x_coff:x_coff+cin]), w)) on the GPU."""
+    _chk(x, torch.bfloat16, "x"); _chk(w, torch.bfloat16, "w"); _chk(y, torch.bfloat16, "y")
+    for t, n in ((pro_scale, "pro_scale"), (pro_shift, "pro_shift"), (epi_scale, "epi_scale"),
+                 (epi_shift, "epi_shift"), (stat_sum, "stat_sum"), (stat_sq, "stat_sq")):
+        _chk(t, torch.float32, n)
+    _chk(residual, torch.bfloat16, "residual")
+    b = x.shape[0]
+    d = _desc(g, b, x.shape[-1], x_coff, y.shape[-1], y_coff)
+    f = _lib.ConvFused(_lib.ptr(pro_scale), _lib.ptr(pro_shift), pro_act, _lib.ptr(epi_scale),
+                       _lib.ptr(epi_shift), epi_act, _lib.ptr(residual),
+                       residual.shape[-1] if residual is not None else 0, res_coff,
+                       _lib.ptr(stat_sum), _lib.ptr(stat_sq))
+    lib = _lib.cuda_lib()
+    _lib.check(lib.idcb_conv_fprop(C.byref(d), _lib.ptr(x), _lib.ptr(w), _lib.ptr(y), C.byref(f),
+                                   _lib.stream()))
+    _lib.count_launch()
+
+
+def conv_dgrad_raw(g: ConvGeom, dy: torch.Tensor, w: torch.Tensor, dx: torch.Tensor | None, *,
+                   dy_coff: int = 0, dx_coff: int = 0, dx_pitch: int | None = None, mode: int = 0,
+                   aux=None, aux_coff: int = 0, bwd_scale=None, bwd_shift=None, bwd_act: int = ACT_NONE,
+                   gacc=None, g_coff: int = 0, stat_a=None, stat_b=None) -> None:
+    """dx = epi(conv^T(dy, w)); see include/idcb200.h for the epilogue modes."""
+    _chk(dy, torch.bfloat16, "dy"); _chk(w, torch.bfloat16, "w"); _chk(dx, torch.bfloat16, "dx")
+    _chk(aux, torch.bfloat16, "aux"); _chk(gacc, torch.float32, "gacc")
+    b = dy.shape[0]
+    if dx_pitch is None:
+        dx_pitch = dx.shape[-1] if dx is not None else g.cin
+    d = _desc(g, b, dx_pitch, dx_coff, dy.shape[-1], dy_coff)
+    f = _lib.ConvBwdFused(mode, _lib.ptr(aux), aux.shape[-1] if aux is not None else 0, aux_coff,
+                          _lib.ptr(bwd_scale), _lib.ptr(bwd_shift), bwd_act, _lib.ptr(gacc),
+                          gacc.shape[-1] if gacc is not None else 0, g_coff, _lib.ptr(stat_a),
+                          _lib.ptr(stat_b))
+    lib = _lib.cuda_lib()
+    _lib.check(lib.idcb_conv_dgrad(C.byref(d), _lib.ptr(dy), _lib.ptr(w), _lib.ptr(dx), C.byref(f),
+                                   _lib.stream()))
+    _lib.count_launch()
+
+
+def conv_wgrad_raw(g: ConvGeom, x: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor, *, x_coff: int = 0,
+                   dy_coff: int = 0, pro_scale=None, pro_shift=None, pro_act: int = ACT_NONE) -> None:
+    """dw (fp32 [Cout,KH,KW,Cin]) += pro(x)^T * dy."""
+    _chk(x, torch.bfloat16, "x"); _chk(dy, torch.bfloat16, "dy"); _chk(dw, torch.float32, "dw")
+    b = x.shape[0]
+    d = _desc(g, b, x.shape[-1], x_coff, dy.shape[-1], dy_coff)
+    lib = _lib.cuda_lib()
+    _lib.check(lib.idcb_conv_wgrad(C.byref(d), _lib.ptr(x), _lib.ptr(dy), _lib.ptr(dw),
+                                   _lib.ptr(pro_scale), _lib.ptr(pro_shift), pro_act, _lib.stream()))
+    _lib.count_launch()
+
+
+# ---------------------------------------------------------------------------------------------
+# PyTorch fp32 statement of the same math (CPU execution path and numerical oracle)
+# ---------------------------------------------------------------------------------------------
+def act_ref(v: torch.Tensor, act: int) -> torch.Tensor:
+    if act == ACT_RELU:
+        return torch.relu(v)
+    if act == ACT_RELU6:
+        return torch.clamp(v, 0.0, 6.0)
+    return v
+
+
+def conv_ref(g: ConvGeom, x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """NHWC conv with explicit (possibly asymmetric) zero padding. x [B,H,W,Cin], w [Cout,KH,KW,Cin]."""
+    xn = x.permute(0, 3, 1, 2)
+    xn = F.pad(xn, (g.pad_l, g.pad_r, g.pad_t, g.pad_b))
+    y = F.conv2d(xn, w.permute(0, 3, 1, 2), stride=g.stride)
+    return y.permute(0, 2, 3, 1).contiguous()

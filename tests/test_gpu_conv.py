@@ -1,0 +1,218 @@
+"""GPU numerics of the tcgen05 implicit-GEMM convolutions against a plain PyTorch fp32 reference
+of the same op, at the shapes the three model families use."""
+import pytest
+import torch
+
+from idc_models_b200.ops import conv as C
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(*shape, scale=1.0):
+    return (torch.randn(*shape, device="cuda") * scale).to(torch.bfloat16)
+
+
+def _close(got, want, tol=2e-2):
+    got = got.float()
+    want = want.float()
+    err = (got - want).abs().max().item()
+    ref = want.abs().max().item() + 1e-6
+    assert err <= tol * ref, f"max abs err {err:.4g} vs ref max {ref:.4g}"
+
+
+FWD_CASES = [
+    # b, h, w, cin, cout, k, stride, padding
+    (2, 8, 8, 64, 64, 1, 1, "same"),
+    (3, 13, 13, 256, 128, 1, 1, "same"),
+    (2, 12, 12, 64, 64, 3, 1, "same"),
+    (4, 13, 13, 128, 32, 3, 1, "same"),
+    (2, 6, 6, 96, 128, 1, 1, "same"),
+    (2, 25, 25, 64, 256, 3, 1, "same"),
+    (5, 4, 4, 576, 160, 1, 1, "same"),
+    (2, 7, 7, 24, 144, 1, 1, "same"),
+    (2, 3, 3, 512, 512, 3, 1, "same"),
+    (128, 1, 1, 992, 128, 1, 1, "same"),
+]
+
+
+@pytest.mark.parametrize("b,h,w,cin,cout,k,stride,padding", FWD_CASES)
+def test_fprop_plain(b, h, w, cin, cout, k, stride, padding):
+    torch.manual_seed(0)
+    g = C.geom(h, w, cin, cout, k, stride, padding)
+    x = _rand(b, h, w, cin)
+    wt = _rand(cout, k, k, cin, scale=(k * k * cin) ** -0.5)
+    y = torch.zeros(b, g.ho, g.wo, cout, device="cuda", dtype=torch.bfloat16)
+    C.conv_fprop_raw(g, x, wt, y)
+    torch.cuda.synchronize()
+    _close(y, C.conv_ref(g, x.float(), wt.float()))
+
+
+def test_fprop_fused_densenet_pattern():
+    """BN+ReLU prologue on a channel prefix of a concat buffer, raw output written at a channel
+    offset, batch statistics accumulated in the epilogue."""
+    torch.manual_seed(1)
+    b, h, w, ctot, cin, cout = 4, 13, 13, 256, 96, 128
+    g = C.geom(h, w, cin, cout, 1)
+    buf = _rand(b, h, w, ctot)
+    wt = _rand(cout, 1, 1, cin, scale=cin ** -0.5)
+    sc = torch.rand(cin, device="cuda") + 0.5
+    sh = torch.randn(cin, device="cuda") * 0.3
+    y = torch.zeros(b, h, w, cout, device="cuda", dtype=torch.bfloat16)
+    s1 = torch.zeros(cout, device="cuda")
+    s2 = torch.zeros(cout, device="cuda")
+    C.conv_fprop_raw(g, buf, wt, y, pro_scale=sc, pro_shift=sh, pro_act=C.ACT_RELU, stat_sum=s1,
+                     stat_sq=s2)
+    torch.cuda.synchronize()
+    a = torch.relu(buf[..., :cin].float() * sc + sh).to(torch.bfloat16).float()
+    want = C.conv_ref(g, a, wt.float())
+    _close(y, want)
+    yf = y.float().reshape(-1, cout)
+    _close(s1, yf.sum(0), 1e-3)
+    _close(s2, (yf * yf).sum(0), 1e-3)
+    # 3x3 128->32 written into the buffer at channel offset cin
+    g3 = C.geom(h, w, cout, 32, 3)
+    w3 = _rand(32, 3, 3, cout, scale=(9 * cout) ** -0.5)
+    sc3 = torch.rand(cout, device="cuda") + 0.5
+    sh3 = torch.randn(cout, device="cuda") * 0.3
+    before = buf.clone()
+    C.conv_fprop_raw(g3, y, w3, buf, y_coff=cin, pro_scale=sc3, pro_shift=sh3, pro_act=C.ACT_RELU)
+    torch.cuda.synchronize()
+    a3 = torch.relu(y.float() * sc3 + sh3).to(torch.bfloat16).float()
+    _close(buf[..., cin:cin + 32], C.conv_ref(g3, a3, w3.float()))
+    assert torch.equal(buf[..., :cin], before[..., :cin])
+    assert torch.equal(buf[..., cin + 32:], before[..., cin + 32:])
+
+
+def test_fprop_epilogue_bias_relu_residual():
+    torch.manual_seed(2)
+    b, h, w, cin, cout = 2, 12, 12, 64, 64
+    g = C.geom(h, w, cin, cout, 3)
+    x = _rand(b, h, w, cin)
+    wt = _rand(cout, 3, 3, cin, scale=(9 * cin) ** -0.5)
+    es = torch.rand(cout, device="cuda") + 0.5
+    eh = torch.randn(cout, device="cuda")
+    res = _rand(b, h, w, cout)
+    y = torch.zeros(b, h, w, cout, device="cuda", dtype=torch.bfloat16)
+    C.conv_fprop_raw(g, x, wt, y, epi_scale=es, epi_shift=eh, epi_act=C.ACT_RELU6, residual=res)
+    torch.cuda.synchronize()
+    want = torch.clamp(C.conv_ref(g, x.float(), wt.float()) * es + eh, 0, 6) + res.float()
+    _close(y, want)
+
+
+DGRAD_CASES = [
+    (2, 12, 12, 64, 64, 3),
+    (4, 13, 13, 128, 32, 3),
+    (3, 13, 13, 256, 128, 1),
+    (2, 6, 6, 512, 512, 3),
+    (2, 7, 7, 24, 144, 1),
+    (128, 1, 1, 992, 128, 1),
+]
+
+
+def _dgrad_ref(g, dy, wt, xshape):
+    x = torch.zeros(xshape, device="cuda", requires_grad=True)
+    y = C.conv_ref(g, x, wt.float())
+    (gx,) = torch.autograd.grad(y, x, dy.float())
+    return gx
+
+
+@pytest.mark.parametrize("b,h,w,cin,cout,k", DGRAD_CASES)
+def test_dgrad_plain(b, h, w, cin, cout, k):
+    torch.manual_seed(3)
+    g = C.geom(h, w, cin, cout, k)
+    wt = _rand(cout, k, k, cin, scale=(k * k * cout) ** -0.5)
+    dy = _rand(b, g.ho, g.wo, cout)
+    dx = torch.zeros(b, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    C.conv_dgrad_raw(g, dy, wt, dx)
+    torch.cuda.synchronize()
+    _close(dx, _dgrad_ref(g, dy, wt, (b, h, w, cin)))
+
+
+def test_dgrad_relu_mask_and_bias_grad():
+    torch.manual_seed(4)
+    b, h, w, cin, cout = 2, 12, 12, 64, 128
+    g = C.geom(h, w, cin, cout, 3)
+    wt = _rand(cout, 3, 3, cin, scale=(9 * cout) ** -0.5)
+    dy = _rand(b, h, w, cout)
+    xin = torch.relu(_rand(b, h, w, cin))
+    dx = torch.zeros(b, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    db = torch.zeros(cin, device="cuda")
+    C.conv_dgrad_raw(g, dy, wt, dx, mode=1, aux=xin, stat_a=db)
+    torch.cuda.synchronize()
+    want = _dgrad_ref(g, dy, wt, (b, h, w, cin)) * (xin.float() > 0)
+    _close(dx, want)
+    _close(db, dx.float().reshape(-1, cin).sum(0), 1e-3)
+
+
+def test_dgrad_bn_relu_backward_into_g():
+    """mode 2: BN+ReLU backward fused in the dgrad epilogue, accumulated into the dense block's
+    fp32 gradient buffer at a channel prefix."""
+    torch.manual_seed(5)
+    b, h, w, ctot, cin, cout = 4, 13, 13, 256, 96, 128
+    g = C.geom(h, w, cin, cout, 1)
+    wt = _rand(cout, 1, 1, cin, scale=cout ** -0.5)
+    dy = _rand(b, h, w, cout)
+    xraw = _rand(b, h, w, ctot)
+    sc = torch.rand(cin, device="cuda") + 0.5
+    sh = torch.randn(cin, device="cuda") * 0.3
+    G = torch.randn(b, h, w, ctot, device="cuda")
+    G0 = G.clone()
+    dpre = torch.zeros(b, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    sa = torch.zeros(cin, device="cuda")
+    sb = torch.zeros(cin, device="cuda")
+    C.conv_dgrad_raw(g, dy, wt, dpre, mode=2, aux=xraw, bwd_scale=sc, bwd_shift=sh,
+                     bwd_act=C.ACT_RELU, gacc=G, stat_a=sa, stat_b=sb)
+    torch.cuda.synchronize()
+    da = _dgrad_ref(g, dy, wt, (b, h, w, cin))
+    xr = xraw[..., :cin].float()
+    want = da * ((xr * sc + sh) > 0)
+    _close(dpre, want)
+    _close(G[..., :cin] - G0[..., :cin], want * sc, 2e-2)
+    assert torch.equal(G[..., cin:], G0[..., cin:])
+    _close(sa, want.reshape(-1, cin).sum(0), 2e-2)
+    _close(sb, (want * xr).reshape(-1, cin).sum(0), 2e-2)
+
+
+WGRAD_CASES = [
+    (2, 8, 8, 64, 64, 1),
+    (4, 13, 13, 128, 32, 3),
+    (3, 13, 13, 256, 128, 1),
+    (2, 12, 12, 64, 64, 3),
+    (2, 6, 6, 96, 128, 1),
+    (2, 7, 7, 24, 144, 1),
+    (2, 3, 3, 512, 512, 3),
+    (16, 25, 25, 64, 128, 3),
+]
+
+
+@pytest.mark.parametrize("b,h,w,cin,cout,k", WGRAD_CASES)
+def test_wgrad(b, h, w, cin, cout, k):
+    torch.manual_seed(6)
+    g = C.geom(h, w, cin, cout, k)
+    x = _rand(b, h, w, cin)
+    dy = _rand(b, g.ho, g.wo, cout, scale=0.1)
+    dw = torch.zeros(cout, k, k, cin, device="cuda")
+    C.conv_wgrad_raw(g, x, dy, dw)
+    torch.cuda.synchronize()
+    wref = torch.zeros(cout, k, k, cin, device="cuda", requires_grad=True)
+    y = C.conv_ref(g, x.float(), wref)
+    (gw,) = torch.autograd.grad(y, wref, dy.float())
+    _close(dw, gw, 1e-2)
+
+
+def test_wgrad_prologue_and_offsets():
+    torch.manual_seed(7)
+    b, h, w, ctot, cin, cout = 4, 13, 13, 256, 96, 32
+    g = C.geom(h, w, cin, cout, 3)
+    buf = _rand(b, h, w, ctot)
+    dybuf = _rand(b, h, w, 64, scale=0.1)
+    sc = torch.rand(cin, device="cuda") + 0.5
+    sh = torch.randn(cin, device="cuda") * 0.3
+    dw = torch.zeros(cout, 3, 3, cin, device="cuda")
+    C.conv_wgrad_raw(g, buf, dybuf, dw, dy_coff=32, pro_scale=sc, pro_shift=sh, pro_act=C.ACT_RELU)
+    torch.cuda.synchronize()
+    a = torch.relu(buf[..., :cin].float() * sc + sh).to(torch.bfloat16).float()
+    wref = torch.zeros(cout, 3, 3, cin, device="cuda", requires_grad=True)
+    y = C.conv_ref(g, a, wref)
+    (gw,) = torch.autograd.grad(y, wref, dybuf[..., 32:64].float())
+    _close(dw, gw, 1e-2)
