@@ -1,0 +1,284 @@
+// Depthwise 3x3 convolution (stride 1 / 2) for MobileNetV2, NHWC bf16, weights [KH][KW][C] bf16.
+//   fprop : y = dw( act(scale*x+shift) )                + batch statistics of y
+//   dgrad : dpre = dw^T(dy) * act'(scale*x+shift)       + BN-backward sums
+//   wgrad : dw += sum_pos act(scale*x+shift) * dy
+// Bandwidth-bound (~6 % of MobileNetV2 MACs), so these are direct kernels, one
+// thread per 8 channels, 16-byte accesses, fused BN prologue/epilogue bookkeeping instead of separate
+// BN kernels. Reference: DepthwiseConv2D layers inside tf.keras.applications.MobileNetV2
+// (/root/reference/dist_model_tf_mobile.py:119), executed by TF's depthwise CUDA kernels.
+#include "common.cuh"
+#include "../include/idcb200.h"
+
+namespace idcb {
+
+struct DwArgs {
+    const __nv_bfloat16* x; int x_pitch, x_coff;
+    const __nv_bfloat16* w;             // [k][k][C]
+    __nv_bfloat16* y; int y_pitch, y_coff;
+    const __nv_bfloat16* dy; int dy_pitch, dy_coff;
+    __nv_bfloat16* dx; int dx_pitch, dx_coff;
+    float* dw;                          // fp32 [k][k][C]
+    int B, H, W, C, Ho, Wo, k, stride, pad_t, pad_l;
+    const float* scale; const float* shift; int act;
+    float* stat_a; float* stat_b;
+};
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
+    uint4 q = *reinterpret_cast<const uint4*>(p);
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(&q);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        float2 f = unpack_bf16x2(w[e]);
+        v[2 * e] = f.x;
+        v[2 * e + 1] = f.y;
+    }
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
+    uint4 q;
+    uint32_t* w = reinterpret_cast<uint32_t*>(&q);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) w[e] = pack_bf16x2(v[2 * e], v[2 * e + 1]);
+    *reinterpret_cast<uint4*>(p) = q;
+}
+
+// block-level reduction of 8 per-thread values into global atomics (one channel octet per block row)
+__device__ __forceinline__ void block_reduce8_atomic(const float (&v)[8], float* dst, float (*sh)[9]) {
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sh[threadIdx.x][e] = v[e];
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        float t = 0.f;
+        for (int r = 0; r < (int)blockDim.x; ++r) t += sh[r][threadIdx.x];
+        atomicAdd(dst + threadIdx.x, t);
+    }
+}
+
+__global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
+    __shared__ float sh[256][9];
+    const int c = blockIdx.y * 8;
+    float sc[8], sf[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        sc[e] = p.scale ? p.scale[c + e] : 1.f;
+        sf[e] = p.scale ? p.shift[c + e] : 0.f;
+    }
+    float wk[9][8];
+    for (int t = 0; t < p.k * p.k; ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
+    float sa[8], sb[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sa[e] = sb[e] = 0.f;
+    const long long npos = 1LL * p.B * p.Ho * p.Wo;
+    for (long long pos = blockIdx.x * (long long)blockDim.x + threadIdx.x; pos < npos;
+         pos += (long long)gridDim.x * blockDim.x) {
+        const int wo = static_cast<int>(pos % p.Wo);
+        const long long t2 = pos / p.Wo;
+        const int ho = static_cast<int>(t2 % p.Ho);
+        const int b = static_cast<int>(t2 / p.Ho);
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+        for (int kh = 0; kh < p.k; ++kh) {
+            const int hi = ho * p.stride - p.pad_t + kh;
+            if (hi < 0 || hi >= p.H) continue;
+            for (int kw = 0; kw < p.k; ++kw) {
+                const int wi = wo * p.stride - p.pad_l + kw;
+                if (wi < 0 || wi >= p.W) continue;
+                float xv[8];
+                load8(p.x + (static_cast<size_t>(b * p.H + hi) * p.W + wi) * p.x_pitch + p.x_coff + c, xv);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    float a = xv[e];
+                    if (p.scale) a = __bfloat162float(__float2bfloat16_rn(apply_act(fmaf(a, sc[e], sf[e]), p.act)));
+                    acc[e] = fmaf(a, wk[kh * p.k + kw][e], acc[e]);
+                }
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            acc[e] = __bfloat162float(__float2bfloat16_rn(acc[e]));
+            sa[e] += acc[e];
+            sb[e] += acc[e] * acc[e];
+        }
+        store8(p.y + pos * p.y_pitch + p.y_coff + c, acc);
+    }
+    if (p.stat_a) block_reduce8_atomic(sa, p.stat_a + c, sh);
+    if (p.stat_b) block_reduce8_atomic(sb, p.stat_b + c, sh);
+}
+
+__global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
+    __shared__ float sh[256][9];
+    const int c = blockIdx.y * 8;
+    float sc[8], sf[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        sc[e] = p.scale ? p.scale[c + e] : 1.f;
+        sf[e] = p.scale ? p.shift[c + e] : 0.f;
+    }
+    float wk[9][8];
+    for (int t = 0; t < p.k * p.k; ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
+    float sa[8], sb[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sa[e] = sb[e] = 0.f;
+    const long long npos = 1LL * p.B * p.H * p.W;
+    for (long long pos = blockIdx.x * (long long)blockDim.x + threadIdx.x; pos < npos;
+         pos += (long long)gridDim.x * blockDim.x) {
+        const int wi = static_cast<int>(pos % p.W);
+        const long long t2 = pos / p.W;
+        const int hi = static_cast<int>(t2 % p.H);
+        const int b = static_cast<int>(t2 / p.H);
+        float g[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] = 0.f;
+        for (int kh = 0; kh < p.k; ++kh) {
+            const int hn = hi + p.pad_t - kh;
+            if (hn < 0 || hn % p.stride) continue;
+            const int ho = hn / p.stride;
+            if (ho >= p.Ho) continue;
+            for (int kw = 0; kw < p.k; ++kw) {
+                const int wn = wi + p.pad_l - kw;
+                if (wn < 0 || wn % p.stride) continue;
+                const int wo = wn / p.stride;
+                if (wo >= p.Wo) continue;
+                float dv[8];
+                load8(p.dy + (static_cast<size_t>(b * p.Ho + ho) * p.Wo + wo) * p.dy_pitch + p.dy_coff + c, dv);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) g[e] = fmaf(dv[e], wk[kh * p.k + kw][e], g[e]);
+            }
+        }
+        float xv[8];
+        if (p.scale || p.stat_b) load8(p.x + pos * p.x_pitch + p.x_coff + c, xv);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            if (p.scale) g[e] *= act_mask(fmaf(xv[e], sc[e], sf[e]), p.act);
+            g[e] = __bfloat162float(__float2bfloat16_rn(g[e]));
+            sa[e] += g[e];
+            if (p.stat_b) sb[e] += g[e] * xv[e];
+        }
+        store8(p.dx + pos * p.dx_pitch + p.dx_coff + c, g);
+    }
+    if (p.stat_a) block_reduce8_atomic(sa, p.stat_a + c, sh);
+    if (p.stat_b) block_reduce8_atomic(sb, p.stat_b + c, sh);
+}
+
+__global__ void __launch_bounds__(256) dw_wgrad_kernel(DwArgs p) {
+    __shared__ float sh[256][9];
+    const int c = blockIdx.y * 8;
+    float sc[8], sf[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        sc[e] = p.scale ? p.scale[c + e] : 1.f;
+        sf[e] = p.scale ? p.shift[c + e] : 0.f;
+    }
+    float acc[9][8];
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[t][e] = 0.f;
+    const long long npos = 1LL * p.B * p.Ho * p.Wo;
+    for (long long pos = blockIdx.x * (long long)blockDim.x + threadIdx.x; pos < npos;
+         pos += (long long)gridDim.x * blockDim.x) {
+        const int wo = static_cast<int>(pos % p.Wo);
+        const long long t2 = pos / p.Wo;
+        const int ho = static_cast<int>(t2 % p.Ho);
+        const int b = static_cast<int>(t2 / p.Ho);
+        float dv[8];
+        load8(p.dy + pos * p.dy_pitch + p.dy_coff + c, dv);
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+            const int hi = ho * p.stride - p.pad_t + kh;
+            if (hi < 0 || hi >= p.H) continue;
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                const int wi = wo * p.stride - p.pad_l + kw;
+                if (wi < 0 || wi >= p.W) continue;
+                float xv[8];
+                load8(p.x + (static_cast<size_t>(b * p.H + hi) * p.W + wi) * p.x_pitch + p.x_coff + c, xv);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    float a = xv[e];
+                    if (p.scale) a = __bfloat162float(__float2bfloat16_rn(apply_act(fmaf(a, sc[e], sf[e]), p.act)));
+                    acc[kh * 3 + kw][e] = fmaf(a, dv[e], acc[kh * 3 + kw][e]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) block_reduce8_atomic(acc[t], p.dw + static_cast<size_t>(t) * p.C + c, sh);
+}
+
+static int fill(DwArgs& p, const idcb_conv_desc* d) {
+    IDCB_REQUIRE(d != nullptr, "depthwise: null descriptor");
+    IDCB_REQUIRE(d->cin == d->cout && d->cin % 8 == 0, "depthwise: C must be a multiple of 8");
+    IDCB_REQUIRE(d->kh == 3 && d->kw == 3, "depthwise: only 3x3 is implemented");
+    IDCB_REQUIRE(d->x_pitch % 8 == 0 && d->x_coff % 8 == 0 && d->y_pitch % 8 == 0 && d->y_coff % 8 == 0,
+                 "depthwise: alignment");
+    p.B = d->batch; p.H = d->h; p.W = d->w; p.C = d->cin; p.Ho = d->ho; p.Wo = d->wo;
+    p.k = 3; p.stride = d->stride; p.pad_t = d->pad_t; p.pad_l = d->pad_l;
+    return 0;
+}
+
+static dim3 dw_grid(long long npos, int C) {
+    int gx = static_cast<int>(ceil_div_ll(npos, 256));
+    const int cap = ceil_div(8 * num_sms(), C / 8);
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    return dim3(gx, C / 8);
+}
+
+}  // namespace idcb
+
+using namespace idcb;
+
+extern "C" int idcb_dwconv_fprop(const idcb_conv_desc* d, const void* x, const void* w, void* y,
+                                 const float* scale, const float* shift, int act, float* stat_sum,
+                                 float* stat_sq, void* stream) {
+    DwArgs p{};
+    if (fill(p, d)) return 1;
+    p.x = (const __nv_bfloat16*)x; p.x_pitch = d->x_pitch; p.x_coff = d->x_coff;
+    p.w = (const __nv_bfloat16*)w;
+    p.y = (__nv_bfloat16*)y; p.y_pitch = d->y_pitch; p.y_coff = d->y_coff;
+    p.scale = scale; p.shift = shift; p.act = act; p.stat_a = stat_sum; p.stat_b = stat_sq;
+    const long long npos = 1LL * p.B * p.Ho * p.Wo;
+    if (npos == 0) return 0;
+    dw_fprop_kernel<<<dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_dwconv_dgrad(const idcb_conv_desc* d, const void* dy, const void* w, const void* x,
+                                 void* dx, const float* scale, const float* shift, int act,
+                                 float* stat_a, float* stat_b, void* stream) {
+    DwArgs p{};
+    if (fill(p, d)) return 1;
+    p.x = (const __nv_bfloat16*)x; p.x_pitch = d->x_pitch; p.x_coff = d->x_coff;
+    p.w = (const __nv_bfloat16*)w;
+    p.dy = (const __nv_bfloat16*)dy; p.dy_pitch = d->y_pitch; p.dy_coff = d->y_coff;
+    p.dx = (__nv_bfloat16*)dx; p.dx_pitch = d->x_pitch; p.dx_coff = d->x_coff;
+    p.scale = scale; p.shift = shift; p.act = act; p.stat_a = stat_a; p.stat_b = stat_b;
+    IDCB_REQUIRE(!(scale || stat_b) || x != nullptr, "dwconv_dgrad: x needed for the fused backward");
+    const long long npos = 1LL * p.B * p.H * p.W;
+    if (npos == 0) return 0;
+    dw_dgrad_kernel<<<dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_dwconv_wgrad(const idcb_conv_desc* d, const void* x, const void* dy, float* dw,
+                                 const float* scale, const float* shift, int act, void* stream) {
+    DwArgs p{};
+    if (fill(p, d)) return 1;
+    p.x = (const __nv_bfloat16*)x; p.x_pitch = d->x_pitch; p.x_coff = d->x_coff;
+    p.dy = (const __nv_bfloat16*)dy; p.dy_pitch = d->y_pitch; p.dy_coff = d->y_coff;
+    p.dw = dw;
+    p.scale = scale; p.shift = shift; p.act = act;
+    const long long npos = 1LL * p.B * p.Ho * p.Wo;
+    if (npos == 0) return 0;
+    int gx = static_cast<int>(ceil_div_ll(npos, 256 * 8));
+    const int cap = ceil_div(4 * num_sms(), p.C / 8);
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    dw_wgrad_kernel<<<dim3(gx, p.C / 8), 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}

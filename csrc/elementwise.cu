@@ -1,0 +1,585 @@
+// Bandwidth-bound helper kernels: BatchNorm bookkeeping (finalize / fold / backward coefficients),
+// per-channel affine transforms, channel statistics, pooling forward/backward, casts.
+//
+// These replace the cuDNN BatchNorm / pooling calls and Eigen element-wise kernels TensorFlow
+// launches for the reference's Keras layers (e.g.
+// /root/reference/dist_model_tf_dense.py:131 DenseNet BN/pool layers, dist_model_tf_vgg.py:119
+// VGG16 MaxPooling2D). Activations are NHWC bf16 addressed as (base, pitch, coff).
+#include "common.cuh"
+#include "../include/idcb200.h"
+
+namespace idcb {
+
+// ---------------------------------------------------------------------------------------------
+// BatchNorm per-channel kernels (C is small: <= 2048)
+// ---------------------------------------------------------------------------------------------
+__global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* __restrict__ sq,
+                                   float count, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float eps, float* scale,
+                                   float* shift, float* mean_out, float* rstd_out,
+                                   float* moving_mean, float* moving_var, float momentum, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float m = sum[c] / count;
+    float v = sq[c] / count - m * m;
+    v = fmaxf(v, 0.f);
+    const float r = rsqrtf(v + eps);
+    const float s = gamma[c] * r;
+    scale[c] = s;
+    shift[c] = beta[c] - m * s;
+    if (mean_out) mean_out[c] = m;
+    if (rstd_out) rstd_out[c] = r;
+    if (moving_mean) {
+        const float unbiased = count > 1.f ? v * (count / (count - 1.f)) : v;
+        moving_mean[c] = moving_mean[c] * momentum + m * (1.f - momentum);
+        moving_var[c] = moving_var[c] * momentum + unbiased * (1.f - momentum);
+    }
+}
+
+__global__ void bn_fold_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
+                               const float* __restrict__ mean, const float* __restrict__ var,
+                               float eps, float* scale, float* shift, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float s = gamma[c] * rsqrtf(var[c] + eps);
+    scale[c] = s;
+    shift[c] = beta[c] - mean[c] * s;
+}
+
+// BN backward coefficients from the epilogue sums of the consumer's dgrad (mode 2):
+//   sa = sum dpre, sb = sum dpre * x_raw
+//   dbeta = sa ; dgamma = rstd * (sb - mean * sa)
+// standalone BN (acc_s1 == null):  dx = A*g + B*x + C0 with
+//   A = scale, B = -scale*rstd*dgamma/N, C0 = -scale*(dbeta/N) + scale*rstd*mean*dgamma/N
+// shared-buffer BN (DenseNet): S1 += scale*dbeta ; S2 += scale*dgamma (coefficients come later from
+// bn_shared_coeffs once every consumer has contributed).
+__global__ void bn_bwd_coeffs_kernel(const float* __restrict__ sa, const float* __restrict__ sb,
+                                     const float* __restrict__ mean, const float* __restrict__ rstd,
+                                     const float* __restrict__ scale, float count, float* dgamma,
+                                     float* dbeta, float* A, float* B, float* C0, float* acc_s1,
+                                     float* acc_s2, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float a = sa[c], b = sb[c], m = mean[c], r = rstd[c], s = scale[c];
+    const float dg = r * (b - m * a);
+    if (dgamma) dgamma[c] += dg;
+    if (dbeta) dbeta[c] += a;
+    if (acc_s1) {
+        acc_s1[c] += s * a;
+        acc_s2[c] += s * dg;
+    }
+    if (A) {
+        A[c] = s;
+        B[c] = -s * r * dg / count;
+        C0[c] = -s * a / count + s * r * m * dg / count;
+    }
+}
+
+// DenseNet shared-buffer channels: dx = G - S1/N - xhat*S2/N = 1*G + B*x + C0
+__global__ void bn_shared_coeffs_kernel(const float* __restrict__ s1, const float* __restrict__ s2,
+                                        const float* __restrict__ mean,
+                                        const float* __restrict__ rstd, float count, float* A,
+                                        float* B, float* C0, int C) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float r = rstd[c], m = mean[c];
+    A[c] = 1.f;
+    B[c] = -r * s2[c] / count;
+    C0[c] = -s1[c] / count + r * m * s2[c] / count;
+}
+
+// ---------------------------------------------------------------------------------------------
+// y = act(scale*x + shift) (+ residual)     [bn apply / fold]
+// ---------------------------------------------------------------------------------------------
+__global__ void affine_act_kernel(const __nv_bfloat16* __restrict__ x, int x_pitch, int x_coff,
+                                  __nv_bfloat16* y, int y_pitch, int y_coff,
+                                  const float* __restrict__ scale, const float* __restrict__ shift,
+                                  int act, const __nv_bfloat16* __restrict__ res, int r_pitch,
+                                  int r_coff, long long M, int C) {
+    const int c8 = C >> 3;
+    const long long total = M * c8;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long m = i / c8;
+        const int c = static_cast<int>(i - m * c8) * 8;
+        uint4 q = *reinterpret_cast<const uint4*>(x + m * x_pitch + x_coff + c);
+        uint4 rr = make_uint4(0, 0, 0, 0);
+        if (res) rr = *reinterpret_cast<const uint4*>(res + m * r_pitch + r_coff + c);
+        uint32_t* w = reinterpret_cast<uint32_t*>(&q);
+        const uint32_t* rw = reinterpret_cast<const uint32_t*>(&rr);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            float2 f = unpack_bf16x2(w[e]);
+            const float s0 = scale ? scale[c + 2 * e] : 1.f, s1 = scale ? scale[c + 2 * e + 1] : 1.f;
+            const float t0 = shift ? shift[c + 2 * e] : 0.f, t1 = shift ? shift[c + 2 * e + 1] : 0.f;
+            f.x = apply_act(fmaf(f.x, s0, t0), act);
+            f.y = apply_act(fmaf(f.y, s1, t1), act);
+            if (res) {
+                float2 r2 = unpack_bf16x2(rw[e]);
+                f.x += r2.x;
+                f.y += r2.y;
+            }
+            w[e] = pack_bf16x2(f.x, f.y);
+        }
+        *reinterpret_cast<uint4*>(y + m * y_pitch + y_coff + c) = q;
+    }
+}
+
+// out(bf16) = A[c]*g + B[c]*x + C0[c];  g is fp32 (G buffer) or bf16 (dpre)
+template <bool kGFloat>
+__global__ void affine2_kernel(const void* __restrict__ g, int g_pitch, int g_coff,
+                               const __nv_bfloat16* __restrict__ x, int x_pitch, int x_coff,
+                               __nv_bfloat16* out, int o_pitch, int o_coff,
+                               const float* __restrict__ A, const float* __restrict__ B,
+                               const float* __restrict__ C0, long long M, int C) {
+    const int c8 = C >> 3;
+    const long long total = M * c8;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long m = i / c8;
+        const int c = static_cast<int>(i - m * c8) * 8;
+        float gv[8];
+        if (kGFloat) {
+            const float* gp = static_cast<const float*>(g) + m * g_pitch + g_coff + c;
+            float4 a = *reinterpret_cast<const float4*>(gp);
+            float4 b = *reinterpret_cast<const float4*>(gp + 4);
+            gv[0] = a.x; gv[1] = a.y; gv[2] = a.z; gv[3] = a.w;
+            gv[4] = b.x; gv[5] = b.y; gv[6] = b.z; gv[7] = b.w;
+        } else {
+            uint4 q = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(g) +
+                                                      m * g_pitch + g_coff + c);
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(&q);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                float2 f = unpack_bf16x2(w[e]);
+                gv[2 * e] = f.x;
+                gv[2 * e + 1] = f.y;
+            }
+        }
+        uint4 xq = *reinterpret_cast<const uint4*>(x + m * x_pitch + x_coff + c);
+        const uint32_t* xw = reinterpret_cast<const uint32_t*>(&xq);
+        uint4 o;
+        uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            float2 xf = unpack_bf16x2(xw[e]);
+            const int c0 = c + 2 * e;
+            const float r0 = fmaf(A[c0], gv[2 * e], fmaf(B[c0], xf.x, C0[c0]));
+            const float r1 = fmaf(A[c0 + 1], gv[2 * e + 1], fmaf(B[c0 + 1], xf.y, C0[c0 + 1]));
+            ow[e] = pack_bf16x2(r0, r1);
+        }
+        *reinterpret_cast<uint4*>(out + m * o_pitch + o_coff + c) = o;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Per-channel sum / sum of squares of a bf16 NHWC slice (for BN stats of tensors that are not
+// produced by a GEMM epilogue). grid.x = channel groups of 64, grid.y = row splits.
+// ---------------------------------------------------------------------------------------------
+__global__ void channel_stats_kernel(const __nv_bfloat16* __restrict__ x, int pitch, int coff,
+                                     long long M, int C, float* sum, float* sq) {
+    // block = 256 threads = 8 channel-octets x 32 row lanes
+    const int oct = threadIdx.x & 7;
+    const int rl = threadIdx.x >> 3;
+    const int c = blockIdx.x * 64 + oct * 8;
+    float s[8], q[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s[e] = q[e] = 0.f;
+    if (c < C) {
+        for (long long m = blockIdx.y * 32 + rl; m < M; m += (long long)gridDim.y * 32) {
+            uint4 v = *reinterpret_cast<const uint4*>(x + m * pitch + coff + c);
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                float2 f = unpack_bf16x2(w[e]);
+                s[2 * e] += f.x; q[2 * e] += f.x * f.x;
+                s[2 * e + 1] += f.y; q[2 * e + 1] += f.y * f.y;
+            }
+        }
+    }
+    __shared__ float sh[2][32][65];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        sh[0][rl][oct * 8 + e] = s[e];
+        sh[1][rl][oct * 8 + e] = q[e];
+    }
+    __syncthreads();
+    if (threadIdx.x < 128) {
+        const int which = threadIdx.x >> 6;
+        const int ch = threadIdx.x & 63;
+        float t = 0.f;
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) t += sh[which][r][ch];
+        if (blockIdx.x * 64 + ch < C) atomicAdd((which ? sq : sum) + blockIdx.x * 64 + ch, t);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Pooling. One thread handles 8 channels of one output position.
+//   max: y = max over window of act(scale*x+shift) (prologue optional); window positions outside the
+//        input (pad) are skipped (equivalent to Keras ZeroPadding2D + VALID pooling on ReLU outputs).
+//   avg: y = mean over the k x k window (no padding).
+// ---------------------------------------------------------------------------------------------
+struct PoolArgs {
+    const __nv_bfloat16* x; int x_pitch, x_coff;
+    __nv_bfloat16* y; int y_pitch, y_coff;
+    int B, H, W, C, Ho, Wo, k, stride, pad;
+    const float* scale; const float* shift; int act;
+    int is_max;
+    float* stat_sum; float* stat_sq;
+};
+
+__global__ void pool_fwd_kernel(PoolArgs p) {
+    const int c8 = p.C >> 3;
+    const long long total = 1LL * p.B * p.Ho * p.Wo * c8;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c = static_cast<int>(i % c8) * 8;
+        long long pos = i / c8;
+        const int wo = static_cast<int>(pos % p.Wo);
+        pos /= p.Wo;
+        const int ho = static_cast<int>(pos % p.Ho);
+        const int b = static_cast<int>(pos / p.Ho);
+        float acc[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = p.is_max ? -3.0e38f : 0.f;
+        bool any = false;
+        for (int kh = 0; kh < p.k; ++kh) {
+            const int hi = ho * p.stride - p.pad + kh;
+            if (hi < 0 || hi >= p.H) continue;
+            for (int kw = 0; kw < p.k; ++kw) {
+                const int wi = wo * p.stride - p.pad + kw;
+                if (wi < 0 || wi >= p.W) continue;
+                any = true;
+                uint4 v = *reinterpret_cast<const uint4*>(
+                    p.x + (static_cast<long long>(b * p.H + hi) * p.W + wi) * p.x_pitch + p.x_coff + c);
+                const uint32_t* w = reinterpret_cast<const uint32_t*>(&v);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    float2 f = unpack_bf16x2(w[e]);
+                    if (p.scale) {
+                        f.x = apply_act(fmaf(f.x, p.scale[c + 2 * e], p.shift[c + 2 * e]), p.act);
+                        f.y = apply_act(fmaf(f.y, p.scale[c + 2 * e + 1], p.shift[c + 2 * e + 1]), p.act);
+                        // the pooled tensor is stored in bf16; compare in that precision
+                        f.x = __bfloat162float(__float2bfloat16_rn(f.x));
+                        f.y = __bfloat162float(__float2bfloat16_rn(f.y));
+                    }
+                    if (p.is_max) {
+                        acc[2 * e] = fmaxf(acc[2 * e], f.x);
+                        acc[2 * e + 1] = fmaxf(acc[2 * e + 1], f.y);
+                    } else {
+                        acc[2 * e] += f.x;
+                        acc[2 * e + 1] += f.y;
+                    }
+                }
+            }
+        }
+        const float inv = 1.f / (p.k * p.k);
+        uint4 o;
+        uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            float a0 = acc[2 * e], a1 = acc[2 * e + 1];
+            if (!p.is_max) { a0 *= inv; a1 *= inv; }
+            if (!any) { a0 = 0.f; a1 = 0.f; }
+            ow[e] = pack_bf16x2(a0, a1);
+        }
+        const long long opos = (static_cast<long long>(b * p.Ho + ho) * p.Wo + wo);
+        *reinterpret_cast<uint4*>(p.y + opos * p.y_pitch + p.y_coff + c) = o;
+    }
+}
+
+// Backward, gather form: one thread = 8 channels of one INPUT position.
+//   max : dx = sum over windows containing the position of dy * [a == y_window]  (a = act(scale*x+shift));
+//         then the activation/affine backward: dx *= act'(pre) (dpre w.r.t. scale*x+shift; the caller
+//         handles the BN part) ; relu_mask_src (optional): dx *= (x > 0) when x itself is a ReLU output.
+//   avg : dx = sum over windows of dy / k^2.
+// stat_a[c] += sum dx ; stat_b[c] += sum dx * x_raw   (bias gradient / BN backward sums)
+struct PoolBwdArgs {
+    const __nv_bfloat16* x; int x_pitch, x_coff;     // forward input (raw)
+    const __nv_bfloat16* y; int y_pitch, y_coff;     // forward output (pooled), max only
+    const __nv_bfloat16* dy; int dy_pitch, dy_coff;
+    __nv_bfloat16* dx; int dx_pitch, dx_coff;
+    int B, H, W, C, Ho, Wo, k, stride, pad;
+    const float* scale; const float* shift; int act;
+    int is_max;
+    int relu_mask;   // dx *= (x > 0)
+    float* stat_a; float* stat_b;
+};
+
+__global__ void pool_bwd_kernel(PoolBwdArgs p) {
+    const int c8 = p.C >> 3;
+    const long long total = 1LL * p.B * p.H * p.W * c8;
+    __shared__ float s_a[256][9];   // padded to dodge bank conflicts on the final reduce
+    float sa[8], sb[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sa[e] = sb[e] = 0.f;
+    // each block walks a fixed channel octet so the statistics can be reduced per block
+    const int oct = blockIdx.y;
+    const int c = oct * 8;
+    const long long npos = 1LL * p.B * p.H * p.W;
+    (void)total;
+    for (long long pos = blockIdx.x * (long long)blockDim.x + threadIdx.x; pos < npos;
+         pos += (long long)gridDim.x * blockDim.x) {
+        const int wi = static_cast<int>(pos % p.W);
+        const long long t = pos / p.W;
+        const int hi = static_cast<int>(t % p.H);
+        const int b = static_cast<int>(t / p.H);
+        uint4 xv = *reinterpret_cast<const uint4*>(p.x + pos * p.x_pitch + p.x_coff + c);
+        const uint32_t* xw = reinterpret_cast<const uint32_t*>(&xv);
+        float xr[8], a[8], pre[8];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            float2 f = unpack_bf16x2(xw[e]);
+            xr[2 * e] = f.x; xr[2 * e + 1] = f.y;
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            pre[e] = p.scale ? fmaf(xr[e], p.scale[c + e], p.shift[c + e]) : xr[e];
+            a[e] = p.scale ? __bfloat162float(__float2bfloat16_rn(apply_act(pre[e], p.act))) : xr[e];
+        }
+        float g[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] = 0.f;
+        // windows (ho, wo) with ho*stride - pad <= hi < ho*stride - pad + k
+        const int ho_lo = max(0, (hi + p.pad - p.k + p.stride) / p.stride);
+        const int ho_hi = min(p.Ho - 1, (hi + p.pad) / p.stride);
+        const int wo_lo = max(0, (wi + p.pad - p.k + p.stride) / p.stride);
+        const int wo_hi = min(p.Wo - 1, (wi + p.pad) / p.stride);
+        for (int ho = ho_lo; ho <= ho_hi; ++ho)
+            for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+                const long long op = (static_cast<long long>(b * p.Ho + ho) * p.Wo + wo);
+                uint4 dv = *reinterpret_cast<const uint4*>(p.dy + op * p.dy_pitch + p.dy_coff + c);
+                const uint32_t* dw = reinterpret_cast<const uint32_t*>(&dv);
+                if (p.is_max) {
+                    uint4 yv = *reinterpret_cast<const uint4*>(p.y + op * p.y_pitch + p.y_coff + c);
+                    const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        float2 d = unpack_bf16x2(dw[e]);
+                        float2 yy = unpack_bf16x2(yw[e]);
+                        if (a[2 * e] == yy.x) g[2 * e] += d.x;
+                        if (a[2 * e + 1] == yy.y) g[2 * e + 1] += d.y;
+                    }
+                } else {
+                    const float inv = 1.f / (p.k * p.k);
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        float2 d = unpack_bf16x2(dw[e]);
+                        g[2 * e] += d.x * inv;
+                        g[2 * e + 1] += d.y * inv;
+                    }
+                }
+            }
+        uint4 o;
+        uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            if (p.scale) g[e] *= act_mask(pre[e], p.act);
+            if (p.relu_mask && !(xr[e] > 0.f)) g[e] = 0.f;
+            g[e] = __bfloat162float(__float2bfloat16_rn(g[e]));
+            sa[e] += g[e];
+            sb[e] += g[e] * xr[e];
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) ow[e] = pack_bf16x2(g[2 * e], g[2 * e + 1]);
+        *reinterpret_cast<uint4*>(p.dx + pos * p.dx_pitch + p.dx_coff + c) = o;
+    }
+    if (p.stat_a == nullptr) return;
+    for (int pass = 0; pass < 2; ++pass) {
+        if (pass == 1 && p.stat_b == nullptr) break;
+        __syncthreads();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s_a[threadIdx.x][e] = pass ? sb[e] : sa[e];
+        __syncthreads();
+        if (threadIdx.x < 8) {
+            float t = 0.f;
+            for (int r = 0; r < (int)blockDim.x; ++r) t += s_a[r][threadIdx.x];
+            atomicAdd((pass ? p.stat_b : p.stat_a) + c + threadIdx.x, t);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// casts / input packing
+// ---------------------------------------------------------------------------------------------
+// fp32 NHWC [.., Cin] -> bf16 NHWC [.., Cpad] with zero fill of the pad channels.
+__global__ void pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* y, long long npos,
+                                  int cin, int cpad) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < npos * cpad;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long pos = i / cpad;
+        const int c = static_cast<int>(i - pos * cpad);
+        y[i] = __float2bfloat16_rn(c < cin ? x[pos * cin + c] : 0.f);
+    }
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* y, long long n) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x)
+        y[i] = __float2bfloat16_rn(x[i]);
+}
+
+static inline int ew_grid(long long work_items, int threads) {
+    long long g = ceil_div_ll(work_items, threads);
+    const long long cap = 8LL * num_sms();
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return static_cast<int>(g);
+}
+
+}  // namespace idcb
+
+using namespace idcb;
+typedef const __nv_bfloat16* cbf;
+typedef __nv_bfloat16* bf;
+
+extern "C" int idcb_bn_finalize(const float* sum, const float* sq, float count, const float* gamma,
+                                const float* beta, float eps, float* scale, float* shift,
+                                float* mean_out, float* rstd_out, float* moving_mean,
+                                float* moving_var, float momentum, int C, void* stream) {
+    IDCB_REQUIRE(C > 0 && count > 0.f, "bn_finalize: bad sizes");
+    bn_finalize_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(
+        sum, sq, count, gamma, beta, eps, scale, shift, mean_out, rstd_out, moving_mean, moving_var,
+        momentum, C);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_bn_fold(const float* gamma, const float* beta, const float* mean,
+                            const float* var, float eps, float* scale, float* shift, int C,
+                            void* stream) {
+    bn_fold_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(gamma, beta, mean, var, eps,
+                                                                       scale, shift, C);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_bn_bwd_coeffs(const float* sa, const float* sb, const float* mean,
+                                  const float* rstd, const float* scale, float count, float* dgamma,
+                                  float* dbeta, float* A, float* B, float* C0, float* acc_s1,
+                                  float* acc_s2, int C, void* stream) {
+    IDCB_REQUIRE((acc_s1 == nullptr) == (acc_s2 == nullptr), "bn_bwd_coeffs: S1/S2 go together");
+    bn_bwd_coeffs_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(
+        sa, sb, mean, rstd, scale, count, dgamma, dbeta, A, B, C0, acc_s1, acc_s2, C);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_bn_shared_coeffs(const float* s1, const float* s2, const float* mean,
+                                     const float* rstd, float count, float* A, float* B, float* C0,
+                                     int C, void* stream) {
+    bn_shared_coeffs_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(s1, s2, mean, rstd,
+                                                                                count, A, B, C0, C);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_affine_act(const void* x, int x_pitch, int x_coff, void* y, int y_pitch,
+                               int y_coff, const float* scale, const float* shift, int act,
+                               const void* res, int r_pitch, int r_coff, long long M, int C,
+                               void* stream) {
+    IDCB_REQUIRE(C % 8 == 0 && x_pitch % 8 == 0 && y_pitch % 8 == 0 && x_coff % 8 == 0 &&
+                     y_coff % 8 == 0 && r_pitch % 8 == 0 && r_coff % 8 == 0,
+                 "affine_act: channel counts/pitches must be multiples of 8");
+    if (M == 0) return 0;
+    affine_act_kernel<<<ew_grid(M * (C / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+        (cbf)x, x_pitch, x_coff, (bf)y, y_pitch, y_coff, scale, shift, act, (cbf)res, r_pitch, r_coff,
+        M, C);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_affine2(const void* g, int g_is_float, int g_pitch, int g_coff, const void* x,
+                            int x_pitch, int x_coff, void* out, int o_pitch, int o_coff,
+                            const float* A, const float* B, const float* C0, long long M, int C,
+                            void* stream) {
+    IDCB_REQUIRE(C % 8 == 0 && g_pitch % 8 == 0 && g_coff % 8 == 0 && x_pitch % 8 == 0 &&
+                     x_coff % 8 == 0 && o_pitch % 8 == 0 && o_coff % 8 == 0,
+                 "affine2: channel counts/pitches must be multiples of 8");
+    if (M == 0) return 0;
+    const int grid = ew_grid(M * (C / 8), 256);
+    if (g_is_float)
+        affine2_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(
+            g, g_pitch, g_coff, (cbf)x, x_pitch, x_coff, (bf)out, o_pitch, o_coff, A, B, C0, M, C);
+    else
+        affine2_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(
+            g, g_pitch, g_coff, (cbf)x, x_pitch, x_coff, (bf)out, o_pitch, o_coff, A, B, C0, M, C);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_channel_stats(const void* x, int pitch, int coff, long long M, int C, float* sum,
+                                  float* sq, void* stream) {
+    IDCB_REQUIRE(C % 8 == 0 && pitch % 8 == 0 && coff % 8 == 0, "channel_stats: alignment");
+    if (M == 0) return 0;
+    int splits = static_cast<int>(ceil_div_ll(M, 32 * 16));
+    const int cap = ceil_div(4 * num_sms(), ceil_div(C, 64));
+    if (splits > cap) splits = cap;
+    if (splits < 1) splits = 1;
+    dim3 grid(ceil_div(C, 64), splits);
+    channel_stats_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((cbf)x, pitch, coff, M, C, sum, sq);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_pool_fwd(const idcb_pool_desc* d, const void* x, void* y, const float* scale,
+                             const float* shift, int act, void* stream) {
+    IDCB_REQUIRE(d && d->c % 8 == 0 && d->x_pitch % 8 == 0 && d->y_pitch % 8 == 0 &&
+                     d->x_coff % 8 == 0 && d->y_coff % 8 == 0, "pool_fwd: alignment");
+    PoolArgs p{};
+    p.x = (cbf)x; p.x_pitch = d->x_pitch; p.x_coff = d->x_coff;
+    p.y = (bf)y; p.y_pitch = d->y_pitch; p.y_coff = d->y_coff;
+    p.B = d->batch; p.H = d->h; p.W = d->w; p.C = d->c; p.Ho = d->ho; p.Wo = d->wo;
+    p.k = d->k; p.stride = d->stride; p.pad = d->pad;
+    p.scale = scale; p.shift = shift; p.act = act; p.is_max = d->is_max;
+    const long long items = 1LL * p.B * p.Ho * p.Wo * (p.C / 8);
+    if (items == 0) return 0;
+    pool_fwd_kernel<<<ew_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_pool_bwd(const idcb_pool_desc* d, const void* x, const void* y, const void* dy,
+                             int dy_pitch, int dy_coff, void* dx, int dx_pitch, int dx_coff,
+                             const float* scale, const float* shift, int act, int relu_mask,
+                             float* stat_a, float* stat_b, void* stream) {
+    IDCB_REQUIRE(d && d->c % 8 == 0 && d->x_pitch % 8 == 0 && d->y_pitch % 8 == 0 &&
+                     dy_pitch % 8 == 0 && dx_pitch % 8 == 0 && dy_coff % 8 == 0 && dx_coff % 8 == 0,
+                 "pool_bwd: alignment");
+    PoolBwdArgs p{};
+    p.x = (cbf)x; p.x_pitch = d->x_pitch; p.x_coff = d->x_coff;
+    p.y = (cbf)y; p.y_pitch = d->y_pitch; p.y_coff = d->y_coff;
+    p.dy = (cbf)dy; p.dy_pitch = dy_pitch; p.dy_coff = dy_coff;
+    p.dx = (bf)dx; p.dx_pitch = dx_pitch; p.dx_coff = dx_coff;
+    p.B = d->batch; p.H = d->h; p.W = d->w; p.C = d->c; p.Ho = d->ho; p.Wo = d->wo;
+    p.k = d->k; p.stride = d->stride; p.pad = d->pad;
+    p.scale = scale; p.shift = shift; p.act = act; p.is_max = d->is_max; p.relu_mask = relu_mask;
+    p.stat_a = stat_a; p.stat_b = stat_b;
+    const long long npos = 1LL * p.B * p.H * p.W;
+    if (npos == 0) return 0;
+    int gx = static_cast<int>(ceil_div_ll(npos, 256));
+    const int cap = ceil_div(8 * num_sms(), p.C / 8);
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    dim3 grid(gx, p.C / 8);
+    pool_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_pack_input(const float* x, void* y, long long npos, int cin, int cpad,
+                               void* stream) {
+    if (npos == 0) return 0;
+    pack_input_kernel<<<ew_grid(npos * cpad, 256), 256, 0, (cudaStream_t)stream>>>(x, (bf)y, npos, cin,
+                                                                                  cpad);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_cast_f32_bf16(const float* x, void* y, long long n, void* stream) {
+    if (n == 0) return 0;
+    cast_f32_bf16_kernel<<<ew_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(x, (bf)y, n);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}

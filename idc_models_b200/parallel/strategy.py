@@ -1,0 +1,145 @@
+"""Distribution strategies with the ``tf.distribute`` surface the reference scripts use
+(``strategy.scope()``, ``strategy.num_replicas_in_sync``), re-designed as one process per replica.
+
+* :class:`MirroredStrategy` — synchronous data parallelism (SURVEY.md 2.B B12, 2.D;
+  /root/reference/dist_model_tf_dense.py:22, dist_model_tf_mobile.py:115, dist_model_tf_vgg.py:115):
+  identical variables on every replica, the global batch split across replicas, ONE packed gradient
+  sum per step followed by an identical update everywhere. ``comm='fused'`` runs the hand-written
+  NVLink kernel that fuses the reduction with the optimizer update (parallel/fused_comm.py);
+  ``comm='nccl'``/``'gloo'`` call the library all-reduce and then the optimizer (the baseline).
+* :class:`CentralStorageStrategy` — variables and optimizer state owned by ONE replica
+  (dist_model_tf_dense.py:24 behind ``use_mirror=False``): gradients are reduced to
+  the owner, the owner updates, new values are broadcast.
+* default (no scope) — a single replica.
+"""
+from __future__ import annotations
+
+import contextlib
+import threading
+
+import torch
+
+from .world import World
+
+_tls = threading.local()
+
+
+def current_strategy() -> "Strategy":
+    s = getattr(_tls, "strategy", None)
+    return s if s is not None else _DEFAULT
+
+
+class Strategy:
+    name = "default"
+
+    def __init__(self, world: World | None = None, comm: str = "auto"):
+        self.world = world or World.single()
+        if comm == "auto":
+            comm = "nccl" if self.world.device.type == "cuda" else "gloo"
+        self.comm = comm
+        self._fused = None
+
+    @property
+    def num_replicas_in_sync(self) -> int:
+        return self.world.size
+
+    @property
+    def replica_id(self) -> int:
+        return self.world.rank
+
+    @contextlib.contextmanager
+    def scope(self):
+        prev = getattr(_tls, "strategy", None)
+        _tls.strategy = self
+        try:
+            yield self
+        finally:
+            _tls.strategy = prev
+
+    # ---- batch splitting (global batch -> this replica's slice) ------------------------------
+    def local_slice(self, n: int) -> slice:
+        per = -(-n // self.world.size)
+        lo = min(self.world.rank * per, n)
+        return slice(lo, min(lo + per, n))
+
+    # ---- variable creation (C3): make replicas identical -------------------------------------
+    def sync_variables(self, store) -> None:
+        if self.world.is_distributed:
+            self.world.broadcast(store.master, 0)
+            self.world.broadcast(store.stats, 0)
+            store.refresh_shadow()
+
+    # ---- per-step gradient reduction + update (C1 + K13) --------------------------------------
+    def reduce_and_apply(self, store, optimizer, grad_scale: float = 1.0) -> None:
+        """Sum gradients over replicas and apply the optimizer on every replica."""
+        w = self.world
+        if not w.is_distributed:
+            optimizer.apply(grad_scale)
+            return
+        if self.comm == "fused":
+            self._fused_comm(store).allreduce_apply(optimizer, grad_scale)
+            return
+        for b, e in optimizer.ranges:
+            w.all_reduce_sum(store.grad[b:e])
+        optimizer.apply(grad_scale)
+
+    def _fused_comm(self, store):
+        if self._fused is None or self._fused.store is not store:
+            from .fused_comm import FusedComm
+            self._fused = FusedComm(self.world, store)
+        return self._fused
+
+    # ---- scalar metric reduction (C2) -----------------------------------------------------------
+    def reduce_scalars(self, t: torch.Tensor) -> torch.Tensor:
+        return self.world.all_reduce_sum(t)
+
+    # ---- BN moving statistics: MEAN over replicas when read (C4) -------------------------------
+    def aggregate_moving_stats(self, store) -> None:
+        if self.world.is_distributed and store.n_stats:
+            self.world.all_reduce_sum(store.stats)
+            store.stats.div_(self.world.size)
+
+
+class MirroredStrategy(Strategy):
+    name = "mirrored"
+
+    def __init__(self, devices=None, world: World | None = None, comm: str = "auto"):
+        """``devices`` is accepted for signature parity (dist_model_tf_dense.py:22); the number of
+        replicas is the number of launched processes (torchrun ``--nproc-per-node``)."""
+        super().__init__(world or World.from_env(), comm)
+        self.devices = devices
+
+
+class CentralStorageStrategy(Strategy):
+    name = "central_storage"
+
+    def __init__(self, compute_devices=None, parameter_device=None, world: World | None = None,
+                 comm: str = "auto", owner: int = 0):
+        super().__init__(world or World.from_env(), comm)
+        self.owner = owner
+
+    def reduce_and_apply(self, store, optimizer, grad_scale: float = 1.0) -> None:
+        w = self.world
+        if not w.is_distributed:
+            optimizer.apply(grad_scale)
+            return
+        # gradients -> owner ; owner applies ; fresh variables -> everyone
+        for b, e in optimizer.ranges:
+            w.reduce_to(store.grad[b:e], self.owner)
+        if w.rank == self.owner:
+            optimizer.apply(grad_scale)
+        else:
+            for b, e in optimizer.ranges:
+                store.grad[b:e].zero_()
+        for b, e in optimizer.ranges:
+            w.broadcast(store.master[b:e], self.owner)
+        if store.shadow is not None:
+            for b, e in optimizer.ranges:
+                store.shadow[b:e].copy_(store.master[b:e])
+
+
+_DEFAULT = Strategy(World.single("cpu"), comm="none")
+
+
+def get_strategy() -> Strategy:
+    return current_strategy()

@@ -1,0 +1,210 @@
+"""compile / fit / evaluate / predict with Keras semantics:
+
+* ``fit`` runs epochs ``initial_epoch .. epochs-1`` — the reference's phase 2 passes
+  ``initial_epoch=history.epoch[-1]`` (= 9) and ``epochs=20``, i.e. 11 epochs
+  (/root/reference/dist_model_tf_mobile.py:157-159);
+* after every epoch the FULL ``validation_data`` is evaluated; ``History.history`` has the keys
+  ``loss / <metric> / val_loss / val_<metric>`` and ``History.epoch`` the epoch indices;
+* ``evaluate(ds, steps=20)`` consumes at most 20 batches and returns ``[loss, metric...]``
+  (dist_model_tf_mobile.py:134);
+* under a strategy each replica takes its slice of every global batch, the loss is divided by the
+  GLOBAL batch size, gradients are summed over replicas and the same update is applied everywhere
+  (SURVEY.md B8, B12); loss / metric accumulators are summed over replicas (C2).
+
+Recompiling creates fresh optimizer state (dist_model_tf_mobile.py:152-154).
+"""
+from __future__ import annotations
+
+import sys
+import time
+
+import torch
+
+from ..optim import optimizers as O
+from . import losses as L
+from . import metrics as M
+
+
+class History:
+    def __init__(self):
+        self.history: dict[str, list] = {}
+        self.epoch: list[int] = []
+
+    def _append(self, epoch: int, logs: dict) -> None:
+        self.epoch.append(epoch)
+        for k, v in logs.items():
+            self.history.setdefault(k, []).append(v)
+
+
+class Callback:
+    def set_model(self, model):
+        self.model = model
+
+    def on_train_begin(self, logs=None): ...
+    def on_epoch_begin(self, epoch, logs=None): ...
+    def on_epoch_end(self, epoch, logs=None): ...
+    def on_train_end(self, logs=None): ...
+
+
+class ModelCheckpoint(Callback):
+    """``tf.keras.callbacks.ModelCheckpoint(filepath, save_weights_only=True, verbose=1)`` — weights
+    are written at the end of every epoch, overwriting (fed_model.py:100-105,135)."""
+
+    def __init__(self, filepath: str, save_weights_only: bool = True, verbose: int = 0, **kw):
+        self.filepath, self.verbose = filepath, verbose
+
+    def on_epoch_end(self, epoch, logs=None):
+        path = self.filepath.format(epoch=epoch + 1, **(logs or {}))
+        if self.verbose:
+            print(f"\nEpoch {epoch + 1:05d}: saving model to {path}")
+        self.model.save_weights(path)
+
+
+def compile_model(net, optimizer, loss, metrics) -> None:
+    net.loss = L.get(loss if loss is not None else ("bce" if net.n_outputs == 1 else "cce"))
+    net.metrics = [M.get(m, net.n_outputs) for m in metrics]
+    # accuracy rule used by the in-kernel counters (and by the reference executor)
+    net.acc_threshold, net.acc_on_prob = 0.5, False
+    for m in net.metrics:
+        if isinstance(m, M.BinaryAccuracy):
+            net.acc_threshold, net.acc_on_prob = m.threshold, m.threshold_on == "prob"
+    opt = O.get(optimizer)
+    if opt.store is not None:          # a bound optimizer object reused for another compile
+        opt = opt.clone()
+    ranges = net.store.ranges(net.trainable_layer_indices())
+    net.optimizer = opt.bind(net.store, ranges)
+    net.store.grad.zero_()
+    net._dirty = False
+    net.executor.prepare()
+
+
+def _check_compiled(net):
+    if net.optimizer is None or net.loss is None:
+        raise RuntimeError("model.compile(...) must be called before fit/evaluate")
+    if net._dirty:
+        # Keras semantics: changing `trainable` after compile has no effect until the next compile.
+        pass
+
+
+def _builtin_metric(m) -> bool:
+    return isinstance(m, (M.BinaryAccuracy, M.CategoricalAccuracy))
+
+
+def _as_batches(data):
+    if isinstance(data, tuple) and len(data) == 2 and isinstance(data[0], torch.Tensor):
+        return [data]
+    return data
+
+
+class _Accum:
+    """Device-side (loss_sum, correct, count) accumulator + host-side extra metrics."""
+
+    def __init__(self, net):
+        self.net = net
+        self.acc = torch.zeros(3, dtype=torch.float32, device=net.device)
+        self.extra = [m for m in net.metrics if not _builtin_metric(m)]
+        for m in self.extra:
+            m.reset()
+
+    def add(self, stats, logits, y):
+        self.acc += stats.to(self.acc.dtype)
+        for m in self.extra:
+            if logits is not None and logits.shape[0]:
+                m.update(logits.float().cpu(), y.cpu())
+
+    def result(self, prefix: str = "") -> dict:
+        net = self.net
+        acc = net.strategy.reduce_scalars(self.acc.clone())
+        loss_sum, correct, count = (float(v) for v in acc.tolist())
+        out = {prefix + "loss": loss_sum / count if count else 0.0}
+        for m in net.metrics:
+            if _builtin_metric(m):
+                out[prefix + m.name] = correct / count if count else 0.0
+            else:
+                t = torch.tensor([m.total, m.count], dtype=torch.float64)
+                if net.strategy.world.is_distributed:
+                    t = net.strategy.reduce_scalars(t.to(net.device)).cpu()
+                out[prefix + m.name] = float(t[0] / t[1]) if t[1] else 0.0
+        return out
+
+
+def train_on_batch(net, x, y) -> dict:
+    _check_compiled(net)
+    n = x.shape[0]
+    sl = net.strategy.local_slice(n)
+    stats, logits = net.executor.train_batch(x[sl], y[sl], n)
+    net.strategy.reduce_and_apply(net.store, net.optimizer, 1.0)
+    return {"stats": stats, "logits": logits}
+
+
+def fit(net, data, epochs, initial_epoch, validation_data, callbacks, verbose, steps_per_epoch,
+        validation_steps):
+    _check_compiled(net)
+    hist = History()
+    for cb in callbacks:
+        cb.set_model(net)
+        cb.on_train_begin()
+    net.stop_training = False
+    for epoch in range(initial_epoch, epochs):
+        t0 = time.time()
+        for cb in callbacks:
+            cb.on_epoch_begin(epoch)
+        accum = _Accum(net)
+        nb = 0
+        for x, y in _as_batches(data):
+            n = x.shape[0]
+            sl = net.strategy.local_slice(n)
+            xs, ys = x[sl], y[sl]
+            stats, logits = net.executor.train_batch(xs, ys, n)
+            net.strategy.reduce_and_apply(net.store, net.optimizer, 1.0)
+            accum.add(stats, logits, ys)
+            nb += 1
+            if steps_per_epoch is not None and nb >= steps_per_epoch:
+                break
+        logs = accum.result()
+        if validation_data is not None:
+            logs.update(_evaluate(net, validation_data, validation_steps, prefix="val_"))
+        hist._append(epoch, logs)
+        for cb in callbacks:
+            cb.on_epoch_end(epoch, logs)
+        if verbose and net.strategy.world.rank == 0:
+            body = " - ".join(f"{k}: {v:.4f}" for k, v in logs.items())
+            print(f"Epoch {epoch + 1}/{epochs} - {time.time() - t0:.0f}s - {body}")
+            sys.stdout.flush()
+        if net.stop_training:
+            break
+    for cb in callbacks:
+        cb.on_train_end()
+    net.history = hist
+    return hist
+
+
+def _evaluate(net, data, steps, prefix="") -> dict:
+    accum = _Accum(net)
+    nb = 0
+    for x, y in _as_batches(data):
+        sl = net.strategy.local_slice(x.shape[0])
+        xs, ys = x[sl], y[sl]
+        stats, logits = net.executor.eval_batch(xs, ys)
+        accum.add(stats, logits, ys)
+        nb += 1
+        if steps is not None and nb >= steps:
+            break
+    return accum.result(prefix)
+
+
+def evaluate(net, data, steps, verbose, return_dict):
+    _check_compiled(net)
+    logs = _evaluate(net, data, steps)
+    if verbose and net.strategy.world.rank == 0:
+        print(" - ".join(f"{k}: {v:.4f}" for k, v in logs.items()))
+    if return_dict:
+        return logs
+    return [logs["loss"]] + [logs[m.name] for m in net.metrics]
+
+
+def predict(net, x):
+    if isinstance(x, torch.Tensor):
+        return net.executor.predict(x)
+    outs = [net.executor.predict(b[0] if isinstance(b, tuple) else b) for b in x]
+    return torch.cat(outs, 0)

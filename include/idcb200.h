@@ -94,6 +94,101 @@ int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const void* w, void
 int idcb_conv_wgrad(const idcb_conv_desc* d, const void* x, const void* dy, float* dw,
                     const float* pro_scale, const float* pro_shift, int pro_act, void* stream);
 
+/* ---- depthwise 3x3 convolution (direct, bandwidth-bound) ------------------------------------ */
+/* TF depthwise kernels behind DepthwiseConv2D in MobileNetV2 (dist_model_tf_mobile.py:119;
+ * SURVEY 2.E K7). Weights bf16 [3][3][C]; the descriptor has cin == cout == C.
+ *   fprop: y = dw(act(scale*x+shift)), stat_sum/sq += batch statistics of y
+ *   dgrad: dpre = dw^T(dy) * act'(scale*x+shift); stat_a += sum dpre, stat_b += sum dpre*x
+ *   wgrad: dw (fp32, accumulated) += sum_pos act(scale*x+shift) * dy                          */
+int idcb_dwconv_fprop(const idcb_conv_desc* d, const void* x, const void* w, void* y,
+                      const float* scale, const float* shift, int act, float* stat_sum,
+                      float* stat_sq, void* stream);
+int idcb_dwconv_dgrad(const idcb_conv_desc* d, const void* dy, const void* w, const void* x, void* dx,
+                      const float* scale, const float* shift, int act, float* stat_a, float* stat_b,
+                      void* stream);
+int idcb_dwconv_wgrad(const idcb_conv_desc* d, const void* x, const void* dy, float* dw,
+                      const float* scale, const float* shift, int act, void* stream);
+
+/* ---- BatchNorm bookkeeping (per-channel, tiny) ---------------------------------------------- */
+/* cuDNN BatchNormalizationForwardTraining / Backward as used by Keras BatchNormalization
+ * (dist_model_tf_dense.py:131, dist_model_tf_mobile.py:119). The heavy parts
+ * (normalise, activation, reductions) are fused into conv prologues/epilogues; these kernels only
+ * turn per-channel sums into scale/shift, moving statistics and backward coefficients.           */
+int idcb_bn_finalize(const float* sum, const float* sq, float count, const float* gamma,
+                     const float* beta, float eps, float* scale, float* shift, float* mean_out,
+                     float* rstd_out, float* moving_mean, float* moving_var, float momentum, int C,
+                     void* stream);
+/* inference-mode (frozen layer) fold of moving statistics into scale/shift */
+int idcb_bn_fold(const float* gamma, const float* beta, const float* mean, const float* var, float eps,
+                 float* scale, float* shift, int C, void* stream);
+int idcb_bn_bwd_coeffs(const float* sa, const float* sb, const float* mean, const float* rstd,
+                       const float* scale, float count, float* dgamma, float* dbeta, float* A,
+                       float* B, float* C0, float* acc_s1, float* acc_s2, int C, void* stream);
+int idcb_bn_shared_coeffs(const float* s1, const float* s2, const float* mean, const float* rstd,
+                          float count, float* A, float* B, float* C0, int C, void* stream);
+/* y = act(scale*x+shift) (+res)  — BN apply, residual Add of MobileNetV2 */
+int idcb_affine_act(const void* x, int x_pitch, int x_coff, void* y, int y_pitch, int y_coff,
+                    const float* scale, const float* shift, int act, const void* res, int r_pitch,
+                    int r_coff, long long M, int C, void* stream);
+/* out = A[c]*g + B[c]*x + C0[c]  — BN backward applied element-wise; g fp32 or bf16 */
+int idcb_affine2(const void* g, int g_is_float, int g_pitch, int g_coff, const void* x, int x_pitch,
+                 int x_coff, void* out, int o_pitch, int o_coff, const float* A, const float* B,
+                 const float* C0, long long M, int C, void* stream);
+int idcb_channel_stats(const void* x, int pitch, int coff, long long M, int C, float* sum, float* sq,
+                       void* stream);
+
+/* ---- pooling ---------------------------------------------------------------------------------- */
+/* cuDNN pooling behind MaxPooling2D / AveragePooling2D (VGG16 block pools
+ * dist_model_tf_vgg.py:119, DenseNet pool1 and transition pools dist_model_tf_dense.py:131,
+ * secure_fed_model.py:88). `pad` models Keras ZeroPadding2D in front of a VALID pool.            */
+typedef struct idcb_pool_desc {
+    int batch, h, w, c, ho, wo, k, stride, pad, is_max;
+    int x_pitch, x_coff, y_pitch, y_coff;
+} idcb_pool_desc;
+int idcb_pool_fwd(const idcb_pool_desc* d, const void* x, void* y, const float* scale,
+                  const float* shift, int act, void* stream);
+int idcb_pool_bwd(const idcb_pool_desc* d, const void* x, const void* y, const void* dy, int dy_pitch,
+                  int dy_coff, void* dx, int dx_pitch, int dx_coff, const float* scale,
+                  const float* shift, int act, int relu_mask, float* stat_a, float* stat_b,
+                  void* stream);
+
+/* ---- input packing / casts --------------------------------------------------------------------- */
+/* convert_image_dtype + channel padding to 8 (dist_model_tf_mobile.py:37-40 produces fp32 [0,1]) */
+int idcb_pack_input(const float* x, void* y, long long npos, int cin, int cpad, void* stream);
+int idcb_cast_f32_bf16(const float* x, void* y, long long n, void* stream);
+
+/* ---- head: GAP + Dense + loss + accuracy, forward and backward in one kernel ------------------- */
+/* dist_model_tf_mobile.py:123-132 (GlobalAveragePooling2D, Dense(1), BinaryCrossentropy(from_logits),
+ * metrics=['accuracy']); dist_model_tf_dense.py:135-144 (Dense(10), CategoricalCrossentropy).     */
+typedef struct idcb_head_desc {
+    int batch, hw, c, k;
+    int x_pitch, x_coff;
+    const float* pro_scale;   /* optional BN(+activation) applied before the pooling */
+    const float* pro_shift;
+    int pro_act;
+    int loss_kind;            /* 0 = BCE from logits, 1 = softmax cross-entropy (integer labels) */
+    int acc_on_prob;          /* 0 = threshold the raw logit (Keras quirk), 1 = threshold sigmoid */
+    float threshold;
+    int training;             /* 0 = forward only */
+    float grad_scale;         /* 1 / global batch */
+    int dx_pitch, dx_coff;
+    int g_pitch, g_coff;
+} idcb_head_desc;
+int idcb_head(const idcb_head_desc* d, const void* x, const float* w, const float* bias,
+              const float* labels, float* logits, float* acc, float* dw, float* db, void* dx,
+              float* gacc, float* stat_a, float* stat_b, void* stream);
+
+/* ---- optimizers (flat buffers) ------------------------------------------------------------------ */
+#define IDCB_OPT_RMSPROP 0
+#define IDCB_OPT_SGD 1
+#define IDCB_OPT_ADAM 2
+/* Keras RMSprop/SGD/Adam update (dist_model_tf_mobile.py:130, fed_model.py:126,208; SURVEY 2.B B7,
+ * 2.E K13) over one contiguous range: updates fp32 master, writes the bf16 shadow, optionally
+ * re-zeroes the gradient range. For Adam `lr` must already contain the bias correction.           */
+int idcb_optim_step(int kind, float* w, float* g, float* s1, float* s2, void* shadow, long long n,
+                    float lr, float p1, float p2, float eps, float grad_scale, int zero_grad,
+                    void* stream);
+
 #ifdef __cplusplus
 }
 #endif
