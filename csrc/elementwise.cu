@@ -214,6 +214,48 @@ __global__ void channel_stats_kernel(const __nv_bfloat16* __restrict__ x, int pi
     }
 }
 
+// sum_g[c] += sum_m g ; sum_gx[c] += sum_m g*x   (BN backward sums when dpre is already in memory)
+__global__ void channel_stats2_kernel(const __nv_bfloat16* __restrict__ g, int g_pitch, int g_coff,
+                                      const __nv_bfloat16* __restrict__ x, int x_pitch, int x_coff,
+                                      long long M, int C, float* sum_g, float* sum_gx) {
+    const int oct = threadIdx.x & 7;
+    const int rl = threadIdx.x >> 3;
+    const int c = blockIdx.x * 64 + oct * 8;
+    float s[8], q[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) s[e] = q[e] = 0.f;
+    if (c < C) {
+        for (long long m = blockIdx.y * 32 + rl; m < M; m += (long long)gridDim.y * 32) {
+            uint4 gv = *reinterpret_cast<const uint4*>(g + m * g_pitch + g_coff + c);
+            uint4 xv = *reinterpret_cast<const uint4*>(x + m * x_pitch + x_coff + c);
+            const uint32_t* gw = reinterpret_cast<const uint32_t*>(&gv);
+            const uint32_t* xw = reinterpret_cast<const uint32_t*>(&xv);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                float2 a = unpack_bf16x2(gw[e]);
+                float2 b = unpack_bf16x2(xw[e]);
+                s[2 * e] += a.x; q[2 * e] += a.x * b.x;
+                s[2 * e + 1] += a.y; q[2 * e + 1] += a.y * b.y;
+            }
+        }
+    }
+    __shared__ float sh[2][32][65];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        sh[0][rl][oct * 8 + e] = s[e];
+        sh[1][rl][oct * 8 + e] = q[e];
+    }
+    __syncthreads();
+    if (threadIdx.x < 128) {
+        const int which = threadIdx.x >> 6;
+        const int ch = threadIdx.x & 63;
+        float t = 0.f;
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) t += sh[which][r][ch];
+        if (blockIdx.x * 64 + ch < C) atomicAdd((which ? sum_gx : sum_g) + blockIdx.x * 64 + ch, t);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Pooling. One thread handles 8 channels of one output position.
 //   max: y = max over window of act(scale*x+shift) (prologue optional); window positions outside the
@@ -519,6 +561,23 @@ extern "C" int idcb_channel_stats(const void* x, int pitch, int coff, long long 
     if (splits < 1) splits = 1;
     dim3 grid(ceil_div(C, 64), splits);
     channel_stats_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((cbf)x, pitch, coff, M, C, sum, sq);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_channel_stats2(const void* g, int g_pitch, int g_coff, const void* x, int x_pitch,
+                                   int x_coff, long long M, int C, float* sum_g, float* sum_gx,
+                                   void* stream) {
+    IDCB_REQUIRE(C % 8 == 0 && g_pitch % 8 == 0 && g_coff % 8 == 0 && x_pitch % 8 == 0 && x_coff % 8 == 0,
+                 "channel_stats2: alignment");
+    if (M == 0) return 0;
+    int splits = static_cast<int>(ceil_div_ll(M, 32 * 16));
+    const int cap = ceil_div(4 * num_sms(), ceil_div(C, 64));
+    if (splits > cap) splits = cap;
+    if (splits < 1) splits = 1;
+    dim3 grid(ceil_div(C, 64), splits);
+    channel_stats2_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((cbf)g, g_pitch, g_coff, (cbf)x, x_pitch,
+                                                               x_coff, M, C, sum_g, sum_gx);
     IDCB_LAUNCH_CHECK();
     return 0;
 }

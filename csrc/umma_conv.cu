@@ -746,7 +746,6 @@ extern "C" int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const vo
                      "conv_dgrad: mode 2 needs bwd_scale/bwd_shift");
         IDCB_REQUIRE(f->gacc == nullptr || (f->g_pitch % 4 == 0 && f->g_coff % 4 == 0),
                      "conv_dgrad: G pitch/offset must be multiples of 4");
-        if (f->mode == 0) a.aux = nullptr;
     }
     IDCB_REQUIRE(a.y != nullptr || a.gacc != nullptr, "conv_dgrad: no output given");
     CUtensorMap tm;

@@ -63,7 +63,7 @@ typedef struct idcb_conv_fused {
 } idcb_conv_fused;
 
 /* Fused epilogue of dgrad.
- *   mode 0: dx = acc
+ *   mode 0: dx = acc (+ aux, an optional bf16 tensor added in: the residual branch of an Add layer)
  *   mode 1: dx = acc * (aux > 0)                 ReLU backward of the layer that produced aux (= x)
  *   mode 2: dpre = acc * act'(bwd_scale*aux + bwd_shift)    BN+activation backward, aux = raw x
  *           dx (bf16, optional) = dpre ; gacc (fp32, optional) += bwd_scale * dpre
@@ -136,6 +136,9 @@ int idcb_affine2(const void* g, int g_is_float, int g_pitch, int g_coff, const v
                  const float* C0, long long M, int C, void* stream);
 int idcb_channel_stats(const void* x, int pitch, int coff, long long M, int C, float* sum, float* sq,
                        void* stream);
+/* sum_g[c] += sum_p g, sum_gx[c] += sum_p g*x — BN backward sums for a dpre that is already in memory */
+int idcb_channel_stats2(const void* g, int g_pitch, int g_coff, const void* x, int x_pitch, int x_coff,
+                        long long M, int C, float* sum_g, float* sum_gx, void* stream);
 
 /* ---- pooling ---------------------------------------------------------------------------------- */
 /* cuDNN pooling behind MaxPooling2D / AveragePooling2D (VGG16 block pools
