@@ -1,0 +1,235 @@
+#!/usr/bin/env python
+"""Headline benchmark: IDC patches/sec, DenseNet-121 binary classifier, data-parallel bf16 training on
+synthetic 50x50x3 patches (BASELINE.json: "IDC patches/sec at 1/2/4/8 B200 (DenseNet-121)", config
+"DenseNet-121 binary IDC classifier, data-parallel bf16 on 8xB200, global batch 1024").
+
+    python bench.py --gpus N --steps K --warmup W          # N=1: plain python; N>1: launched by torchrun
+
+Weak scaling: 128 patches per GPU (global batch 1024 at N=8). Every layer trains (BatchNorm in batch-
+statistics mode), RMSprop, one full optimizer step per iteration, gradients summed over ranks.
+
+Timed regions
+* ``value`` / ``ms_per_step``: device time of K steps. Each step is bracketed by CUDA events on the
+  launching stream; between timed steps a 256 MiB buffer is written to flush the 126 MB L2 (outside the
+  events). The per-step times are summed, the MAX over ranks is reported.
+* ``e2e``: the same K steps through the public API (``model.train_on_batch``) including, every step, the
+  host->device copy of that step's batch from pinned memory and a device->host read of the step's loss;
+  wall-clock between two barriers + synchronize, max over ranks.
+
+``--impl reference`` is the reference arm: the upstream scripts need TensorFlow 2.1 / TFF / phe, none of
+which can be installed offline, so it prints ``{"impl": "reference", "unavailable": ...}`` and exits 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+
+def _reference_arm() -> int:
+    why = ("/root/reference is 5 TensorFlow-2.1 scripts with no setup.py/pyproject (pip: 'not installable'); "
+           "tensorflow, tensorflow_federated, tensorflow_datasets and phe are absent from the image and "
+           "/opt/wheelhouse, and there is no network")
+    try:
+        import tensorflow  # noqa: F401
+        why = "tensorflow imports, but the reference scripts still need tensorflow_federated / tfds / phe"
+    except Exception:
+        pass
+    print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+class ClockSampler:
+    """Samples SM clock / throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.sm_max = [], set(), None
+        self._stop = threading.Event()
+        self._th = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def start(self):
+        if self.nv is not None:
+            self._th = threading.Thread(target=self._run, daemon=True)
+            self._th.start()
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._th is not None:
+            self._th.join(timeout=1.0)
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="densenet121")
+    ap.add_argument("--batch-per-gpu", type=int, default=128)
+    ap.add_argument("--comm", default="auto", help="auto|fused|nccl")
+    ap.add_argument("--no-graph", action="store_true", help="launch kernels eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--no-l2-flush", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return _reference_arm()
+    if args.warmup < 3:
+        args.warmup = 3
+
+    import torch
+    import torch.distributed as dist
+
+    from idc_models_b200.models.applications import build_transfer_model
+    from idc_models_b200.ops import _lib
+    from idc_models_b200.optim.optimizers import RMSprop
+    from idc_models_b200.parallel.strategy import MirroredStrategy
+    from idc_models_b200.parallel.world import World
+    from idc_models_b200.train.losses import BinaryCrossentropy
+
+    world = World.from_env()
+    if world.size != args.gpus:
+        if world.size == 1 and args.gpus > 1:
+            print(f"bench.py: --gpus {args.gpus} needs `python -m torch.distributed.run --nproc-per-node "
+                  f"{args.gpus} bench.py ...`", file=sys.stderr)
+            return 2
+    if world.device.type != "cuda":
+        print("bench.py needs a CUDA device", file=sys.stderr)
+        return 2
+    dev = world.device
+    n = world.size
+    per = args.batch_per_gpu
+    gb = per * n
+    comm = args.comm
+    if comm == "auto":
+        comm = "nccl"
+    strategy = MirroredStrategy(world=world, comm=comm)
+    with strategy.scope():
+        model = build_transfer_model(args.model, (50, 50, 3), 1, device=dev, seed=0)
+        model.base.trainable = True          # full-model training, BatchNorm on batch statistics
+        model.compile(optimizer=RMSprop(lr=1e-4), loss=BinaryCrossentropy(from_logits=True),
+                      metrics=["accuracy"])
+    ex = model.executor
+    ex.use_graphs = not args.no_graph
+
+    # synthetic data: a ring of distinct global batches in pinned host memory
+    ring = 8
+    g = torch.Generator().manual_seed(1234)
+    hx = [torch.rand(gb, 50, 50, 3, generator=g).pin_memory() for _ in range(ring)]
+    hy = [(torch.rand(gb, generator=g) > 0.5).float().pin_memory() for _ in range(ring)]
+    sl = strategy.local_slice(gb)
+    dx = [t[sl].to(dev) for t in hx]
+    dy = [t[sl].to(dev) for t in hy]
+    flush = None if args.no_l2_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step_device(i):
+        ex.train_batch(dx[i % ring], dy[i % ring], gb)
+        strategy.reduce_and_apply(model.store, model.optimizer, 1.0)
+
+    # ---- warm-up (also captures the CUDA graph) ----
+    for i in range(args.warmup):
+        step_device(i)
+    torch.cuda.synchronize()
+    world.barrier()
+
+    # ---- device-timed region ----
+    sampler = ClockSampler(dev.index or 0)
+    sampler.start()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    _lib.reset_launches()
+    world.barrier()
+    torch.cuda.synchronize()
+    for i in range(args.steps):
+        if flush is not None:
+            flush.fill_(i & 0xFF)
+        starts[i].record()
+        step_device(i)
+        ends[i].record()
+    torch.cuda.synchronize()
+    world.barrier()
+    launches = _lib.launches()
+    dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
+    clocks = sampler.stop()
+    t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
+    if world.is_distributed:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms = float(t.item())
+
+    # ---- end-to-end region: public API + H2D of every batch + D2H of the loss ----
+    world.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    last_loss = 0.0
+    for i in range(args.steps):
+        out = model.train_on_batch(hx[i % ring], hy[i % ring])     # slices, copies H2D, runs the step
+        last_loss = float(out["stats"][0].item())                   # D2H read of the step's loss sum
+    torch.cuda.synchronize()
+    world.barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world.is_distributed:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+
+    if world.rank == 0:
+        ms_per_step = dev_ms / args.steps
+        value = gb * args.steps / (dev_ms / 1e3)
+        h2d = per * 50 * 50 * 3 * 4 + per * 4
+        out = {
+            "metric": "IDC patches/sec (DenseNet-121 training, fwd+bwd+RMSprop)",
+            "value": round(value, 1), "unit": "patches/s", "n_gpus": n, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "impl": "ours",
+            "config": {"model": args.model, "global_batch": gb, "per_gpu_batch": per,
+                       "image": "50x50x3", "seq_len": None, "parallelism": f"dp{n}", "comm": comm,
+                       "optimizer": "rmsprop", "trainable": "all layers", "cuda_graph": ex.use_graphs,
+                       "l2": "flushed between timed steps (256 MiB write)" if flush is not None else "not flushed",
+                       "timing": "per-step CUDA events, summed, max over ranks"},
+            "clocks": clocks,
+            "e2e": {"value": round(gb * args.steps / e2e_s, 1), "unit": "patches/s",
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                    "ms_per_step": round(e2e_s * 1e3 / args.steps, 4), "last_loss_sum": last_loss},
+            "gpu_launches": launches,
+        }
+        print(json.dumps(out))
+    world.barrier()
+    if world.is_distributed:
+        world.shutdown()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

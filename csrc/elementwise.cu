@@ -396,12 +396,49 @@ __global__ void pool_bwd_kernel(PoolBwdArgs p) {
                 if (p.is_max) {
                     uint4 yv = *reinterpret_cast<const uint4*>(p.y + op * p.y_pitch + p.y_coff + c);
                     const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
+                    float ymax[8], dd[8];
+                    bool hit[8];
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         float2 d = unpack_bf16x2(dw[e]);
                         float2 yy = unpack_bf16x2(yw[e]);
-                        if (a[2 * e] == yy.x) g[2 * e] += d.x;
-                        if (a[2 * e + 1] == yy.y) g[2 * e + 1] += d.y;
+                        ymax[2 * e] = yy.x; ymax[2 * e + 1] = yy.y;
+                        dd[2 * e] = d.x; dd[2 * e + 1] = d.y;
+                    }
+                    bool any_hit = false;
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        hit[e] = a[e] == ymax[e];
+                        any_hit |= hit[e];
+                    }
+                    if (any_hit) {
+                        // cuDNN / TF / PyTorch route the gradient to the FIRST maximum of the window
+                        // (row-major scan): drop the hit if an earlier window element ties.
+                        const int h0 = ho * p.stride - p.pad, w0 = wo * p.stride - p.pad;
+                        const int qme = (hi - h0) * p.k + (wi - w0);
+                        for (int q = 0; q < qme; ++q) {
+                            const int h2 = h0 + q / p.k, w2 = w0 + q % p.k;
+                            if (h2 < 0 || h2 >= p.H || w2 < 0 || w2 >= p.W) continue;
+                            uint4 ov = *reinterpret_cast<const uint4*>(
+                                p.x + (static_cast<long long>(b * p.H + h2) * p.W + w2) * p.x_pitch +
+                                p.x_coff + c);
+                            const uint32_t* ow2 = reinterpret_cast<const uint32_t*>(&ov);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                float2 f = unpack_bf16x2(ow2[e]);
+                                if (p.scale) {
+                                    f.x = __bfloat162float(__float2bfloat16_rn(apply_act(
+                                        fmaf(f.x, p.scale[c + 2 * e], p.shift[c + 2 * e]), p.act)));
+                                    f.y = __bfloat162float(__float2bfloat16_rn(apply_act(
+                                        fmaf(f.y, p.scale[c + 2 * e + 1], p.shift[c + 2 * e + 1]), p.act)));
+                                }
+                                if (f.x == ymax[2 * e]) hit[2 * e] = false;
+                                if (f.y == ymax[2 * e + 1]) hit[2 * e + 1] = false;
+                            }
+                        }
+#pragma unroll
+                        for (int e = 0; e < 8; ++e)
+                            if (hit[e]) g[e] += dd[e];
                     }
                 } else {
                     const float inv = 1.f / (p.k * p.k);

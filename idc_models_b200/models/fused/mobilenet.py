@@ -1,0 +1,299 @@
+"""Fused sm_100a pipeline for MobileNetV2 (alpha 1.0) + GAP + Dense head
+(/root/reference/dist_model_tf_mobile.py:119-129; FedAvg north-star config uses it too).
+
+Per inverted-residual block: expand 1x1 (tcgen05) -> depthwise 3x3 (direct kernel) -> project 1x1
+(tcgen05) -> one element-wise kernel that applies the project BatchNorm and the residual Add. Every
+other BatchNorm + ReLU6 is a per-channel scale/shift applied by the CONSUMING kernel while it loads its
+operand, and each producer accumulates the batch statistics of what it stores, so the activations of
+the 52 BatchNorm / 35 ReLU6 layers never make a round trip through memory. Keras ``correct_pad``
+asymmetric padding of the stride-2 depthwise convs and of ``Conv1`` is expressed as (pad_t, pad_l).
+"""
+from __future__ import annotations
+
+import torch
+
+from ...ops import conv as OC
+from ...ops import kernels as K
+from ..spec import MBV2_CFG, correct_pad
+from .common import ACT_NONE, ACT_RELU6, BNState, FusedExecutor, Scratch
+
+
+class _Plan:
+    pass
+
+
+class _Blk:
+    pass
+
+
+class _Stat:
+    """sum / sum-of-squares slots in the per-step scratch for one produced tensor"""
+
+    def __init__(self, sc: Scratch, c: int):
+        self.sc, self.c = sc, c
+        self.o_sum, self.o_sq = sc.reserve(c), sc.reserve(c)
+
+    @property
+    def sum(self):
+        return self.sc.view(self.o_sum, self.c)
+
+    @property
+    def sq(self):
+        return self.sc.view(self.o_sq, self.c)
+
+
+class MobileNetV2Executor(FusedExecutor):
+    def build_plan(self, batch: int):
+        net = self.net
+        dev = net.device
+        bf = torch.bfloat16
+        ft = self.first_trainable
+        p = _Plan()
+        H, W, C = net.input_shape
+        p.x32 = torch.zeros(batch, H, W, C, dtype=torch.float32, device=dev)
+        p.labels = torch.zeros(batch, dtype=torch.float32, device=dev)
+        p.acc = torch.zeros(4, dtype=torch.float32, device=dev)
+        p.logits = torch.zeros(batch, net.n_outputs, dtype=torch.float32, device=dev)
+        p.x16 = torch.zeros(batch, H, W, 8, dtype=bf, device=dev)
+        sc = Scratch(dev)
+        p.scratch = sc
+
+        def idx(n):
+            return net.get_layer(n).index
+
+        def z(h, w, c, dtype=bf):
+            return torch.zeros(batch, h, w, c, dtype=dtype, device=dev)
+
+        def coef(c):
+            return tuple(torch.zeros(c, device=dev) for _ in range(3))
+
+        # stem: Conv1_pad + Conv1 3x3/2 VALID
+        p.g_stem = OC.geom(H, W, 8, 32, 3, 2, (correct_pad(H), correct_pad(W)))
+        h, w = p.g_stem.ho, p.g_stem.wo
+        p.s_raw = z(h, w, 32)
+        p.st_stem = _Stat(sc, 32)
+        p.i_stem, p.i_stem_bn = idx("Conv1"), idx("bn_Conv1")
+        p.bn_stem = BNState(self, "bn_Conv1", 32, sc, ft <= p.i_stem_bn)
+        if ft <= p.i_stem_bn:
+            p.dpre_stem = z(h, w, 32)
+            p.ds_raw = z(h, w, 32)
+            p.c_stem = coef(32)
+        p.blocks = []
+        cin = 32
+        block_id = 0
+        for t, c, n, s in MBV2_CFG:
+            for i in range(n):
+                stride = s if i == 0 else 1
+                b = _Blk()
+                b.prefix = "expanded_conv_" if block_id == 0 else f"block_{block_id}_"
+                b.has_expand = block_id != 0
+                b.stride, b.cin, b.cout, b.cexp = stride, cin, c, (t * cin if block_id != 0 else cin)
+                b.add = cin == c and stride == 1
+                b.h, b.w = h, w
+                if b.has_expand:
+                    b.i_e, b.i_ebn = idx(b.prefix + "expand"), idx(b.prefix + "expand_BN")
+                    b.ge = OC.geom(h, w, cin, b.cexp, 1)
+                    b.e_raw = z(h, w, b.cexp)
+                    b.st_e = _Stat(sc, b.cexp)
+                    b.bn_e = BNState(self, b.prefix + "expand_BN", b.cexp, sc, ft <= b.i_ebn)
+                b.i_d, b.i_dbn = idx(b.prefix + "depthwise"), idx(b.prefix + "depthwise_BN")
+                pad = "same" if stride == 1 else (correct_pad(h), correct_pad(w))
+                b.gd = OC.geom(h, w, b.cexp, b.cexp, 3, stride, pad)
+                ho, wo = b.gd.ho, b.gd.wo
+                b.d_raw = z(ho, wo, b.cexp)
+                b.st_d = _Stat(sc, b.cexp)
+                b.bn_d = BNState(self, b.prefix + "depthwise_BN", b.cexp, sc, ft <= b.i_dbn)
+                b.i_p, b.i_pbn = idx(b.prefix + "project"), idx(b.prefix + "project_BN")
+                b.gp = OC.geom(ho, wo, b.cexp, c, 1)
+                b.p_raw = z(ho, wo, c)
+                b.st_p = _Stat(sc, c)
+                b.bn_p = BNState(self, b.prefix + "project_BN", c, sc, ft <= b.i_pbn)
+                b.out = z(ho, wo, c)
+                b.ho, b.wo = ho, wo
+                # backward buffers
+                b.bwd = ft <= b.i_pbn
+                if b.bwd:
+                    b.dout = z(ho, wo, c)            # dL/d(out), written by the consumer
+                    b.dp_raw = z(ho, wo, c)
+                    b.c_p = coef(c)
+                    if ft <= b.i_dbn:
+                        b.dpre_d = z(ho, wo, b.cexp)
+                        b.dd_raw = z(ho, wo, b.cexp)
+                        b.c_d = coef(b.cexp)
+                    if b.has_expand and ft <= b.i_ebn:
+                        b.dpre_e = z(h, w, b.cexp)
+                        b.de_raw = z(h, w, b.cexp)
+                        b.c_e = coef(b.cexp)
+                p.blocks.append(b)
+                cin, h, w = c, ho, wo
+                block_id += 1
+        # Conv_1 1x1 -> 1280
+        p.i_c, p.i_cbn = idx("Conv_1"), idx("Conv_1_bn")
+        p.gc = OC.geom(h, w, cin, 1280, 1)
+        p.c_raw = z(h, w, 1280)
+        p.st_c = _Stat(sc, 1280)
+        p.bn_c = BNState(self, "Conv_1_bn", 1280, sc, ft <= p.i_cbn)
+        p.hw = h * w
+        if ft <= p.i_cbn:
+            p.dpre_c = z(h, w, 1280)
+            p.dc_raw = z(h, w, 1280)
+            p.c_c = coef(1280)
+        p.head_layer = net.layers[-1]
+        sc.finalize()
+        return p
+
+    # -------------------------------------------------------------------------------------------------
+    def _bn(self, bn: BNState, training: bool, st: _Stat, count: float) -> None:
+        if training and bn.trainable:
+            bn.finalize(st.sum, st.sq, count)
+        else:
+            bn.fold()
+
+    @staticmethod
+    def _cnt(t: torch.Tensor) -> float:
+        return float(t.numel() // t.shape[-1])
+
+    def run(self, p, training: bool, grad_scale: float) -> None:
+        net = self.net
+        p.scratch.zero()
+        p.acc.zero_()
+        tr = training
+
+        def ss(st):
+            return (st.sum, st.sq) if tr else (None, None)
+
+        K.pack_input(p.x32, p.x16)
+        a, q = ss(p.st_stem)
+        OC.conv_fprop_raw(p.g_stem, p.x16, self.w16("Conv1/kernel"), p.s_raw, stat_sum=a, stat_sq=q)
+        self._bn(p.bn_stem, tr, p.st_stem, self._cnt(p.s_raw))
+        cur = None      # materialised block input; None -> lazy stem output
+        for b in p.blocks:
+            if b.has_expand:
+                a, q = ss(b.st_e)
+                OC.conv_fprop_raw(b.ge, cur, self.w16(b.prefix + "expand/kernel"), b.e_raw, stat_sum=a, stat_sq=q)
+                self._bn(b.bn_e, tr, b.st_e, self._cnt(b.e_raw))
+                dw_in, dw_bn = b.e_raw, b.bn_e
+            else:
+                dw_in, dw_bn = p.s_raw, p.bn_stem
+            a, q = ss(b.st_d)
+            K.dwconv_fprop(b.gd, dw_in, self.w16(b.prefix + "depthwise/depthwise_kernel"), b.d_raw,
+                           scale=dw_bn.scale, shift=dw_bn.shift, act=ACT_RELU6, stat_sum=a, stat_sq=q)
+            self._bn(b.bn_d, tr, b.st_d, self._cnt(b.d_raw))
+            a, q = ss(b.st_p)
+            OC.conv_fprop_raw(b.gp, b.d_raw, self.w16(b.prefix + "project/kernel"), b.p_raw,
+                              pro_scale=b.bn_d.scale, pro_shift=b.bn_d.shift, pro_act=ACT_RELU6,
+                              stat_sum=a, stat_sq=q)
+            self._bn(b.bn_p, tr, b.st_p, self._cnt(b.p_raw))
+            K.affine_act(b.p_raw, b.out, b.cout, b.bn_p.scale, b.bn_p.shift, ACT_NONE,
+                         res=cur if b.add else None)
+            cur = b.out
+        a, q = ss(p.st_c)
+        OC.conv_fprop_raw(p.gc, cur, self.w16("Conv_1/kernel"), p.c_raw, stat_sum=a, stat_sq=q)
+        self._bn(p.bn_c, tr, p.st_c, self._cnt(p.c_raw))
+        hl = p.head_layer
+        wname, bname = hl.spec.params[0].name, hl.spec.params[1].name
+        head_train = tr and hl.index in self.trainable
+        bwd = tr and self.first_trainable <= p.i_cbn
+        K.head(p.c_raw, p.hw, 1280, net.n_outputs, self.w32(wname), self.w32(bname), p.labels, p.logits,
+               p.acc, pro_scale=p.bn_c.scale, pro_shift=p.bn_c.shift, pro_act=ACT_RELU6,
+               loss_kind=self.loss_kinds[net.loss.kind], acc_on_prob=net.acc_on_prob,
+               threshold=net.acc_threshold, training=tr, grad_scale=grad_scale,
+               dw=self.gw(wname) if head_train else None, db=self.gw(bname) if head_train else None,
+               dx=p.dpre_c if bwd else None, stat_a=p.bn_c.sa if bwd else None,
+               stat_b=p.bn_c.sb if bwd else None)
+        if bwd:
+            self._backward(p)
+
+    # -------------------------------------------------------------------------------------------------
+    def _bn_bwd(self, bn: BNState, count: float, coefs, need_dx: bool) -> None:
+        """sa/sb of ``bn`` are filled: emit parameter gradients and (optionally) the dx coefficients."""
+        A, B, C0 = coefs
+        if bn.trainable:
+            if need_dx:
+                K.bn_bwd_coeffs(bn.sa, bn.sb, bn.mean, bn.rstd, bn.scale, count, dgamma=bn.dgamma,
+                                dbeta=bn.dbeta, A=A, B=B, C0=C0)
+            else:
+                K.bn_bwd_coeffs(bn.sa, bn.sb, bn.mean, bn.rstd, bn.scale, count, dgamma=bn.dgamma,
+                                dbeta=bn.dbeta)
+        elif need_dx:
+            A.copy_(bn.scale); B.zero_(); C0.zero_()
+
+    def _backward(self, p) -> None:
+        ft, tr = self.first_trainable, self.trainable
+        # ---- Conv_1 -------------------------------------------------------------------------------------
+        last = p.blocks[-1]
+        need = ft <= p.i_c
+        self._bn_bwd(p.bn_c, self._cnt(p.c_raw), p.c_c, need)
+        if not need:
+            return
+        K.affine2(p.dpre_c, p.c_raw, p.dc_raw, 1280, *p.c_c)
+        if p.i_c in tr:
+            OC.conv_wgrad_raw(p.gc, last.out, p.dc_raw, self.gw("Conv_1/kernel"))
+        if not last.bwd:
+            return
+        OC.conv_dgrad_raw(p.gc, p.dc_raw, self.w16("Conv_1/kernel"), last.dout, mode=0)
+        # ---- blocks -------------------------------------------------------------------------------------
+        for bi in range(len(p.blocks) - 1, -1, -1):
+            b = p.blocks[bi]
+            if not b.bwd:
+                return
+            prev = p.blocks[bi - 1] if bi > 0 else None
+            xin = prev.out if prev is not None else None
+            # project BN (no activation): dpre = dout
+            K.channel_stats2(b.dout, b.p_raw, b.cout, b.bn_p.sa, b.bn_p.sb)
+            need = ft <= b.i_p
+            self._bn_bwd(b.bn_p, self._cnt(b.p_raw), b.c_p, need)
+            if not need:
+                # a residual branch may still carry gradient further down
+                if b.add and prev is not None and prev.bwd:
+                    prev.dout.copy_(b.dout)
+                    continue
+                return
+            K.affine2(b.dout, b.p_raw, b.dp_raw, b.cout, *b.c_p)
+            if b.i_p in tr:
+                OC.conv_wgrad_raw(b.gp, b.d_raw, b.dp_raw, self.gw(b.prefix + "project/kernel"),
+                                  pro_scale=b.bn_d.scale, pro_shift=b.bn_d.shift, pro_act=ACT_RELU6)
+            stop = ft > b.i_dbn
+            if not stop:
+                OC.conv_dgrad_raw(b.gp, b.dp_raw, self.w16(b.prefix + "project/kernel"), b.dpre_d, mode=2,
+                                  aux=b.d_raw, bwd_scale=b.bn_d.scale, bwd_shift=b.bn_d.shift,
+                                  bwd_act=ACT_RELU6, stat_a=b.bn_d.sa, stat_b=b.bn_d.sb)
+                need = ft <= b.i_d
+                self._bn_bwd(b.bn_d, self._cnt(b.d_raw), b.c_d, need)
+                stop = not need
+            if not stop:
+                K.affine2(b.dpre_d, b.d_raw, b.dd_raw, b.cexp, *b.c_d)
+                dw_in, dw_bn = (b.e_raw, b.bn_e) if b.has_expand else (p.s_raw, p.bn_stem)
+                if b.i_d in tr:
+                    K.dwconv_wgrad(b.gd, dw_in, b.dd_raw, self.gw(b.prefix + "depthwise/depthwise_kernel"),
+                                   scale=dw_bn.scale, shift=dw_bn.shift, act=ACT_RELU6)
+                below = ft <= (b.i_ebn if b.has_expand else p.i_stem_bn)
+                if below:
+                    dpre = b.dpre_e if b.has_expand else p.dpre_stem
+                    K.dwconv_dgrad(b.gd, b.dd_raw, self.w16(b.prefix + "depthwise/depthwise_kernel"), dw_in,
+                                   dpre, scale=dw_bn.scale, shift=dw_bn.shift, act=ACT_RELU6,
+                                   stat_a=dw_bn.sa, stat_b=dw_bn.sb)
+                    if b.has_expand:
+                        need = ft <= b.i_e
+                        self._bn_bwd(b.bn_e, self._cnt(b.e_raw), b.c_e, need)
+                        if need:
+                            K.affine2(b.dpre_e, b.e_raw, b.de_raw, b.cexp, *b.c_e)
+                            if b.i_e in tr:
+                                OC.conv_wgrad_raw(b.ge, xin, b.de_raw, self.gw(b.prefix + "expand/kernel"))
+                            if prev is not None and prev.bwd:
+                                OC.conv_dgrad_raw(b.ge, b.de_raw, self.w16(b.prefix + "expand/kernel"),
+                                                  prev.dout, mode=0, aux=b.dout if b.add else None)
+                                continue
+                    else:
+                        # first block: the depthwise conv reads the stem directly
+                        need = ft <= p.i_stem
+                        self._bn_bwd(p.bn_stem, self._cnt(p.s_raw), p.c_stem, need)
+                        if need:
+                            K.affine2(p.dpre_stem, p.s_raw, p.ds_raw, 32, *p.c_stem)
+                            OC.conv_wgrad_raw(p.g_stem, p.x16, p.ds_raw, self.gw("Conv1/kernel"))
+                        return
+            # the main branch stopped inside this block; only a residual can carry gradient on
+            if b.add and prev is not None and prev.bwd:
+                prev.dout.copy_(b.dout)
+                continue
+            return

@@ -213,9 +213,9 @@ class Network:
             kind = self._executor_kind
             if kind == "auto":
                 kind = "fused" if self.device.type == "cuda" else "reference"
-            if kind == "reference":
+            if kind in ("reference", "reference_bf16"):
                 from .reference import RefExecutor
-                self._executor = RefExecutor(self)
+                self._executor = RefExecutor(self, emulate_bf16=(kind == "reference_bf16"))
             elif kind == "fused":
                 from .fused import make_fused_executor
                 self._executor = make_fused_executor(self)

@@ -13,10 +13,15 @@ import torch.nn.functional as F
 
 
 class RefExecutor:
-    def __init__(self, net):
+    def __init__(self, net, emulate_bf16: bool = False):
         self.net = net
         self._leaves: dict[str, torch.Tensor] = {}
         self._leaf_dev = None
+        # Oracle mode for the fused bf16 pipelines: every layer output is rounded to bf16 (straight-
+        # through for autograd), which is where the fused kernels round when they store activations.
+        # All arithmetic stays fp32. Without it, discontinuous ops (max-pool argmax, ReLU masks, tiny-
+        # batch BatchNorm) amplify the harmless storage rounding into large apparent differences.
+        self.emulate_bf16 = emulate_bf16
 
     # parameters as autograd leaves whose .grad aliases the flat gradient buffer
     def _leaf(self, name: str, requires_grad: bool) -> torch.Tensor:
@@ -125,6 +130,8 @@ class RefExecutor:
                     out = torch.relu(out)
             else:  # pragma: no cover
                 raise NotImplementedError(k)
+            if self.emulate_bf16 and k in ("input", "conv", "dwconv", "bn", "act", "maxpool", "avgpool", "add"):
+                out = out + (out.to(torch.bfloat16).to(out.dtype) - out).detach()
             vals[sp.name] = out
             if upto is not None and sp.name == upto:
                 break

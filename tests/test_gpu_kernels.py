@@ -227,7 +227,7 @@ def test_optimizer_kernels_match_closed_form(kind):
             st.grad.copy_(torch.randn(n, generator=g).to(dev))
             opt.apply(grad_scale=0.5, zero_grad=True)
         res[dev] = st
-    close(res["cuda"].master, res["cpu"].master, 1e-5, kind)
+    close(res["cuda"].master.cpu(), res["cpu"].master, 1e-5, kind)
     assert torch.equal(res["cuda"].master[1024:2048].cpu(), w0[1024:2048])
     assert res["cuda"].grad[:1024].abs().max().item() == 0.0
     close(res["cuda"].shadow[:1024], res["cuda"].master[:1024], 1e-2)

@@ -12,7 +12,7 @@ def _pair(arch, input_shape=(50, 50, 3), units=1, fine_tune_at=0, seed=0):
     from idc_models_b200.models.applications import build_transfer_model
     from idc_models_b200.optim.optimizers import SGD
     nets = []
-    for ex in ("fused", "reference"):
+    for ex in ("fused", "reference_bf16"):
         net = build_transfer_model(arch, input_shape, units, device="cuda", seed=seed, executor=ex)
         net.base.trainable = True
         for l in net.base.layers[:fine_tune_at]:
@@ -39,7 +39,7 @@ def _pair(arch, input_shape=(50, 50, 3), units=1, fine_tune_at=0, seed=0):
     return f, r
 
 
-def _compare(f, r, batch=8, units=1, tol_logit=0.08, min_cos=0.97):
+def _compare(f, r, batch=32, units=1, tol_logit=0.08, min_cos=0.97):
     torch.manual_seed(3)
     h, w, c = f.input_shape
     x = torch.rand(batch, h, w, c, device="cuda")
@@ -109,8 +109,8 @@ def test_densenet201_cifar_shape_10_classes():
 
 def test_fused_eval_matches_reference():
     f, r = _pair("densenet121")
-    x = torch.rand(8, 50, 50, 3, device="cuda").to(torch.bfloat16).float()
-    y = (torch.rand(8, device="cuda") > 0.5).float()
+    x = torch.rand(32, 50, 50, 3, device="cuda").to(torch.bfloat16).float()
+    y = (torch.rand(32, device="cuda") > 0.5).float()
     sf, lf = f.executor.eval_batch(x, y)
     sr, lr = r.executor.eval_batch(x, y)
     assert (lf - lr).abs().max().item() < 0.08 * max(1.0, lr.abs().max().item())
@@ -129,3 +129,21 @@ def test_training_reduces_loss_densenet():
     h = net.fit([(x, y)] * 4, epochs=3, verbose=0)
     print(h.history)
     assert h.history["loss"][-1] < h.history["loss"][0]
+
+
+def test_mobilenet_v2_full_backward():
+    f, r = _pair("mobilenet_v2")
+    _compare(f, r)
+
+
+def test_mobilenet_v2_fine_tune_at_100():
+    f, r = _pair("mobilenet_v2", fine_tune_at=100)
+    assert sum(t.numel() for t in f.trainable_weights) == 1863873
+    _compare(f, r)
+
+
+def test_head_only_phase1_all_archs():
+    """phase 1 of the transfer scripts: frozen base, only the Dense head trains"""
+    for arch in ("vgg16", "densenet121", "mobilenet_v2"):
+        f, r = _pair(arch, fine_tune_at=10 ** 6)
+        _compare(f, r)
