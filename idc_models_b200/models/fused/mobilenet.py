@@ -81,7 +81,8 @@ class MobileNetV2Executor(FusedExecutor):
         p.blocks = []
         cin = 32
         block_id = 0
-        for t, c, n, s in MBV2_CFG:
+        from ..spec import MBV2_CFGS
+        for t, c, n, s in MBV2_CFGS[net.base.name]:
             for i in range(n):
                 stride = s if i == 0 else 1
                 b = _Blk()

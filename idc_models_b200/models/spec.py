@@ -167,7 +167,10 @@ class _Builder:
 # DenseNet (keras.applications.densenet) — dist_model_tf_dense.py:131
 # ---------------------------------------------------------------------------------------------
 DENSENET_BLOCKS = {"densenet121": (6, 12, 24, 16), "densenet169": (6, 12, 32, 32),
-                   "densenet201": (6, 12, 48, 32)}
+                   "densenet201": (6, 12, 48, 32),
+                   # not a Keras application: a shallow variant used by the numerics tests, where the
+                   # fused bf16 pipeline can be compared tightly against the fp32 oracle
+                   "densenet_tiny": (2, 2, 2, 2)}
 DENSENET_EPS = 1.001e-5
 GROWTH = 32
 
@@ -221,8 +224,14 @@ def correct_pad(size: int, k: int = 3) -> tuple[int, int]:
     return c - adjust, c
 
 
-def mobilenet_v2(input_shape=(50, 50, 3)) -> ModelSpec:
-    b = _Builder("mobilenetv2_1.00_224", input_shape)
+MBV2_CFGS = {"mobilenetv2_1.00_224": MBV2_CFG,
+             # shallow test variant (see densenet_tiny)
+             "mobilenetv2_tiny": [(1, 16, 1, 1), (6, 24, 2, 2), (6, 32, 2, 2)]}
+
+
+def mobilenet_v2(input_shape=(50, 50, 3), name: str = "mobilenetv2_1.00_224") -> ModelSpec:
+    b = _Builder(name, input_shape)
+    MBV2_CFG = MBV2_CFGS[name]  # noqa: N806 - shadows the module constant on purpose
     h, w, _ = input_shape
     b.zeropad("Conv1_pad", (correct_pad(h), correct_pad(w)))
     b.conv("Conv1", 32, 3, 2, "valid")
@@ -290,6 +299,8 @@ ARCHS = {
     "densenet169": lambda shape=(50, 50, 3): densenet("densenet169", shape),
     "densenet201": lambda shape=(50, 50, 3): densenet("densenet201", shape),
     "mobilenet_v2": lambda shape=(50, 50, 3): mobilenet_v2(shape),
+    "densenet_tiny": lambda shape=(50, 50, 3): densenet("densenet_tiny", shape),
+    "mobilenet_v2_tiny": lambda shape=(50, 50, 3): mobilenet_v2(shape, "mobilenetv2_tiny"),
     "vgg16": lambda shape=(50, 50, 3): vgg16(shape),
     "small_cnn": lambda shape=(10, 10, 3): small_cnn(shape),
 }
