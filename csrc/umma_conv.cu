@@ -10,9 +10,10 @@
 //                (zero padding, channel-prefix views of a DenseNet concat buffer, and the fused
 //                BatchNorm scale/shift + ReLU/ReLU6 prologue happen here, in registers), write the
 //                128-byte-swizzled operand tile into shared memory, fence it to the async proxy and
-//                arrive on the stage's "full" mbarrier. After the main loop the same four warps are
-//                the epilogue: tcgen05.ld the fp32 accumulators out of TMEM, apply the fused epilogue
-//                and store.
+//                arrive on the stage's "full" mbarrier. The loads of k-block i+1 are issued before
+//                k-block i is transformed and stored, so two k-blocks of global traffic are in flight
+//                per CTA. After the main loop the same four warps are the epilogue: tcgen05.ld the fp32
+//                accumulators out of TMEM, apply the fused epilogue and store.
 //   warp 4     : TMA producer for the second operand (weights, or dy for wgrad).
 //   warp 5     : allocates TMEM, then one lane issues tcgen05.mma (UMMA 128 x N x 16, bf16 -> fp32)
 //                and tcgen05.commit to recycle the stage / publish the accumulator.
@@ -20,6 +21,10 @@
 // The activation tile layout [rows = positions][64 channels = 128 B], SWIZZLE_128B, is read as a
 // K-major operand by fprop/dgrad (K = channels) and as an MN-major operand by wgrad (K = positions),
 // so no transposed copies of activations, gradients or weights ever exist in memory.
+//
+// The GEMM K axis of fprop and the M axis of wgrad are the LINEARISED (tap, channel) index, so a conv
+// with few input channels (the RGB stems, Cin padded to 8) packs several filter taps into one 64-wide
+// k-block instead of wasting 7/8 of every MMA.
 //
 // Replaces the cuDNN convolution calls TensorFlow makes for the reference's Keras models
 // (/root/reference/dist_model_tf_vgg.py:119, dist_model_tf_dense.py:131,
@@ -31,7 +36,7 @@ namespace idcb {
 
 constexpr int kBM = 128;      // UMMA M (rows of the accumulator = TMEM lanes)
 constexpr int kBK = 64;       // K elements per pipeline stage (one 128-byte swizzle row)
-constexpr int kStages = 4;
+constexpr int kMaxStages = 4;
 constexpr int kThreads = 192;
 constexpr int kATileBytes = kBM * 128;  // 16 KiB
 
@@ -44,12 +49,12 @@ struct ConvArgs {
     int M;     // B * Ho * Wo
     int Cout;  // N extent
     int flip;  // dgrad: tap index into the weight tensor is mirrored
+    int stages;
     // prologue on A: a = act(scale[c] * x + shift[c]) (null scale => identity)
     const float* pro_scale;
     const float* pro_shift;
     int pro_act;
-    // epilogue
-    int epi_mode;  // 0: y = act(acc*es+eh) (+res); 1: y = acc * (aux > 0); 2: BN/act backward
+    // epilogue (mode is a template parameter)
     const float* epi_scale;
     const float* epi_shift;
     int epi_act;
@@ -64,14 +69,10 @@ struct ConvArgs {
     int g_pitch, g_coff;
     float* stat_a;  // per-N column sums: mode 0/1: sum(y); mode 2: sum(dpre)
     float* stat_b;  //                    mode 0: sum(y^2);  mode 2: sum(dpre * x_raw)
-    // second-operand TMA addressing
-    int w_cols_per_tap;  // column stride between taps in the 2-D weight view
+    int w_cols_per_tap;  // dgrad: column stride between taps in the 2-D weight view
 };
 
-// ---------------------------------------------------------------------------------------------
-// Butterfly transpose-reduce: on return v[0] of lane l holds the sum over the warp of column l.
-// 31 shuffles instead of 160.
-// ---------------------------------------------------------------------------------------------
+// Butterfly transpose-reduce: on return lane l holds the sum over the warp of column l.
 __device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
 #pragma unroll
     for (int n = 16; n >= 1; n >>= 1) {
@@ -86,6 +87,17 @@ __device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
     return v[0];
 }
 
+__device__ __forceinline__ void transform8(uint4& q, const float* sc, const float* sh, int act) {
+    uint32_t* w = reinterpret_cast<uint32_t*>(&q);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        float2 f = unpack_bf16x2(w[e]);
+        f.x = apply_act(fmaf(f.x, sc[2 * e], sh[2 * e]), act);
+        f.y = apply_act(fmaf(f.y, sc[2 * e + 1], sh[2 * e + 1]), act);
+        w[e] = pack_bf16x2(f.x, f.y);
+    }
+}
+
 template <int kBN, bool kBMN>
 struct FwdSmem {
     static constexpr int kBTileBytes = kBMN ? ((kBN + 63) / 64) * 8192 : kBN * 128;
@@ -95,19 +107,19 @@ struct FwdSmem {
 // =============================================================================================
 // fprop / dgrad kernel
 // =============================================================================================
-template <int kBN, bool kBMN>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int kBN, bool kBMN, int kEpi>
+__global__ void __launch_bounds__(kThreads, 2)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ ConvArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     using L = FwdSmem<kBN, kBMN>;
-    // carve
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
+    const int nstages = p.stages;
     uint8_t* a_tiles = smem;
-    uint8_t* b_tiles = smem + kStages * kATileBytes;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + kStages * L::kBTileBytes);
-    uint64_t* empty_bar = full_bar + kStages;
-    uint64_t* acc_bar = empty_bar + kStages;
+    uint8_t* b_tiles = smem + nstages * kATileBytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + nstages * L::kBTileBytes);
+    uint64_t* empty_bar = full_bar + kMaxStages;
+    uint64_t* acc_bar = empty_bar + kMaxStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
     float* s_scale = reinterpret_cast<float*>(tmem_slot + 4);
     float* s_shift = s_scale + p.Cin;
@@ -116,12 +128,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     const int lane = threadIdx.x & 31;
     const int m0 = blockIdx.x * kBM;
     const int n0 = blockIdx.y * kBN;
-    const int cblocks = (p.Cin + kBK - 1) / kBK;
-    const int num_kb = p.KH * p.KW * cblocks;
+    const int taps = p.KH * p.KW;
+    const int cblocks = (p.Cin + kBK - 1) / kBK;                 // dgrad: k-blocks per tap
+    const int ktot = taps * p.Cin;                              // fprop: linearised K extent
+    const int num_kb = kBMN ? taps * cblocks : (ktot + kBK - 1) / kBK;
     const bool has_pro = p.pro_scale != nullptr;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; ++s) {
+        for (int s = 0; s < nstages; ++s) {
             mbar_init(&full_bar[s], 4 + 1);  // 4 producer warps + the TMA thread
             mbar_init(&empty_bar[s], 1);     // one tcgen05.commit
         }
@@ -142,7 +156,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
 
     if (warp < 4) {
         // ===================== A producers =====================
-        const int j = threadIdx.x & 7;    // 16-byte chunk inside the 128-byte row
+        const int j = threadIdx.x & 7;       // 16-byte chunk inside the 128-byte row
         const int rbase = threadIdx.x >> 3;  // 0..15
         int hb[8], wb[8], ib[8];
 #pragma unroll
@@ -163,30 +177,49 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                 ib[i] = 0;
             }
         }
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int kb = 0; kb < num_kb; ++kb) {
-            const int tap = kb / cblocks;
-            const int cb = kb - tap * cblocks;
+        // issue the 8 row loads of k-block kb; returns the channel (or -1) and a validity mask
+        auto issue = [&](int kb, uint4 (&v)[8], uint32_t& okmask) -> int {
+            int tap, c;
+            if (kBMN) {
+                tap = kb / cblocks;
+                c = (kb - tap * cblocks) * kBK + j * 8;
+                if (c >= p.Cin) c = -1;
+            } else {
+                const int kidx = kb * kBK + j * 8;
+                if (kidx < ktot) {
+                    tap = kidx / p.Cin;
+                    c = kidx - tap * p.Cin;
+                } else {
+                    tap = 0;
+                    c = -1;
+                }
+            }
             const int kh = tap / p.KW;
             const int kw = tap - kh * p.KW;
-            const int c = cb * kBK + j * 8;
-            const bool cvalid = c < p.Cin;
-            uint4 v[8];
-            bool ok[8];
+            okmask = 0;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int hi = hb[i] + kh;
                 const int wi = wb[i] + kw;
-                ok[i] = cvalid && hi >= 0 && hi < p.H && wi >= 0 && wi < p.W;
+                const bool ok = c >= 0 && hi >= 0 && hi < p.H && wi >= 0 && wi < p.W;
                 v[i] = make_uint4(0u, 0u, 0u, 0u);
-                if (ok[i]) {
+                if (ok) {
+                    okmask |= 1u << i;
                     const size_t off =
                         (static_cast<size_t>(ib[i] + hi * p.W + wi)) * p.x_pitch + p.x_coff + c;
                     v[i] = __ldg(reinterpret_cast<const uint4*>(p.x + off));
                 }
             }
-            if (has_pro && cvalid) {
+            return c;
+        };
+        int stage = 0;
+        uint32_t phase = 0;
+        uint4 v[8], vn[8];
+        uint32_t ok = 0, okn = 0;
+        int c = issue(0, v, ok), cn = -1;
+        for (int kb = 0; kb < num_kb; ++kb) {
+            if (kb + 1 < num_kb) cn = issue(kb + 1, vn, okn);
+            if (has_pro && c >= 0) {
                 float sc[8], sh[8];
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
@@ -194,18 +227,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                     sh[e] = s_shift[c + e];
                 }
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    if (ok[i]) {
-                        uint32_t* w = reinterpret_cast<uint32_t*>(&v[i]);
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            float2 f = unpack_bf16x2(w[e]);
-                            f.x = apply_act(fmaf(f.x, sc[2 * e], sh[2 * e]), p.pro_act);
-                            f.y = apply_act(fmaf(f.y, sc[2 * e + 1], sh[2 * e + 1]), p.pro_act);
-                            w[e] = pack_bf16x2(f.x, f.y);
-                        }
-                    }
-                }
+                for (int i = 0; i < 8; ++i)
+                    if (ok & (1u << i)) transform8(v[i], sc, sh, p.pro_act);
             }
             mbar_wait(&empty_bar[stage], phase ^ 1);
             uint8_t* a_tile = a_tiles + stage * kATileBytes;
@@ -217,10 +240,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(&full_bar[stage]);
-            if (++stage == kStages) {
+            if (++stage == nstages) {
                 stage = 0;
                 phase ^= 1;
             }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = vn[i];
+            ok = okn;
+            c = cn;
         }
 
         // ===================== epilogue =====================
@@ -237,11 +264,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             uint32_t raw[32];
             tmem_ld_32x32b_x32(t_row + cc, raw);
             tmem_ld_wait();
-            float v[32];
+            float vv[32];
 #pragma unroll
-            for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(raw[e]);
-            float xr[32];  // mode-2 raw x / mode-0 residual / mode-1 mask source
-            const bool need_aux = p.aux != nullptr;
+            for (int e = 0; e < 32; ++e) vv[e] = __uint_as_float(raw[e]);
+            float xr[32];  // mode 0: residual / mode 1: mask source / mode 2: raw x
+            const bool need_aux = (kEpi != 0) || (p.aux != nullptr);
             if (need_aux) {
 #pragma unroll
                 for (int g = 0; g < 4; ++g) {
@@ -259,11 +286,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                 }
             }
             float sa[32], sb[32];
-            if (p.epi_mode == 0) {
+            if (kEpi == 0) {
 #pragma unroll
                 for (int e = 0; e < 32; ++e) {
                     const int n = nb + e;
-                    float o = v[e];
+                    float o = vv[e];
                     if (n < p.Cout) {
                         if (p.epi_scale) o *= p.epi_scale[n];
                         if (p.epi_shift) o += p.epi_shift[n];
@@ -273,16 +300,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                         o = 0.f;
                     }
                     o = __bfloat162float(__float2bfloat16_rn(o));
-                    v[e] = o;
+                    vv[e] = o;
                     sa[e] = mvalid ? o : 0.f;
                     sb[e] = mvalid ? o * o : 0.f;
                 }
-            } else if (p.epi_mode == 1) {
+            } else if (kEpi == 1) {
 #pragma unroll
                 for (int e = 0; e < 32; ++e) {
-                    float o = (nb + e < p.Cout && xr[e] > 0.f) ? v[e] : 0.f;
+                    float o = (nb + e < p.Cout && xr[e] > 0.f) ? vv[e] : 0.f;
                     o = __bfloat162float(__float2bfloat16_rn(o));
-                    v[e] = o;
+                    vv[e] = o;
                     sa[e] = mvalid ? o : 0.f;
                     sb[e] = 0.f;
                 }
@@ -295,11 +322,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                     if (n < p.Cout) {
                         gs = p.bwd_scale[n];
                         const float pre = fmaf(gs, xr[e], p.bwd_shift[n]);
-                        o = v[e] * act_mask(pre, p.bwd_act);
+                        o = vv[e] * act_mask(pre, p.bwd_act);
                     }
                     sa[e] = mvalid ? o : 0.f;
                     sb[e] = mvalid ? o * xr[e] : 0.f;
-                    v[e] = o;
+                    vv[e] = o;
                     xr[e] = gs;  // reuse as the G scale
                 }
             }
@@ -310,24 +337,24 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                 for (int g = 0; g < 4; ++g) {
                     if (nb + g * 8 < p.Cout) {
                         uint4 q;
-                        q.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
-                        q.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
-                        q.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
-                        q.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
+                        q.x = pack_bf16x2(vv[g * 8 + 0], vv[g * 8 + 1]);
+                        q.y = pack_bf16x2(vv[g * 8 + 2], vv[g * 8 + 3]);
+                        q.z = pack_bf16x2(vv[g * 8 + 4], vv[g * 8 + 5]);
+                        q.w = pack_bf16x2(vv[g * 8 + 6], vv[g * 8 + 7]);
                         *reinterpret_cast<uint4*>(yrow + g * 8) = q;
                     }
                 }
             }
-            if (p.epi_mode == 2 && mvalid && p.gacc != nullptr) {
+            if (kEpi == 2 && mvalid && p.gacc != nullptr) {
                 float* grow = p.gacc + static_cast<size_t>(m) * p.g_pitch + p.g_coff + nb;
 #pragma unroll
                 for (int g = 0; g < 8; ++g) {
                     if (nb + g * 4 < p.Cout) {
                         float4 q = *reinterpret_cast<float4*>(grow + g * 4);
-                        q.x = fmaf(xr[g * 4 + 0], v[g * 4 + 0], q.x);
-                        q.y = fmaf(xr[g * 4 + 1], v[g * 4 + 1], q.y);
-                        q.z = fmaf(xr[g * 4 + 2], v[g * 4 + 2], q.z);
-                        q.w = fmaf(xr[g * 4 + 3], v[g * 4 + 3], q.w);
+                        q.x = fmaf(xr[g * 4 + 0], vv[g * 4 + 0], q.x);
+                        q.y = fmaf(xr[g * 4 + 1], vv[g * 4 + 1], q.y);
+                        q.z = fmaf(xr[g * 4 + 2], vv[g * 4 + 2], q.z);
+                        q.w = fmaf(xr[g * 4 + 3], vv[g * 4 + 3], q.w);
                         *reinterpret_cast<float4*>(grow + g * 4) = q;
                     }
                 }
@@ -336,7 +363,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             if (p.stat_a != nullptr) {
                 const float ca = warp_column_sums(sa, lane);
                 if (nb + lane < p.Cout) atomicAdd(p.stat_a + nb + lane, ca);
-                if (p.stat_b != nullptr) {
+                if (kEpi != 1 && p.stat_b != nullptr) {
                     const float cb2 = warp_column_sums(sb, lane);
                     if (nb + lane < p.Cout) atomicAdd(p.stat_b + nb + lane, cb2);
                 }
@@ -349,24 +376,23 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             int stage = 0;
             uint32_t phase = 0;
             for (int kb = 0; kb < num_kb; ++kb) {
-                const int tap = kb / cblocks;
-                const int cb = kb - tap * cblocks;
-                const int wtap = p.flip ? (p.KH * p.KW - 1 - tap) : tap;
                 mbar_wait(&empty_bar[stage], phase ^ 1);
                 uint8_t* b_tile = b_tiles + stage * L::kBTileBytes;
                 mbar_arrive_expect_tx(&full_bar[stage], L::kBTileBytes);
                 if (!kBMN) {
-                    // K-major: rows = output channels, 64 K elements per row
-                    tma_load_2d(b_tile, &tmap_w, &full_bar[stage], wtap * p.w_cols_per_tap + cb * kBK,
-                                n0);
+                    // K-major: rows = output channels, 64 linearised (tap, cin) K elements per row
+                    tma_load_2d(b_tile, &tmap_w, &full_bar[stage], kb * kBK, n0);
                 } else {
                     // MN-major: rows = K (the original Cout), 64 N elements per row, per 64-wide chunk
+                    const int tap = kb / cblocks;
+                    const int cb = kb - tap * cblocks;
+                    const int wtap = p.flip ? (taps - 1 - tap) : tap;
 #pragma unroll
                     for (int ch = 0; ch < (kBN + 63) / 64; ++ch)
                         tma_load_2d(b_tile + ch * 8192, &tmap_w, &full_bar[stage],
                                     wtap * p.w_cols_per_tap + n0 + ch * 64, cb * kBK);
                 }
-                if (++stage == kStages) {
+                if (++stage == nstages) {
                     stage = 0;
                     phase ^= 1;
                 }
@@ -391,7 +417,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                     umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[stage]);
-                if (++stage == kStages) {
+                if (++stage == nstages) {
                     stage = 0;
                     phase ^= 1;
                 }
@@ -408,9 +434,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
 }
 
 // =============================================================================================
-// wgrad kernel: dW[cout][tap][cin] += sum_pos  act(s*x+t)[pos+tap][cin] * dy[pos][cout]
-//   D (TMEM) = [128 cin  x  kBN cout], both operands MN-major, K = positions.
-//   grid = (cin tiles, cout tiles, taps * splits)
+// wgrad kernel: dW[cout][tap*Cin + cin] += sum_pos  act(s*x+t)[pos+tap][cin] * dy[pos][cout]
+//   D (TMEM) = [128 linearised (tap,cin) rows  x  kBN cout], both operands MN-major, K = positions.
+//   grid = (ceil(taps*Cin/128), cout tiles, splits over positions)
 // =============================================================================================
 struct WgradArgs {
     const __nv_bfloat16* x;
@@ -421,31 +447,33 @@ struct WgradArgs {
     const float* pro_scale;
     const float* pro_shift;
     int pro_act;
-    float* dw;  // fp32 [Cout][KH*KW][Cin], accumulated with red.add
+    float* dw;  // fp32 [Cout][KH*KW*Cin], accumulated with red.add
     int splits;
     int kb_per_split;  // 64-position blocks per split
+    int stages;
 };
 
 template <int kBN>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ WgradArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     constexpr int kBTile = ((kBN + 63) / 64) * 8192;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
-    uint8_t* a_tiles = smem;  // [64 pos][128 cin] as two 8 KiB chunks
-    uint8_t* b_tiles = smem + kStages * kATileBytes;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + kStages * kBTile);
-    uint64_t* empty_bar = full_bar + kStages;
-    uint64_t* acc_bar = empty_bar + kStages;
+    const int nstages = p.stages;
+    uint8_t* a_tiles = smem;  // [64 pos][128 k'] as two 8 KiB chunks
+    uint8_t* b_tiles = smem + nstages * kATileBytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + nstages * kBTile);
+    uint64_t* empty_bar = full_bar + kMaxStages;
+    uint64_t* acc_bar = empty_bar + kMaxStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int cin0 = blockIdx.x * 128;
+    const int k0 = blockIdx.x * 128;  // first linearised (tap, cin) row of this tile
     const int n0 = blockIdx.y * kBN;
-    const int tap = blockIdx.z / p.splits;
-    const int split = blockIdx.z - tap * p.splits;
+    const int ktot = p.KH * p.KW * p.Cin;
+    const int split = blockIdx.z;
     const int total_kb = (p.M + 63) / 64;
     const int kb_begin = split * p.kb_per_split;
     int kb_end = kb_begin + p.kb_per_split;
@@ -453,7 +481,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     const int num_kb = kb_end > kb_begin ? kb_end - kb_begin : 0;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; ++s) {
+        for (int s = 0; s < nstages; ++s) {
             mbar_init(&full_bar[s], 4 + 1);
             mbar_init(&empty_bar[s], 1);
         }
@@ -473,13 +501,17 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     }
 
     if (warp < 4) {
-        // ---- A producers: 16 threads cover one position row (128 channels = 256 B) ----
+        // ---- A producers: 16 threads cover one position row (128 k' = 256 B) ----
         const int j16 = threadIdx.x & 15;
-        const int half = j16 >> 3;  // which 64-channel chunk
+        const int half = j16 >> 3;  // which 64-wide chunk
         const int j = j16 & 7;
         const int rbase = threadIdx.x >> 4;  // 0..7
-        const int c = cin0 + j16 * 8;
-        const bool cvalid = c < p.Cin;
+        const int kidx = k0 + j16 * 8;
+        const bool cvalid = kidx < ktot;
+        const int tap = cvalid ? kidx / p.Cin : 0;
+        const int c = cvalid ? kidx - tap * p.Cin : 0;
+        const int kh = tap / p.KW;
+        const int kw = tap - kh * p.KW;
         const bool has_pro = p.pro_scale != nullptr;
         float sc[8], sh[8];
 #pragma unroll
@@ -487,19 +519,13 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
             sc[e] = (has_pro && cvalid) ? p.pro_scale[c + e] : 1.f;
             sh[e] = (has_pro && cvalid) ? p.pro_shift[c + e] : 0.f;
         }
-        const int kh = tap / p.KW;
-        const int kw = tap - kh * p.KW;
         const int hw = p.Ho * p.Wo;
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int kb = kb_begin; kb < kb_end; ++kb) {
-            uint4 v[8];
-            bool ok[8];
+        auto issue = [&](int kb, uint4 (&v)[8], uint32_t& okmask) {
+            okmask = 0;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int m = kb * 64 + i * 8 + rbase;
                 v[i] = make_uint4(0u, 0u, 0u, 0u);
-                ok[i] = false;
                 if (cvalid && m < p.M) {
                     const int b = m / hw;
                     const int rem = m - b * hw;
@@ -508,27 +534,25 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
                     const int hi = ho * p.stride - p.pad_t + kh;
                     const int wi = wo * p.stride - p.pad_l + kw;
                     if (hi >= 0 && hi < p.H && wi >= 0 && wi < p.W) {
-                        ok[i] = true;
+                        okmask |= 1u << i;
                         const size_t off =
                             (static_cast<size_t>((b * p.H + hi) * p.W + wi)) * p.x_pitch + p.x_coff + c;
                         v[i] = __ldg(reinterpret_cast<const uint4*>(p.x + off));
                     }
                 }
             }
+        };
+        int stage = 0;
+        uint32_t phase = 0;
+        uint4 v[8], vn[8];
+        uint32_t ok = 0, okn = 0;
+        issue(kb_begin, v, ok);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+            if (kb + 1 < kb_end) issue(kb + 1, vn, okn);
             if (has_pro) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    if (ok[i]) {
-                        uint32_t* w = reinterpret_cast<uint32_t*>(&v[i]);
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            float2 f = unpack_bf16x2(w[e]);
-                            f.x = apply_act(fmaf(f.x, sc[2 * e], sh[2 * e]), p.pro_act);
-                            f.y = apply_act(fmaf(f.y, sc[2 * e + 1], sh[2 * e + 1]), p.pro_act);
-                            w[e] = pack_bf16x2(f.x, f.y);
-                        }
-                    }
-                }
+                for (int i = 0; i < 8; ++i)
+                    if (ok & (1u << i)) transform8(v[i], sc, sh, p.pro_act);
             }
             mbar_wait(&empty_bar[stage], phase ^ 1);
             uint8_t* a_tile = a_tiles + stage * kATileBytes + half * 8192;
@@ -540,29 +564,31 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(&full_bar[stage]);
-            if (++stage == kStages) {
+            if (++stage == nstages) {
                 stage = 0;
                 phase ^= 1;
             }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = vn[i];
+            ok = okn;
         }
         // ---- epilogue: red.add the fp32 tile into dW ----
         mbar_wait(acc_bar, 0);
         tc_fence_after();
-        const int cin = cin0 + warp * 32 + lane;
+        const int krow = k0 + warp * 32 + lane;
         const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
-        const int taps = p.KH * p.KW;
 #pragma unroll 1
         for (int cc = 0; cc < kBN; cc += 32) {
+            if (n0 + cc >= p.Cout) break;
             uint32_t raw[32];
             tmem_ld_32x32b_x32(t_row + cc, raw);
             tmem_ld_wait();
-            if (cin < p.Cin) {
+            if (krow < ktot) {
 #pragma unroll
                 for (int e = 0; e < 32; ++e) {
                     const int n = n0 + cc + e;
                     if (n < p.Cout)
-                        atomicAdd(p.dw + (static_cast<size_t>(n) * taps + tap) * p.Cin + cin,
-                                  __uint_as_float(raw[e]));
+                        atomicAdd(p.dw + static_cast<size_t>(n) * ktot + krow, __uint_as_float(raw[e]));
                 }
             }
         }
@@ -578,7 +604,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 #pragma unroll
                 for (int ch = 0; ch < (kBN + 63) / 64; ++ch)
                     tma_load_2d(b_tile + ch * 8192, &tmap_dy, &full_bar[stage], n0 + ch * 64, kb * 64);
-                if (++stage == kStages) {
+                if (++stage == nstages) {
                     stage = 0;
                     phase ^= 1;
                 }
@@ -601,7 +627,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
                     umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[stage]);
-                if (++stage == kStages) {
+                if (++stage == nstages) {
                     stage = 0;
                     phase ^= 1;
                 }
@@ -620,13 +646,24 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 // ---------------------------------------------------------------------------------------------
 // Host launchers
 // ---------------------------------------------------------------------------------------------
-template <int kBN, bool kBMN>
-static int launch_gemm(const CUtensorMap& tm, const ConvArgs& a, cudaStream_t st) {
+static int pick_stages(int num_kb, int stage_bytes, int extra_bytes) {
+    int s = num_kb < kMaxStages ? num_kb : kMaxStages;
+    if (s < 1) s = 1;
+    // keep two CTAs resident per SM when the pipeline depth allows it (latency hiding across CTAs)
+    while (s > 2 && 2 * (1024 + s * stage_bytes + extra_bytes + 256) > 227 * 1024) --s;
+    return s;
+}
+
+template <int kBN, bool kBMN, int kEpi>
+static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     using L = FwdSmem<kBN, kBMN>;
-    const size_t smem = 1024 + kStages * L::kStageBytes + (2 * kStages + 1) * 8 + 16 +
-                        2 * sizeof(float) * a.Cin + 64;
+    const int taps = a.KH * a.KW;
+    const int num_kb = kBMN ? taps * ceil_div(a.Cin, kBK) : ceil_div(taps * a.Cin, kBK);
+    const int extra = (2 * kMaxStages + 1) * 8 + 16 + 2 * (int)sizeof(float) * a.Cin + 64;
+    a.stages = pick_stages(num_kb, L::kStageBytes, extra);
+    const size_t smem = 1024 + a.stages * L::kStageBytes + extra;
     IDCB_REQUIRE(smem <= 227 * 1024, "conv: Cin=%d needs %zu bytes of shared memory", a.Cin, smem);
-    auto kern = conv_gemm_kernel<kBN, kBMN>;
+    auto kern = conv_gemm_kernel<kBN, kBMN, kEpi>;
     static bool attr_set = false;
     if (!attr_set) {
         IDCB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -640,9 +677,11 @@ static int launch_gemm(const CUtensorMap& tm, const ConvArgs& a, cudaStream_t st
 }
 
 template <int kBN>
-static int launch_wgrad(const CUtensorMap& tm, const WgradArgs& a, cudaStream_t st) {
+static int launch_wgrad(const CUtensorMap& tm, WgradArgs& a, cudaStream_t st) {
     constexpr int kBTile = ((kBN + 63) / 64) * 8192;
-    const size_t smem = 1024 + kStages * (kATileBytes + kBTile) + (2 * kStages + 1) * 8 + 16 + 64;
+    const int extra = (2 * kMaxStages + 1) * 8 + 16 + 64;
+    a.stages = pick_stages(a.kb_per_split, kATileBytes + kBTile, extra);
+    const size_t smem = 1024 + a.stages * (kATileBytes + kBTile) + extra;
     auto kern = conv_wgrad_kernel<kBN>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -650,7 +689,7 @@ static int launch_wgrad(const CUtensorMap& tm, const WgradArgs& a, cudaStream_t 
                                         227 * 1024));
         attr_set = true;
     }
-    dim3 grid(ceil_div(a.Cin, 128), ceil_div(a.Cout, kBN), a.KH * a.KW * a.splits);
+    dim3 grid(ceil_div(a.KH * a.KW * a.Cin, 128), ceil_div(a.Cout, kBN), a.splits);
     kern<<<grid, kThreads, smem, st>>>(tm, a);
     IDCB_LAUNCH_CHECK();
     return 0;
@@ -691,7 +730,6 @@ extern "C" int idcb_conv_fprop(const idcb_conv_desc* d, const void* x, const voi
     a.y = static_cast<__nv_bfloat16*>(y);
     a.y_pitch = d->y_pitch; a.y_coff = d->y_coff;
     a.w_cols_per_tap = d->cin;
-    a.epi_mode = 0;
     if (f) {
         a.pro_scale = f->pro_scale; a.pro_shift = f->pro_shift; a.pro_act = f->pro_act;
         a.epi_scale = f->epi_scale; a.epi_shift = f->epi_shift; a.epi_act = f->epi_act;
@@ -706,9 +744,9 @@ extern "C" int idcb_conv_fprop(const idcb_conv_desc* d, const void* x, const voi
     if (make_tmap_2d_bf16(&tm, w, d->cout, (uint64_t)d->kh * d->kw * d->cin,
                           (uint64_t)d->kh * d->kw * d->cin, kbn, 64))
         return 1;
-    if (kbn == 32) return launch_gemm<32, false>(tm, a, st);
-    if (kbn == 64) return launch_gemm<64, false>(tm, a, st);
-    return launch_gemm<128, false>(tm, a, st);
+    if (kbn == 32) return launch_gemm<32, false, 0>(tm, a, st);
+    if (kbn == 64) return launch_gemm<64, false, 0>(tm, a, st);
+    return launch_gemm<128, false, 0>(tm, a, st);
 }
 
 // dgrad: the descriptor describes the FORWARD convolution; dy has the forward output geometry and
@@ -732,9 +770,9 @@ extern "C" int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const vo
     a.y = static_cast<__nv_bfloat16*>(dx);
     a.y_pitch = d->x_pitch; a.y_coff = d->x_coff;
     a.w_cols_per_tap = d->cin;
-    a.epi_mode = 0;
+    int mode = 0;
     if (f) {
-        a.epi_mode = f->mode;
+        mode = f->mode;
         a.aux = static_cast<const __nv_bfloat16*>(f->aux);
         a.aux_pitch = f->aux_pitch; a.aux_coff = f->aux_coff;
         a.bwd_scale = f->bwd_scale; a.bwd_shift = f->bwd_shift; a.bwd_act = f->bwd_act;
@@ -754,8 +792,14 @@ extern "C" int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const vo
     if (make_tmap_2d_bf16(&tm, w, d->cout, (uint64_t)d->kh * d->kw * d->cin,
                           (uint64_t)d->kh * d->kw * d->cin, 64, 64))
         return 1;
-    if (kbn == 64) return launch_gemm<64, true>(tm, a, st);
-    return launch_gemm<128, true>(tm, a, st);
+    if (kbn == 64) {
+        if (mode == 0) return launch_gemm<64, true, 0>(tm, a, st);
+        if (mode == 1) return launch_gemm<64, true, 1>(tm, a, st);
+        return launch_gemm<64, true, 2>(tm, a, st);
+    }
+    if (mode == 0) return launch_gemm<128, true, 0>(tm, a, st);
+    if (mode == 1) return launch_gemm<128, true, 1>(tm, a, st);
+    return launch_gemm<128, true, 2>(tm, a, st);
 }
 
 extern "C" int idcb_conv_wgrad(const idcb_conv_desc* d, const void* x, const void* dy, float* dw,
@@ -777,7 +821,7 @@ extern "C" int idcb_conv_wgrad(const idcb_conv_desc* d, const void* x, const voi
     a.dw = dw;
     const int kbn = d->cout <= 32 ? 32 : (d->cout <= 64 ? 64 : 128);
     const int total_kb = ceil_div(a.M, 64);
-    const int base_ctas = ceil_div(a.Cin, 128) * ceil_div(a.Cout, kbn) * a.KH * a.KW;
+    const int base_ctas = ceil_div(a.KH * a.KW * a.Cin, 128) * ceil_div(a.Cout, kbn);
     int splits = ceil_div(2 * num_sms(), base_ctas);
     if (splits > total_kb) splits = total_kb;
     if (splits < 1) splits = 1;
