@@ -507,6 +507,89 @@ static inline int ew_grid(long long work_items, int threads) {
     return static_cast<int>(g);
 }
 
+// ---------------------------------------------------------------------------------------------
+// BatchNorm backward applied in ONE launch: every thread derives the coefficients of its 8 channels
+// from the per-channel sums (what bn_bwd_coeffs / bn_shared_coeffs compute) and then streams
+//     out = A*g + B*x + C0
+// over its rows. mode 0: standalone training BN (also emits dgamma/dbeta), mode 1: frozen BN
+// (out = scale*g), mode 2: DenseNet shared-buffer slice (A = 1, correction from S1/S2).
+// grid = (row splits, ceil(C/64)); block = 256 = 8 channel octets x 32 row lanes.
+// ---------------------------------------------------------------------------------------------
+struct BnApplyArgs {
+    const void* g; int g_is_float, g_pitch, g_coff;
+    const __nv_bfloat16* x; int x_pitch, x_coff;
+    __nv_bfloat16* out; int o_pitch, o_coff;
+    const float* sa; const float* sb;      // mode 0: sum dpre, sum dpre*x ; mode 2: S1, S2
+    const float* mean; const float* rstd; const float* scale;
+    float count;
+    float* dgamma; float* dbeta;
+    int mode;
+    long long M; int C;
+};
+
+template <bool kGFloat>
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(BnApplyArgs p) {
+    const int oct = threadIdx.x & 7;
+    const int rl = threadIdx.x >> 3;
+    const int c = blockIdx.y * 64 + oct * 8;
+    if (c >= p.C) return;
+    float A[8], B[8], C0[8];
+    const float invn = 1.f / p.count;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        const int ch = c + e;
+        if (p.mode == 1) {
+            A[e] = p.scale[ch]; B[e] = 0.f; C0[e] = 0.f;
+        } else if (p.mode == 0) {
+            const float a = p.sa[ch], b = p.sb[ch], m = p.mean[ch], r = p.rstd[ch], s = p.scale[ch];
+            const float dg = r * (b - m * a);
+            A[e] = s;
+            B[e] = -s * r * dg * invn;
+            C0[e] = -s * a * invn + s * r * m * dg * invn;
+            if (blockIdx.x == 0 && rl == 0) {
+                if (p.dgamma) p.dgamma[ch] += dg;
+                if (p.dbeta) p.dbeta[ch] += a;
+            }
+        } else {
+            const float r = p.rstd[ch], m = p.mean[ch];
+            A[e] = 1.f;
+            B[e] = -r * p.sb[ch] * invn;
+            C0[e] = -p.sa[ch] * invn + r * m * p.sb[ch] * invn;
+        }
+    }
+    for (long long m = blockIdx.x * 32 + rl; m < p.M; m += (long long)gridDim.x * 32) {
+        float gv[8];
+        if (kGFloat) {
+            const float* gp = static_cast<const float*>(p.g) + m * p.g_pitch + p.g_coff + c;
+            const float4 a = *reinterpret_cast<const float4*>(gp);
+            const float4 b = *reinterpret_cast<const float4*>(gp + 4);
+            gv[0] = a.x; gv[1] = a.y; gv[2] = a.z; gv[3] = a.w;
+            gv[4] = b.x; gv[5] = b.y; gv[6] = b.z; gv[7] = b.w;
+        } else {
+            const uint4 q = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(p.g) +
+                                                            m * p.g_pitch + p.g_coff + c);
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(&q);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 f = unpack_bf16x2(w[e]);
+                gv[2 * e] = f.x;
+                gv[2 * e + 1] = f.y;
+            }
+        }
+        const uint4 xq = *reinterpret_cast<const uint4*>(p.x + m * p.x_pitch + p.x_coff + c);
+        const uint32_t* xw = reinterpret_cast<const uint32_t*>(&xq);
+        uint4 o;
+        uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float2 xf = unpack_bf16x2(xw[e]);
+            ow[e] = pack_bf16x2(fmaf(A[2 * e], gv[2 * e], fmaf(B[2 * e], xf.x, C0[2 * e])),
+                                fmaf(A[2 * e + 1], gv[2 * e + 1], fmaf(B[2 * e + 1], xf.y, C0[2 * e + 1])));
+        }
+        *reinterpret_cast<uint4*>(p.out + m * p.o_pitch + p.o_coff + c) = o;
+    }
+}
+
 }  // namespace idcb
 
 using namespace idcb;
@@ -584,6 +667,39 @@ extern "C" int idcb_affine2(const void* g, int g_is_float, int g_pitch, int g_co
     else
         affine2_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(
             g, g_pitch, g_coff, (cbf)x, x_pitch, x_coff, (bf)out, o_pitch, o_coff, A, B, C0, M, C);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_bn_bwd_apply(int mode, const void* g, int g_is_float, int g_pitch, int g_coff,
+                                 const void* x, int x_pitch, int x_coff, void* out, int o_pitch,
+                                 int o_coff, const float* sa, const float* sb, const float* mean,
+                                 const float* rstd, const float* scale, float count, float* dgamma,
+                                 float* dbeta, long long M, int C, void* stream) {
+    IDCB_REQUIRE(mode >= 0 && mode <= 2, "bn_bwd_apply: bad mode %d", mode);
+    IDCB_REQUIRE(C % 8 == 0 && g_pitch % 8 == 0 && g_coff % 8 == 0 && x_pitch % 8 == 0 &&
+                     x_coff % 8 == 0 && o_pitch % 8 == 0 && o_coff % 8 == 0,
+                 "bn_bwd_apply: channel counts/pitches must be multiples of 8");
+    IDCB_REQUIRE(mode == 1 ? scale != nullptr : (sa && sb && mean && rstd && count > 0.f),
+                 "bn_bwd_apply: missing per-channel inputs for mode %d", mode);
+    IDCB_REQUIRE(mode != 0 || scale != nullptr, "bn_bwd_apply: mode 0 needs scale");
+    if (M == 0) return 0;
+    BnApplyArgs a{};
+    a.g = g; a.g_is_float = g_is_float; a.g_pitch = g_pitch; a.g_coff = g_coff;
+    a.x = (cbf)x; a.x_pitch = x_pitch; a.x_coff = x_coff;
+    a.out = (bf)out; a.o_pitch = o_pitch; a.o_coff = o_coff;
+    a.sa = sa; a.sb = sb; a.mean = mean; a.rstd = rstd; a.scale = scale; a.count = count;
+    a.dgamma = dgamma; a.dbeta = dbeta; a.mode = mode; a.M = M; a.C = C;
+    const int ygroups = ceil_div(C, 64);
+    int splits = static_cast<int>(ceil_div_ll(M, 32 * 4));
+    const int cap = ceil_div(4 * num_sms(), ygroups);
+    if (splits > cap) splits = cap;
+    if (splits < 1) splits = 1;
+    dim3 grid(splits, ygroups);
+    if (g_is_float)
+        bn_bwd_apply_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    else
+        bn_bwd_apply_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
     IDCB_LAUNCH_CHECK();
     return 0;
 }

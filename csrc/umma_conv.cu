@@ -5,18 +5,24 @@
 //   idcb_conv_dgrad : dx = epilogue( conv^T( dy, W ) )            (stride 1 only)
 //   idcb_conv_wgrad : dW += prologue(x)^T (*) dy                   (split over positions)
 //
-// Data flow per CTA (192 threads):
-//   warps 0-3  : A-operand producers. They gather the im2col rows straight from global memory
+// Data flow per CTA (320 threads):
+//   warps 0-7  : A-operand producers. They gather the im2col rows straight from global memory
 //                (zero padding, channel-prefix views of a DenseNet concat buffer, and the fused
 //                BatchNorm scale/shift + ReLU/ReLU6 prologue happen here, in registers), write the
 //                128-byte-swizzled operand tile into shared memory, fence it to the async proxy and
 //                arrive on the stage's "full" mbarrier. The loads of k-block i+1 are issued before
 //                k-block i is transformed and stored, so two k-blocks of global traffic are in flight
-//                per CTA. After the main loop the same four warps are the epilogue: tcgen05.ld the fp32
-//                accumulators out of TMEM, apply the fused epilogue and store.
-//   warp 4     : TMA producer for the second operand (weights, or dy for wgrad).
-//   warp 5     : allocates TMEM, then one lane issues tcgen05.mma (UMMA 128 x N x 16, bf16 -> fp32)
+//                per CTA. After the main loop the same eight warps are the epilogue: tcgen05.ld the fp32
+//                accumulators out of TMEM (warp w owns TMEM lanes 32*(w%4).. and column half w/4),
+//                apply the fused epilogue and store.
+//   warp 8     : TMA producer for the second operand (weights, or dy for wgrad).
+//   warp 9     : allocates TMEM, then one lane issues tcgen05.mma (UMMA 128 x N x 16, bf16 -> fp32)
 //                and tcgen05.commit to recycle the stage / publish the accumulator.
+//
+// The problems of this workload are tiny (DenseNet-121 at 50x50: M = 128..21632 rows, K = 64..1152),
+// so a CTA lives for a few microseconds and what matters is the length of the per-thread dependent
+// instruction chain, not MMA throughput: index math uses precomputed multiply-high division, rows are
+// spread over eight warps, and the epilogue code is specialised per mode at compile time.
 //
 // The activation tile layout [rows = positions][64 channels = 128 B], SWIZZLE_128B, is read as a
 // K-major operand by fprop/dgrad (K = channels) and as an MN-major operand by wgrad (K = positions),
@@ -37,8 +43,24 @@ namespace idcb {
 constexpr int kBM = 128;      // UMMA M (rows of the accumulator = TMEM lanes)
 constexpr int kBK = 64;       // K elements per pipeline stage (one 128-byte swizzle row)
 constexpr int kMaxStages = 4;
-constexpr int kThreads = 192;
+constexpr int kWorkers = 256;  // 8 producer / epilogue warps
+constexpr int kThreads = kWorkers + 64;
+constexpr int kTmaWarp = 8, kMmaWarp = 9;
+constexpr int kFullArrivals = 8 + 1;    // 8 producer warps + the TMA thread
 constexpr int kATileBytes = kBM * 128;  // 16 KiB
+
+// n / d for n*d < 2^64 with one 64-bit multiply-high (magic == 0 encodes d == 1)
+struct FastDiv {
+    unsigned long long magic;
+};
+static FastDiv make_fdiv(unsigned d) {
+    FastDiv f;
+    f.magic = d <= 1 ? 0ULL : (~0ULL) / d + 1ULL;
+    return f;
+}
+__device__ __forceinline__ unsigned fdiv(unsigned n, const FastDiv& f) {
+    return f.magic ? static_cast<unsigned>(__umul64hi(static_cast<unsigned long long>(n), f.magic)) : n;
+}
 
 struct ConvArgs {
     // activations (A operand source)
@@ -50,10 +72,24 @@ struct ConvArgs {
     int Cout;  // N extent
     int flip;  // dgrad: tap index into the weight tensor is mirrored
     int stages;
+    FastDiv d_hw, d_wo, d_cin, d_kw, d_cb;
     // prologue on A: a = act(scale[c] * x + shift[c]) (null scale => identity)
     const float* pro_scale;
     const float* pro_shift;
     int pro_act;
+    // ... or BatchNorm finalised in-kernel from batch sums (training mode): every CTA derives the
+    // per-channel scale/shift itself; CTA (0,0) also publishes them and updates the moving statistics
+    const float* bn_sum;
+    const float* bn_sq;
+    const float* bn_gamma;
+    const float* bn_beta;
+    float bn_count, bn_eps, bn_momentum;
+    float* bn_scale_out;
+    float* bn_shift_out;
+    float* bn_mean_out;
+    float* bn_rstd_out;
+    float* bn_mmean;
+    float* bn_mvar;
     // epilogue (mode is a template parameter)
     const float* epi_scale;
     const float* epi_shift;
@@ -70,12 +106,24 @@ struct ConvArgs {
     float* stat_a;  // per-N column sums: mode 0/1: sum(y); mode 2: sum(dpre)
     float* stat_b;  //                    mode 0: sum(y^2);  mode 2: sum(dpre * x_raw)
     int w_cols_per_tap;  // dgrad: column stride between taps in the 2-D weight view
+    long long* dbg;      // optional: per-phase clock64 stamps of CTA (0,0) (profiling aid)
 };
 
-// Butterfly transpose-reduce: on return lane l holds the sum over the warp of column l.
-__device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
+#define IDCB_STAMP(i)                                                                     \
+    do {                                                                                  \
+        if (p.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0) p.dbg[i] = clock64(); \
+    } while (0)
+
+// Butterfly transpose-reduce over kW (32 or 16) per-lane values: on return lane l holds the warp-wide
+// sum of column (l % kW).
+template <int kW>
+__device__ __forceinline__ float warp_column_sums(float (&v)[kW], int lane) {
+    if (kW == 16) {
 #pragma unroll
-    for (int n = 16; n >= 1; n >>= 1) {
+        for (int i = 0; i < kW; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
+    }
+#pragma unroll
+    for (int n = (kW == 32 ? 16 : 8); n >= 1; n >>= 1) {
         const bool up = (lane & n) != 0;
 #pragma unroll
         for (int i = 0; i < n; ++i) {
@@ -87,14 +135,153 @@ __device__ __forceinline__ float warp_column_sums(float (&v)[32], int lane) {
     return v[0];
 }
 
-__device__ __forceinline__ void transform8(uint4& q, const float* sc, const float* sh, int act) {
+__device__ __forceinline__ void transform8(uint4& q, const float4& s0, const float4& s1,
+                                           const float4& h0, const float4& h1, int act) {
     uint32_t* w = reinterpret_cast<uint32_t*>(&q);
+    float2 f;
+    f = unpack_bf16x2(w[0]);
+    w[0] = pack_bf16x2(apply_act(fmaf(f.x, s0.x, h0.x), act), apply_act(fmaf(f.y, s0.y, h0.y), act));
+    f = unpack_bf16x2(w[1]);
+    w[1] = pack_bf16x2(apply_act(fmaf(f.x, s0.z, h0.z), act), apply_act(fmaf(f.y, s0.w, h0.w), act));
+    f = unpack_bf16x2(w[2]);
+    w[2] = pack_bf16x2(apply_act(fmaf(f.x, s1.x, h1.x), act), apply_act(fmaf(f.y, s1.y, h1.y), act));
+    f = unpack_bf16x2(w[3]);
+    w[3] = pack_bf16x2(apply_act(fmaf(f.x, s1.z, h1.z), act), apply_act(fmaf(f.y, s1.w, h1.w), act));
+}
+
+template <int kW>
+__device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, float (&v)[kW]) {
+    if (kW == 32) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr, r);
+        tmem_ld_wait();
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-        float2 f = unpack_bf16x2(w[e]);
-        f.x = apply_act(fmaf(f.x, sc[2 * e], sh[2 * e]), act);
-        f.y = apply_act(fmaf(f.y, sc[2 * e + 1], sh[2 * e + 1]), act);
-        w[e] = pack_bf16x2(f.x, f.y);
+        for (int e = 0; e < 32; ++e) v[e] = __uint_as_float(r[e]);
+    } else {
+        uint32_t r[16];
+        tmem_ld_32x32b_x16(taddr, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 16; ++e) v[e] = __uint_as_float(r[e]);
+    }
+}
+
+// bf16 row segment of kW channels -> float (zero where n >= limit or the row is invalid)
+template <int kW>
+__device__ __forceinline__ void load_row_bf16(const __nv_bfloat16* rowptr, bool rowvalid, int nb,
+                                              int limit, float (&out)[kW]) {
+#pragma unroll
+    for (int g = 0; g < kW / 8; ++g) {
+        uint4 q = make_uint4(0u, 0u, 0u, 0u);
+        if (rowvalid && nb + g * 8 < limit) q = *reinterpret_cast<const uint4*>(rowptr + g * 8);
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(&q);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            float2 f = unpack_bf16x2(w[e]);
+            out[g * 8 + 2 * e] = f.x;
+            out[g * 8 + 2 * e + 1] = f.y;
+        }
+    }
+}
+
+// One kW-column slab of the fused epilogue for the row owned by this thread.
+template <int kEpi, int kW>
+__device__ __forceinline__ void epilogue_slab(const ConvArgs& p, uint32_t taddr, int m, bool mvalid,
+                                              int nb, int lane) {
+    float vv[kW];
+    tmem_ld_cols<kW>(taddr, vv);
+    float xr[kW];
+    const bool need_aux = (kEpi != 0) || (p.aux != nullptr);
+    if (need_aux)
+        load_row_bf16<kW>(p.aux + static_cast<size_t>(m) * p.aux_pitch + p.aux_coff + nb, mvalid, nb,
+                          p.Cout, xr);
+    if (kEpi == 0) {
+        if (p.epi_scale != nullptr) {
+#pragma unroll
+            for (int e = 0; e < kW; ++e) vv[e] *= (nb + e < p.Cout) ? __ldg(p.epi_scale + nb + e) : 0.f;
+        }
+        if (p.epi_shift != nullptr) {
+#pragma unroll
+            for (int e = 0; e < kW; ++e) vv[e] += (nb + e < p.Cout) ? __ldg(p.epi_shift + nb + e) : 0.f;
+        }
+        if (p.epi_act == 1) {
+#pragma unroll
+            for (int e = 0; e < kW; ++e) vv[e] = fmaxf(vv[e], 0.f);
+        } else if (p.epi_act == 2) {
+#pragma unroll
+            for (int e = 0; e < kW; ++e) vv[e] = fminf(fmaxf(vv[e], 0.f), 6.f);
+        }
+        if (need_aux) {
+#pragma unroll
+            for (int e = 0; e < kW; ++e) vv[e] += xr[e];
+        }
+    } else if (kEpi == 1) {
+#pragma unroll
+        for (int e = 0; e < kW; ++e) vv[e] = xr[e] > 0.f ? vv[e] : 0.f;
+    } else {
+        // BN + activation backward: dpre = acc * act'(scale*x + shift); xr becomes the G scale
+#pragma unroll
+        for (int e = 0; e < kW; ++e) {
+            const bool nv = nb + e < p.Cout;
+            const float gs = nv ? __ldg(p.bwd_scale + nb + e) : 0.f;
+            const float gh = nv ? __ldg(p.bwd_shift + nb + e) : 0.f;
+            const float pre = fmaf(gs, xr[e], gh);
+            vv[e] = nv ? vv[e] * act_mask(pre, p.bwd_act) : 0.f;
+        }
+    }
+    uint32_t packed[kW / 2];
+#pragma unroll
+    for (int e = 0; e < kW / 2; ++e) packed[e] = pack_bf16x2(vv[2 * e], vv[2 * e + 1]);
+    if (kEpi == 0 && p.stat_a != nullptr) {
+        // BatchNorm statistics must describe exactly what the consumers will read back (bf16)
+#pragma unroll
+        for (int e = 0; e < kW / 2; ++e) {
+            const float2 f = unpack_bf16x2(packed[e]);
+            vv[2 * e] = f.x;
+            vv[2 * e + 1] = f.y;
+        }
+    }
+    if (mvalid && p.y != nullptr) {
+        __nv_bfloat16* yrow = p.y + static_cast<size_t>(m) * p.y_pitch + p.y_coff + nb;
+#pragma unroll
+        for (int g = 0; g < kW / 8; ++g)
+            if (nb + g * 8 < p.Cout)
+                *reinterpret_cast<uint4*>(yrow + g * 8) =
+                    make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+    }
+    if (kEpi == 2 && mvalid && p.gacc != nullptr) {
+        float* grow = p.gacc + static_cast<size_t>(m) * p.g_pitch + p.g_coff + nb;
+#pragma unroll
+        for (int g = 0; g < kW / 4; ++g) {
+            if (nb + g * 4 < p.Cout) {
+                float4 q = *reinterpret_cast<float4*>(grow + g * 4);
+                q.x = fmaf(__ldg(p.bwd_scale + nb + g * 4 + 0), vv[g * 4 + 0], q.x);
+                q.y = fmaf(__ldg(p.bwd_scale + nb + g * 4 + 1), vv[g * 4 + 1], q.y);
+                q.z = fmaf(__ldg(p.bwd_scale + nb + g * 4 + 2), vv[g * 4 + 2], q.z);
+                q.w = fmaf(__ldg(p.bwd_scale + nb + g * 4 + 3), vv[g * 4 + 3], q.w);
+                *reinterpret_cast<float4*>(grow + g * 4) = q;
+            }
+        }
+    }
+    // ---- column statistics (BatchNorm sums / bias gradient / BN-backward sums) ----
+    if (p.stat_a != nullptr) {
+        float sb[kW];
+        const bool want_b = (kEpi != 1) && p.stat_b != nullptr;
+        if (want_b) {
+#pragma unroll
+            for (int e = 0; e < kW; ++e) sb[e] = mvalid ? (kEpi == 2 ? vv[e] * xr[e] : vv[e] * vv[e]) : 0.f;
+        }
+        if (!mvalid) {
+#pragma unroll
+            for (int e = 0; e < kW; ++e) vv[e] = 0.f;
+        }
+        const float ca = warp_column_sums<kW>(vv, lane);
+        const bool owner = lane < kW && nb + lane < p.Cout;
+        if (owner) atomicAdd(p.stat_a + nb + lane, ca);
+        if (want_b) {
+            const float cb = warp_column_sums<kW>(sb, lane);
+            if (owner) atomicAdd(p.stat_b + nb + lane, cb);
+        }
     }
 }
 
@@ -108,7 +295,7 @@ struct FwdSmem {
 // fprop / dgrad kernel
 // =============================================================================================
 template <int kBN, bool kBMN, int kEpi>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ ConvArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     using L = FwdSmem<kBN, kBMN>;
@@ -121,8 +308,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     uint64_t* empty_bar = full_bar + kMaxStages;
     uint64_t* acc_bar = empty_bar + kMaxStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
-    float* s_scale = reinterpret_cast<float*>(tmem_slot + 4);
-    float* s_shift = s_scale + p.Cin;
+    float* s_scale = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full_bar) + 96);  // 16-B aligned
+    float* s_shift = s_scale + ((p.Cin + 3) & ~3);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -132,245 +319,176 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     const int cblocks = (p.Cin + kBK - 1) / kBK;                 // dgrad: k-blocks per tap
     const int ktot = taps * p.Cin;                              // fprop: linearised K extent
     const int num_kb = kBMN ? taps * cblocks : (ktot + kBK - 1) / kBK;
-    const bool has_pro = p.pro_scale != nullptr;
+    const bool has_pro = p.pro_scale != nullptr || p.bn_sum != nullptr;
+    if (threadIdx.x == 0) IDCB_STAMP(0);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nstages; ++s) {
-            mbar_init(&full_bar[s], 4 + 1);  // 4 producer warps + the TMA thread
-            mbar_init(&empty_bar[s], 1);     // one tcgen05.commit
+            mbar_init(&full_bar[s], kFullArrivals);
+            mbar_init(&empty_bar[s], 1);  // one tcgen05.commit
         }
         mbar_init(acc_bar, 1);
         mbar_fence_init();
     }
-    if (warp == 4 && lane == 0) tma_prefetch_desc(&tmap_w);
-    if (warp == 5) tmem_alloc<kBN < 32 ? 32 : kBN>(tmem_slot);
-    if (has_pro)
+    if (warp == kTmaWarp && lane == 0) tma_prefetch_desc(&tmap_w);
+    if (warp == kMmaWarp) tmem_alloc<kBN < 32 ? 32 : kBN>(tmem_slot);
+    if (p.bn_sum != nullptr) {
+        const bool publish = blockIdx.x == 0 && blockIdx.y == 0;
+        const float inv = 1.f / p.bn_count;
+        for (int c = threadIdx.x; c < p.Cin; c += kThreads) {
+            const float mean = p.bn_sum[c] * inv;
+            const float var = fmaxf(p.bn_sq[c] * inv - mean * mean, 0.f);
+            const float rstd = rsqrtf(var + p.bn_eps);
+            const float sc = p.bn_gamma[c] * rstd;
+            const float sh = p.bn_beta[c] - mean * sc;
+            s_scale[c] = sc;
+            s_shift[c] = sh;
+            if (publish) {
+                p.bn_scale_out[c] = sc;
+                p.bn_shift_out[c] = sh;
+                p.bn_mean_out[c] = mean;
+                p.bn_rstd_out[c] = rstd;
+                if (p.bn_mmean != nullptr) {
+                    const float unbiased = p.bn_count > 1.f ? var * (p.bn_count / (p.bn_count - 1.f)) : var;
+                    p.bn_mmean[c] = p.bn_mmean[c] * p.bn_momentum + mean * (1.f - p.bn_momentum);
+                    p.bn_mvar[c] = p.bn_mvar[c] * p.bn_momentum + unbiased * (1.f - p.bn_momentum);
+                }
+            }
+        }
+    } else if (has_pro) {
         for (int c = threadIdx.x; c < p.Cin; c += kThreads) {
             s_scale[c] = p.pro_scale[c];
             s_shift[c] = p.pro_shift[c];
         }
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) IDCB_STAMP(1);
 
-    if (warp < 4) {
+    if (warp < 8) {
         // ===================== A producers =====================
         const int j = threadIdx.x & 7;       // 16-byte chunk inside the 128-byte row
-        const int rbase = threadIdx.x >> 3;  // 0..15
-        int hb[8], wb[8], ib[8];
+        const int rbase = threadIdx.x >> 3;  // 0..31
+        int hb[4], wb[4], roff[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const int m = m0 + i * 16 + rbase;
+        for (int i = 0; i < 4; ++i) {
+            const int m = m0 + i * 32 + rbase;
             if (m < p.M) {
-                const int hw = p.Ho * p.Wo;
-                const int b = m / hw;
-                const int rem = m - b * hw;
-                const int ho = rem / p.Wo;
+                const int b = fdiv(m, p.d_hw);
+                const int rem = m - b * (p.Ho * p.Wo);
+                const int ho = fdiv(rem, p.d_wo);
                 const int wo = rem - ho * p.Wo;
                 hb[i] = ho * p.stride - p.pad_t;
                 wb[i] = wo * p.stride - p.pad_l;
-                ib[i] = b * p.H * p.W;
+                roff[i] = ((b * p.H + hb[i]) * p.W + wb[i]) * p.x_pitch + p.x_coff;
             } else {
-                hb[i] = -100000;
-                wb[i] = -100000;
-                ib[i] = 0;
+                hb[i] = -(1 << 20);
+                wb[i] = -(1 << 20);
+                roff[i] = 0;
             }
         }
-        // issue the 8 row loads of k-block kb; returns the channel (or -1) and a validity mask
-        auto issue = [&](int kb, uint4 (&v)[8], uint32_t& okmask) -> int {
+        // issue the 4 row loads of k-block kb; returns the channel (or -1) and a validity mask
+        auto issue = [&](int kb, uint4 (&v)[4], uint32_t& okmask) -> int {
             int tap, c;
             if (kBMN) {
-                tap = kb / cblocks;
+                tap = fdiv(kb, p.d_cb);
                 c = (kb - tap * cblocks) * kBK + j * 8;
                 if (c >= p.Cin) c = -1;
             } else {
                 const int kidx = kb * kBK + j * 8;
                 if (kidx < ktot) {
-                    tap = kidx / p.Cin;
+                    tap = fdiv(kidx, p.d_cin);
                     c = kidx - tap * p.Cin;
                 } else {
                     tap = 0;
                     c = -1;
                 }
             }
-            const int kh = tap / p.KW;
+            const int kh = fdiv(tap, p.d_kw);
             const int kw = tap - kh * p.KW;
+            const int delta = (kh * p.W + kw) * p.x_pitch + c;
             okmask = 0;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int hi = hb[i] + kh;
-                const int wi = wb[i] + kw;
-                const bool ok = c >= 0 && hi >= 0 && hi < p.H && wi >= 0 && wi < p.W;
+            for (int i = 0; i < 4; ++i) {
+                const unsigned hi = static_cast<unsigned>(hb[i] + kh);
+                const unsigned wi = static_cast<unsigned>(wb[i] + kw);
+                const bool ok = c >= 0 && hi < static_cast<unsigned>(p.H) && wi < static_cast<unsigned>(p.W);
                 v[i] = make_uint4(0u, 0u, 0u, 0u);
                 if (ok) {
                     okmask |= 1u << i;
-                    const size_t off =
-                        (static_cast<size_t>(ib[i] + hi * p.W + wi)) * p.x_pitch + p.x_coff + c;
-                    v[i] = __ldg(reinterpret_cast<const uint4*>(p.x + off));
+                    v[i] = __ldg(reinterpret_cast<const uint4*>(p.x + (roff[i] + delta)));
                 }
             }
             return c;
         };
+        // register-resident software pipeline: kDepth k-blocks of global loads in flight per thread
+        constexpr int kDepth = 3;
         int stage = 0;
         uint32_t phase = 0;
-        uint4 v[8], vn[8];
-        uint32_t ok = 0, okn = 0;
-        int c = issue(0, v, ok), cn = -1;
-        for (int kb = 0; kb < num_kb; ++kb) {
-            if (kb + 1 < num_kb) cn = issue(kb + 1, vn, okn);
-            if (has_pro && c >= 0) {
-                float sc[8], sh[8];
+        uint4 v[kDepth][4];
+        uint32_t ok[kDepth];
+        int cch[kDepth];
 #pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    sc[e] = s_scale[c + e];
-                    sh[e] = s_shift[c + e];
+        for (int d = 0; d < kDepth; ++d) {
+            ok[d] = 0;
+            cch[d] = -1;
+            if (d < num_kb) cch[d] = issue(d, v[d], ok[d]);
+        }
+        for (int kb0 = 0; kb0 < num_kb; kb0 += kDepth) {
+#pragma unroll
+            for (int d = 0; d < kDepth; ++d) {
+                const int kb = kb0 + d;
+                if (kb < num_kb) {  // warp-uniform
+                    if (has_pro && ok[d] != 0) {
+                        const int c = cch[d];
+                        const float4 s0 = *reinterpret_cast<const float4*>(s_scale + c);
+                        const float4 s1 = *reinterpret_cast<const float4*>(s_scale + c + 4);
+                        const float4 h0 = *reinterpret_cast<const float4*>(s_shift + c);
+                        const float4 h1 = *reinterpret_cast<const float4*>(s_shift + c + 4);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (ok[d] & (1u << i)) transform8(v[d][i], s0, s1, h0, h1, p.pro_act);
+                    }
+                    if (threadIdx.x == 0 && kb == 0) IDCB_STAMP(2);
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* a_tile = a_tiles + stage * kATileBytes;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        *reinterpret_cast<uint4*>(a_tile + sw128_offset(i * 32 + rbase, j)) = v[d][i];
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&full_bar[stage]);
+                    if (++stage == nstages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                    if (kb + kDepth < num_kb) cch[d] = issue(kb + kDepth, v[d], ok[d]);
                 }
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    if (ok & (1u << i)) transform8(v[i], sc, sh, p.pro_act);
             }
-            mbar_wait(&empty_bar[stage], phase ^ 1);
-            uint8_t* a_tile = a_tiles + stage * kATileBytes;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int r = i * 16 + rbase;
-                *reinterpret_cast<uint4*>(a_tile + sw128_offset(r, j)) = v[i];
-            }
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&full_bar[stage]);
-            if (++stage == nstages) {
-                stage = 0;
-                phase ^= 1;
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = vn[i];
-            ok = okn;
-            c = cn;
         }
 
         // ===================== epilogue =====================
+        if (threadIdx.x == 0) IDCB_STAMP(3);
         mbar_wait(acc_bar, 0);
         tc_fence_after();
-        const int row = warp * 32 + lane;
-        const int m = m0 + row;
+        if (threadIdx.x == 0) IDCB_STAMP(6);
+        constexpr int kHalf = kBN / 2;               // columns per warp
+        constexpr int kW = kHalf >= 32 ? 32 : 16;    // slab width
+        const int quad = warp & 3;
+        const int half = warp >> 2;
+        const int m = m0 + quad * 32 + lane;
         const bool mvalid = m < p.M;
-        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
 #pragma unroll 1
-        for (int cc = 0; cc < kBN; cc += 32) {
+        for (int cc = half * kHalf; cc < (half + 1) * kHalf; cc += kW) {
             const int nb = n0 + cc;
-            if (nb >= p.Cout) break;  // uniform across the CTA
-            uint32_t raw[32];
-            tmem_ld_32x32b_x32(t_row + cc, raw);
-            tmem_ld_wait();
-            float vv[32];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) vv[e] = __uint_as_float(raw[e]);
-            float xr[32];  // mode 0: residual / mode 1: mask source / mode 2: raw x
-            const bool need_aux = (kEpi != 0) || (p.aux != nullptr);
-            if (need_aux) {
-#pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    uint4 q = make_uint4(0u, 0u, 0u, 0u);
-                    if (mvalid && nb + g * 8 < p.Cout)
-                        q = *reinterpret_cast<const uint4*>(
-                            p.aux + static_cast<size_t>(m) * p.aux_pitch + p.aux_coff + nb + g * 8);
-                    const uint32_t* w = reinterpret_cast<const uint32_t*>(&q);
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        float2 f = unpack_bf16x2(w[e]);
-                        xr[g * 8 + 2 * e] = f.x;
-                        xr[g * 8 + 2 * e + 1] = f.y;
-                    }
-                }
-            }
-            float sa[32], sb[32];
-            if (kEpi == 0) {
-#pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                    const int n = nb + e;
-                    float o = vv[e];
-                    if (n < p.Cout) {
-                        if (p.epi_scale) o *= p.epi_scale[n];
-                        if (p.epi_shift) o += p.epi_shift[n];
-                        o = apply_act(o, p.epi_act);
-                        if (need_aux) o += xr[e];
-                    } else {
-                        o = 0.f;
-                    }
-                    o = __bfloat162float(__float2bfloat16_rn(o));
-                    vv[e] = o;
-                    sa[e] = mvalid ? o : 0.f;
-                    sb[e] = mvalid ? o * o : 0.f;
-                }
-            } else if (kEpi == 1) {
-#pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                    float o = (nb + e < p.Cout && xr[e] > 0.f) ? vv[e] : 0.f;
-                    o = __bfloat162float(__float2bfloat16_rn(o));
-                    vv[e] = o;
-                    sa[e] = mvalid ? o : 0.f;
-                    sb[e] = 0.f;
-                }
-            } else {
-#pragma unroll
-                for (int e = 0; e < 32; ++e) {
-                    const int n = nb + e;
-                    float o = 0.f;
-                    float gs = 0.f;
-                    if (n < p.Cout) {
-                        gs = p.bwd_scale[n];
-                        const float pre = fmaf(gs, xr[e], p.bwd_shift[n]);
-                        o = vv[e] * act_mask(pre, p.bwd_act);
-                    }
-                    sa[e] = mvalid ? o : 0.f;
-                    sb[e] = mvalid ? o * xr[e] : 0.f;
-                    vv[e] = o;
-                    xr[e] = gs;  // reuse as the G scale
-                }
-            }
-            // ---- stores ----
-            if (mvalid && p.y != nullptr) {
-                __nv_bfloat16* yrow = p.y + static_cast<size_t>(m) * p.y_pitch + p.y_coff + nb;
-#pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    if (nb + g * 8 < p.Cout) {
-                        uint4 q;
-                        q.x = pack_bf16x2(vv[g * 8 + 0], vv[g * 8 + 1]);
-                        q.y = pack_bf16x2(vv[g * 8 + 2], vv[g * 8 + 3]);
-                        q.z = pack_bf16x2(vv[g * 8 + 4], vv[g * 8 + 5]);
-                        q.w = pack_bf16x2(vv[g * 8 + 6], vv[g * 8 + 7]);
-                        *reinterpret_cast<uint4*>(yrow + g * 8) = q;
-                    }
-                }
-            }
-            if (kEpi == 2 && mvalid && p.gacc != nullptr) {
-                float* grow = p.gacc + static_cast<size_t>(m) * p.g_pitch + p.g_coff + nb;
-#pragma unroll
-                for (int g = 0; g < 8; ++g) {
-                    if (nb + g * 4 < p.Cout) {
-                        float4 q = *reinterpret_cast<float4*>(grow + g * 4);
-                        q.x = fmaf(xr[g * 4 + 0], vv[g * 4 + 0], q.x);
-                        q.y = fmaf(xr[g * 4 + 1], vv[g * 4 + 1], q.y);
-                        q.z = fmaf(xr[g * 4 + 2], vv[g * 4 + 2], q.z);
-                        q.w = fmaf(xr[g * 4 + 3], vv[g * 4 + 3], q.w);
-                        *reinterpret_cast<float4*>(grow + g * 4) = q;
-                    }
-                }
-            }
-            // ---- column statistics (BatchNorm sums / bias gradient / BN-backward sums) ----
-            if (p.stat_a != nullptr) {
-                const float ca = warp_column_sums(sa, lane);
-                if (nb + lane < p.Cout) atomicAdd(p.stat_a + nb + lane, ca);
-                if (kEpi != 1 && p.stat_b != nullptr) {
-                    const float cb2 = warp_column_sums(sb, lane);
-                    if (nb + lane < p.Cout) atomicAdd(p.stat_b + nb + lane, cb2);
-                }
-            }
+            if (nb >= p.Cout) break;  // warp-uniform
+            epilogue_slab<kEpi, kW>(p, t_row + cc, m, mvalid, nb, lane);
         }
         tc_fence_before();
-    } else if (warp == 4) {
+    } else if (warp == kTmaWarp) {
         // ===================== TMA producer for the weight operand =====================
         if (lane == 0) {
             int stage = 0;
@@ -407,6 +525,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
+                if (kb == 0) IDCB_STAMP(4);
                 const uint32_t a_addr = smem_u32(a_tiles + stage * kATileBytes);
                 const uint32_t b_addr = smem_u32(b_tiles + stage * L::kBTileBytes);
 #pragma unroll
@@ -423,11 +542,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                 }
             }
             umma_commit(acc_bar);
+            IDCB_STAMP(5);
         }
         __syncwarp();
     }
+    if (threadIdx.x == 0) IDCB_STAMP(7);
     __syncthreads();
-    if (warp == 5) {
+    if (threadIdx.x == 0) IDCB_STAMP(8);
+    if (warp == kMmaWarp) {
         tc_fence_after();
         tmem_dealloc<kBN < 32 ? 32 : kBN>(tmem_base);
     }
@@ -444,6 +566,7 @@ struct WgradArgs {
     int B, H, W, Cin;
     int KH, KW, stride, pad_t, pad_l, Ho, Wo;
     int M, Cout;
+    FastDiv d_hw, d_wo, d_cin, d_kw;
     const float* pro_scale;
     const float* pro_shift;
     int pro_act;
@@ -454,7 +577,7 @@ struct WgradArgs {
 };
 
 template <int kBN>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ WgradArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     constexpr int kBTile = ((kBN + 63) / 64) * 8192;
@@ -482,118 +605,128 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nstages; ++s) {
-            mbar_init(&full_bar[s], 4 + 1);
+            mbar_init(&full_bar[s], kFullArrivals);
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(acc_bar, 1);
         mbar_fence_init();
     }
-    if (warp == 4 && lane == 0) tma_prefetch_desc(&tmap_dy);
-    if (warp == 5) tmem_alloc<kBN < 32 ? 32 : kBN>(tmem_slot);
+    if (warp == kTmaWarp && lane == 0) tma_prefetch_desc(&tmap_dy);
+    if (warp == kMmaWarp) tmem_alloc<kBN < 32 ? 32 : kBN>(tmem_slot);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     if (num_kb == 0) {  // uniform: nothing to do for this split
         __syncthreads();
-        if (warp == 5) tmem_dealloc<kBN < 32 ? 32 : kBN>(tmem_base);
+        if (warp == kMmaWarp) tmem_dealloc<kBN < 32 ? 32 : kBN>(tmem_base);
         return;
     }
 
-    if (warp < 4) {
+    if (warp < 8) {
         // ---- A producers: 16 threads cover one position row (128 k' = 256 B) ----
         const int j16 = threadIdx.x & 15;
         const int half = j16 >> 3;  // which 64-wide chunk
         const int j = j16 & 7;
-        const int rbase = threadIdx.x >> 4;  // 0..7
+        const int rbase = threadIdx.x >> 4;  // 0..15
         const int kidx = k0 + j16 * 8;
         const bool cvalid = kidx < ktot;
-        const int tap = cvalid ? kidx / p.Cin : 0;
+        const int tap = cvalid ? fdiv(kidx, p.d_cin) : 0;
         const int c = cvalid ? kidx - tap * p.Cin : 0;
-        const int kh = tap / p.KW;
+        const int kh = fdiv(tap, p.d_kw);
         const int kw = tap - kh * p.KW;
         const bool has_pro = p.pro_scale != nullptr;
-        float sc[8], sh[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            sc[e] = (has_pro && cvalid) ? p.pro_scale[c + e] : 1.f;
-            sh[e] = (has_pro && cvalid) ? p.pro_shift[c + e] : 0.f;
+        float4 s0 = make_float4(1.f, 1.f, 1.f, 1.f), s1 = s0;
+        float4 h0 = make_float4(0.f, 0.f, 0.f, 0.f), h1 = h0;
+        if (has_pro && cvalid) {
+            s0 = make_float4(p.pro_scale[c], p.pro_scale[c + 1], p.pro_scale[c + 2], p.pro_scale[c + 3]);
+            s1 = make_float4(p.pro_scale[c + 4], p.pro_scale[c + 5], p.pro_scale[c + 6], p.pro_scale[c + 7]);
+            h0 = make_float4(p.pro_shift[c], p.pro_shift[c + 1], p.pro_shift[c + 2], p.pro_shift[c + 3]);
+            h1 = make_float4(p.pro_shift[c + 4], p.pro_shift[c + 5], p.pro_shift[c + 6], p.pro_shift[c + 7]);
         }
-        const int hw = p.Ho * p.Wo;
-        auto issue = [&](int kb, uint4 (&v)[8], uint32_t& okmask) {
+        const int tap_off = (kh - p.pad_t) * p.W + (kw - p.pad_l);
+        auto issue = [&](int kb, uint4 (&v)[4], uint32_t& okmask) {
             okmask = 0;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int m = kb * 64 + i * 8 + rbase;
+            for (int i = 0; i < 4; ++i) {
+                const int m = kb * 64 + i * 16 + rbase;
                 v[i] = make_uint4(0u, 0u, 0u, 0u);
                 if (cvalid && m < p.M) {
-                    const int b = m / hw;
-                    const int rem = m - b * hw;
-                    const int ho = rem / p.Wo;
+                    const int b = fdiv(m, p.d_hw);
+                    const int rem = m - b * (p.Ho * p.Wo);
+                    const int ho = fdiv(rem, p.d_wo);
                     const int wo = rem - ho * p.Wo;
-                    const int hi = ho * p.stride - p.pad_t + kh;
-                    const int wi = wo * p.stride - p.pad_l + kw;
-                    if (hi >= 0 && hi < p.H && wi >= 0 && wi < p.W) {
+                    const unsigned hi = static_cast<unsigned>(ho * p.stride - p.pad_t + kh);
+                    const unsigned wi = static_cast<unsigned>(wo * p.stride - p.pad_l + kw);
+                    if (hi < static_cast<unsigned>(p.H) && wi < static_cast<unsigned>(p.W)) {
                         okmask |= 1u << i;
-                        const size_t off =
-                            (static_cast<size_t>((b * p.H + hi) * p.W + wi)) * p.x_pitch + p.x_coff + c;
+                        const int off = ((b * p.H + ho * p.stride) * p.W + wo * p.stride + tap_off) * p.x_pitch +
+                                        p.x_coff + c;
                         v[i] = __ldg(reinterpret_cast<const uint4*>(p.x + off));
                     }
                 }
             }
         };
+        constexpr int kDepth = 3;
         int stage = 0;
         uint32_t phase = 0;
-        uint4 v[8], vn[8];
-        uint32_t ok = 0, okn = 0;
-        issue(kb_begin, v, ok);
-        for (int kb = kb_begin; kb < kb_end; ++kb) {
-            if (kb + 1 < kb_end) issue(kb + 1, vn, okn);
-            if (has_pro) {
+        uint4 v[kDepth][4];
+        uint32_t ok[kDepth];
 #pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    if (ok & (1u << i)) transform8(v[i], sc, sh, p.pro_act);
-            }
-            mbar_wait(&empty_bar[stage], phase ^ 1);
-            uint8_t* a_tile = a_tiles + stage * kATileBytes + half * 8192;
+        for (int d = 0; d < kDepth; ++d) {
+            ok[d] = 0;
+            if (kb_begin + d < kb_end) issue(kb_begin + d, v[d], ok[d]);
+        }
+        for (int kb0 = kb_begin; kb0 < kb_end; kb0 += kDepth) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int r = i * 8 + rbase;
-                *reinterpret_cast<uint4*>(a_tile + sw128_offset(r, j)) = v[i];
-            }
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&full_bar[stage]);
-            if (++stage == nstages) {
-                stage = 0;
-                phase ^= 1;
-            }
+            for (int d = 0; d < kDepth; ++d) {
+                const int kb = kb0 + d;
+                if (kb < kb_end) {  // warp-uniform
+                    if (has_pro) {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = vn[i];
-            ok = okn;
+                        for (int i = 0; i < 4; ++i)
+                            if (ok[d] & (1u << i)) transform8(v[d][i], s0, s1, h0, h1, p.pro_act);
+                    }
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* a_tile = a_tiles + stage * kATileBytes + half * 8192;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        *reinterpret_cast<uint4*>(a_tile + sw128_offset(i * 16 + rbase, j)) = v[d][i];
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&full_bar[stage]);
+                    if (++stage == nstages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                    if (kb + kDepth < kb_end) issue(kb + kDepth, v[d], ok[d]);
+                }
+            }
         }
         // ---- epilogue: red.add the fp32 tile into dW ----
         mbar_wait(acc_bar, 0);
         tc_fence_after();
-        const int krow = k0 + warp * 32 + lane;
-        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+        constexpr int kHalf = kBN / 2;
+        constexpr int kW = kHalf >= 32 ? 32 : 16;
+        const int quad = warp & 3;
+        const int hf = warp >> 2;
+        const int krow = k0 + quad * 32 + lane;
+        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
 #pragma unroll 1
-        for (int cc = 0; cc < kBN; cc += 32) {
+        for (int cc = hf * kHalf; cc < (hf + 1) * kHalf; cc += kW) {
             if (n0 + cc >= p.Cout) break;
-            uint32_t raw[32];
-            tmem_ld_32x32b_x32(t_row + cc, raw);
-            tmem_ld_wait();
+            float vv[kW];
+            tmem_ld_cols<kW>(t_row + cc, vv);
             if (krow < ktot) {
 #pragma unroll
-                for (int e = 0; e < 32; ++e) {
+                for (int e = 0; e < kW; ++e) {
                     const int n = n0 + cc + e;
-                    if (n < p.Cout)
-                        atomicAdd(p.dw + static_cast<size_t>(n) * ktot + krow, __uint_as_float(raw[e]));
+                    if (n < p.Cout) atomicAdd(p.dw + static_cast<size_t>(n) * ktot + krow, vv[e]);
                 }
             }
         }
         tc_fence_before();
-    } else if (warp == 4) {
+    } else if (warp == kTmaWarp) {
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
@@ -637,7 +770,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         __syncwarp();
     }
     __syncthreads();
-    if (warp == 5) {
+    if (warp == kMmaWarp) {
         tc_fence_after();
         tmem_dealloc<kBN < 32 ? 32 : kBN>(tmem_base);
     }
@@ -646,12 +779,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 // ---------------------------------------------------------------------------------------------
 // Host launchers
 // ---------------------------------------------------------------------------------------------
-static int pick_stages(int num_kb, int stage_bytes, int extra_bytes) {
+static long long* g_dbg = nullptr;
+
+static int pick_stages(int num_kb) {
     int s = num_kb < kMaxStages ? num_kb : kMaxStages;
-    if (s < 1) s = 1;
-    // keep two CTAs resident per SM when the pipeline depth allows it (latency hiding across CTAs)
-    while (s > 2 && 2 * (1024 + s * stage_bytes + extra_bytes + 256) > 227 * 1024) --s;
-    return s;
+    return s < 1 ? 1 : s;
 }
 
 template <int kBN, bool kBMN, int kEpi>
@@ -659,10 +791,16 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     using L = FwdSmem<kBN, kBMN>;
     const int taps = a.KH * a.KW;
     const int num_kb = kBMN ? taps * ceil_div(a.Cin, kBK) : ceil_div(taps * a.Cin, kBK);
-    const int extra = (2 * kMaxStages + 1) * 8 + 16 + 2 * (int)sizeof(float) * a.Cin + 64;
-    a.stages = pick_stages(num_kb, L::kStageBytes, extra);
+    const int extra = 96 + 2 * (int)sizeof(float) * (a.Cin + 4) + 64;
+    a.stages = pick_stages(num_kb);
     const size_t smem = 1024 + a.stages * L::kStageBytes + extra;
     IDCB_REQUIRE(smem <= 227 * 1024, "conv: Cin=%d needs %zu bytes of shared memory", a.Cin, smem);
+    IDCB_REQUIRE(1LL * a.B * a.H * a.W * a.x_pitch < (1LL << 31), "conv: input tensor too large for 32-bit offsets");
+    a.d_hw = make_fdiv(a.Ho * a.Wo);
+    a.d_wo = make_fdiv(a.Wo);
+    a.d_cin = make_fdiv(a.Cin);
+    a.d_kw = make_fdiv(a.KW);
+    a.d_cb = make_fdiv(ceil_div(a.Cin, kBK));
     auto kern = conv_gemm_kernel<kBN, kBMN, kEpi>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -671,6 +809,7 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
         attr_set = true;
     }
     dim3 grid(ceil_div(a.M, kBM), ceil_div(a.Cout, kBN), 1);
+    a.dbg = g_dbg;
     kern<<<grid, kThreads, smem, st>>>(tm, a);
     IDCB_LAUNCH_CHECK();
     return 0;
@@ -680,8 +819,13 @@ template <int kBN>
 static int launch_wgrad(const CUtensorMap& tm, WgradArgs& a, cudaStream_t st) {
     constexpr int kBTile = ((kBN + 63) / 64) * 8192;
     const int extra = (2 * kMaxStages + 1) * 8 + 16 + 64;
-    a.stages = pick_stages(a.kb_per_split, kATileBytes + kBTile, extra);
+    a.stages = pick_stages(a.kb_per_split);
     const size_t smem = 1024 + a.stages * (kATileBytes + kBTile) + extra;
+    IDCB_REQUIRE(1LL * a.B * a.H * a.W * a.x_pitch < (1LL << 31), "conv: input tensor too large for 32-bit offsets");
+    a.d_hw = make_fdiv(a.Ho * a.Wo);
+    a.d_wo = make_fdiv(a.Wo);
+    a.d_cin = make_fdiv(a.Cin);
+    a.d_kw = make_fdiv(a.KW);
     auto kern = conv_wgrad_kernel<kBN>;
     static bool attr_set = false;
     if (!attr_set) {
@@ -713,6 +857,13 @@ static int check_geom(const idcb_conv_desc* d) {
 
 using namespace idcb;
 
+// profiling aid: when set (device pointer to >= 16 int64), CTA (0,0) of fprop/dgrad kernels records
+// clock64() at its phase boundaries
+extern "C" int idcb_conv_set_debug(void* dev_ptr) {
+    g_dbg = static_cast<long long*>(dev_ptr);
+    return 0;
+}
+
 extern "C" int idcb_conv_fprop(const idcb_conv_desc* d, const void* x, const void* w, void* y,
                                const idcb_conv_fused* f, void* stream) {
     if (check_geom(d)) return 1;
@@ -738,6 +889,20 @@ extern "C" int idcb_conv_fprop(const idcb_conv_desc* d, const void* x, const voi
         a.stat_a = f->stat_a; a.stat_b = f->stat_b;
         IDCB_REQUIRE((a.pro_scale == nullptr) == (a.pro_shift == nullptr),
                      "conv_fprop: prologue scale and shift must be given together");
+        if (f->bn != nullptr) {
+            const idcb_bn_inline* b = f->bn;
+            IDCB_REQUIRE(a.pro_scale == nullptr, "conv_fprop: give either pro_scale/shift or bn, not both");
+            IDCB_REQUIRE(b->sum && b->sq && b->gamma && b->beta && b->scale_out && b->shift_out &&
+                             b->mean_out && b->rstd_out && b->count > 0.f,
+                         "conv_fprop: incomplete inline BatchNorm description");
+            IDCB_REQUIRE((b->moving_mean == nullptr) == (b->moving_var == nullptr),
+                         "conv_fprop: moving mean/var go together");
+            a.bn_sum = b->sum; a.bn_sq = b->sq; a.bn_gamma = b->gamma; a.bn_beta = b->beta;
+            a.bn_count = b->count; a.bn_eps = b->eps; a.bn_momentum = b->momentum;
+            a.bn_scale_out = b->scale_out; a.bn_shift_out = b->shift_out;
+            a.bn_mean_out = b->mean_out; a.bn_rstd_out = b->rstd_out;
+            a.bn_mmean = b->moving_mean; a.bn_mvar = b->moving_var;
+        }
     }
     CUtensorMap tm;
     const int kbn = d->cout <= 32 ? 32 : (d->cout <= 64 ? 64 : 128);
@@ -822,7 +987,7 @@ extern "C" int idcb_conv_wgrad(const idcb_conv_desc* d, const void* x, const voi
     const int kbn = d->cout <= 32 ? 32 : (d->cout <= 64 ? 64 : 128);
     const int total_kb = ceil_div(a.M, 64);
     const int base_ctas = ceil_div(a.KH * a.KW * a.Cin, 128) * ceil_div(a.Cout, kbn);
-    int splits = ceil_div(2 * num_sms(), base_ctas);
+    int splits = ceil_div(num_sms(), base_ctas);
     if (splits > total_kb) splits = total_kb;
     if (splits < 1) splits = 1;
     a.kb_per_split = ceil_div(total_kb, splits);

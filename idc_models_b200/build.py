@@ -79,7 +79,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path:
     if jobs:
         with cf.ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(_run, jobs))
-    if jobs or not CUDA_LIB.exists():
+    if jobs or not CUDA_LIB.exists() or any(o.stat().st_mtime > CUDA_LIB.stat().st_mtime for o in objs):
         _run([nvcc, "-shared", "-o", str(CUDA_LIB), *map(str, objs), "-cudart", "static",
               "-gencode", "arch=compute_100a,code=sm_100a"])
     return CUDA_LIB

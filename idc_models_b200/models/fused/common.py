@@ -56,6 +56,7 @@ class FusedExecutor:
         self.version = 0          # bumped whenever weights may have changed outside the optimizer
         self.first_trainable = None
         self.use_graphs = False
+        self.capturing = False
         self._graphs: dict = {}
 
     # ---- trainable bookkeeping -----------------------------------------------------------------
@@ -107,19 +108,25 @@ class FusedExecutor:
             plan.labels.zero_()
 
     def _execute(self, plan, training: bool, grad_scale: float) -> None:
-        key = (id(plan), training, grad_scale)
+        # frozen-layer BatchNorm folds are baked into a captured graph, so the key carries the
+        # external-write counter of the weights
+        key = (id(plan), training, grad_scale, self.net.store.ext_version)
         if self.use_graphs:
             g = self._graphs.get(key)
             if g is None:
-                # warm-up run (also JITs nothing: our kernels are precompiled), then capture
+                # warm-up run (module loading, function attributes), then capture
                 self.run(plan, training, grad_scale)
                 if training:
                     self.net.store.grad.zero_()
                 torch.cuda.synchronize()
                 g = torch.cuda.CUDAGraph()
                 n0 = _lib.launches()
-                with torch.cuda.graph(g):
-                    self.run(plan, training, grad_scale)
+                self.capturing = True
+                try:
+                    with torch.cuda.graph(g):
+                        self.run(plan, training, grad_scale)
+                finally:
+                    self.capturing = False
                 self._graphs[key] = (g, _lib.launches() - n0)
                 if training:
                     self.net.store.grad.zero_()
@@ -160,6 +167,8 @@ class BNState:
 
     def __init__(self, ex: FusedExecutor, name: str, channels: int, scratch: Scratch, need_bwd: bool):
         dev = ex.net.device
+        self.ex = ex
+        self._folded_at = None
         self.name = name
         self.c = channels
         sp = ex.net.get_layer(name).spec
@@ -193,10 +202,17 @@ class BNState:
         return self.scratch.view(self.o_sb, self.c)
 
     def fold(self) -> None:
-        """inference mode: scale/shift from the moving statistics"""
+        """inference mode: scale/shift from the moving statistics. Cached: a frozen layer only changes
+        when weights are written from outside the optimizer, a trainable one after every update."""
+        st = self.ex.net.store
+        key = st.version if self.trainable else st.ext_version
+        if self._folded_at == ("fold", key) and not (self.ex.capturing and self.trainable):
+            return
         K.bn_fold(self.gamma, self.beta, self.mmean, self.mvar, self.eps, self.scale, self.shift)
+        self._folded_at = ("fold", key)
 
     def finalize(self, sum_, sq, count: float) -> None:
         """training mode: scale/shift from batch sums; updates the moving statistics"""
         K.bn_finalize(sum_, sq, count, self.gamma, self.beta, self.eps, self.scale, self.shift,
                       self.mean, self.rstd, self.mmean, self.mvar, self.momentum)
+        self._folded_at = None

@@ -145,6 +145,17 @@ class DenseNetExecutor(FusedExecutor):
         else:
             bn.fold()
 
+    def _bn_prologue(self, bn: BNState, training: bool, sum_, sq, count) -> dict:
+        """kwargs for conv_fprop_raw that make ``bn`` (+ activation) the conv's operand prologue.
+        Training-mode BatchNorm is finalised INSIDE the conv kernel from the batch sums (no extra
+        launch); frozen / inference BatchNorm is folded from the moving statistics."""
+        if training and bn.trainable:
+            bn._folded_at = None
+            return {"bn": OC.bn_inline(sum_, sq, bn.gamma, bn.beta, count, bn.eps, bn.momentum, bn.scale,
+                                       bn.shift, bn.mean, bn.rstd, bn.mmean, bn.mvar)}
+        bn.fold()
+        return {"pro_scale": bn.scale, "pro_shift": bn.shift}
+
     def run(self, p, training: bool, grad_scale: float) -> None:
         net = self.net
         sc = p.scratch
@@ -166,26 +177,26 @@ class DenseNetExecutor(FusedExecutor):
         for bi, blk in enumerate(p.blocks):
             bsum, bsq = sc.view(blk.o_sum, blk.ctot), sc.view(blk.o_sq, blk.ctot)
             for dl in blk.layers:
-                self._bn_forward(dl.bn0, training, bsum, bsq, blk.count)
                 s1, q1 = sc.view(dl.o_sum1, 128), sc.view(dl.o_sq1, 128)
                 OC.conv_fprop_raw(dl.g1, blk.buf, self.w16(dl.name + "_1_conv/kernel"), dl.y1,
-                                  pro_scale=dl.bn0.scale, pro_shift=dl.bn0.shift, pro_act=ACT_RELU,
-                                  stat_sum=s1 if stats else None, stat_sq=q1 if stats else None)
-                self._bn_forward(dl.bn1, training, s1, q1, blk.count)
+                                  pro_act=ACT_RELU, stat_sum=s1 if stats else None,
+                                  stat_sq=q1 if stats else None,
+                                  **self._bn_prologue(dl.bn0, training, bsum, bsq, blk.count))
                 OC.conv_fprop_raw(dl.g2, dl.y1, self.w16(dl.name + "_2_conv/kernel"), blk.buf, y_coff=dl.cin,
-                                  pro_scale=dl.bn1.scale, pro_shift=dl.bn1.shift, pro_act=ACT_RELU,
+                                  pro_act=ACT_RELU,
                                   stat_sum=bsum[dl.cin:dl.cin + GROWTH] if stats else None,
-                                  stat_sq=bsq[dl.cin:dl.cin + GROWTH] if stats else None)
-            self._bn_forward(blk.bn_t, training, bsum, bsq, blk.count)
+                                  stat_sq=bsq[dl.cin:dl.cin + GROWTH] if stats else None,
+                                  **self._bn_prologue(dl.bn1, training, s1, q1, blk.count))
             if bi + 1 < len(p.blocks):
                 nxt = p.blocks[bi + 1]
-                OC.conv_fprop_raw(blk.gt, blk.buf, self.w16(blk.tconv), blk.t, pro_scale=blk.bn_t.scale,
-                                  pro_shift=blk.bn_t.shift, pro_act=ACT_RELU)
+                OC.conv_fprop_raw(blk.gt, blk.buf, self.w16(blk.tconv), blk.t, pro_act=ACT_RELU,
+                                  **self._bn_prologue(blk.bn_t, training, bsum, bsq, blk.count))
                 K.pool_fwd(blk.t, nxt.buf, nxt.c0, 2, 2, 0, False)
                 if stats:
                     K.channel_stats(nxt.buf, nxt.c0, sc.view(nxt.o_sum, nxt.c0), sc.view(nxt.o_sq, nxt.c0))
         # ---- head (final BN + ReLU folded into the pooling read) --------------------------------------
         lb = p.blocks[-1]
+        self._bn_forward(lb.bn_t, training, sc.view(lb.o_sum, lb.ctot), sc.view(lb.o_sq, lb.ctot), lb.count)
         hl = p.head_layer
         wname, bname = hl.spec.params[0].name, hl.spec.params[1].name
         head_train = training and hl.index in self.trainable
@@ -222,10 +233,8 @@ class DenseNetExecutor(FusedExecutor):
         s1 = sc.view(blk.o_s1, blk.ctot)[c_lo:c_lo + c_n]
         s2 = sc.view(blk.o_s2, blk.ctot)[c_lo:c_lo + c_n]
         bn = blk.bn_t
-        K.bn_shared_coeffs(s1, s2, bn.mean[c_lo:c_lo + c_n], bn.rstd[c_lo:c_lo + c_n], blk.count,
-                           blk.cA[c_lo:c_lo + c_n], blk.cB[c_lo:c_lo + c_n], blk.cC[c_lo:c_lo + c_n])
-        K.affine2(blk.G, blk.buf, out, c_n, blk.cA[c_lo:c_lo + c_n], blk.cB[c_lo:c_lo + c_n],
-                  blk.cC[c_lo:c_lo + c_n], g_coff=c_lo, x_coff=c_lo)
+        K.bn_bwd_apply(2, blk.G, blk.buf, out, c_n, blk.count, sa=s1, sb=s2, mean=bn.mean[c_lo:c_lo + c_n],
+                       rstd=bn.rstd[c_lo:c_lo + c_n], g_coff=c_lo, x_coff=c_lo)
 
     def _backward(self, p) -> None:
         ft = self.first_trainable
@@ -276,12 +285,9 @@ class DenseNetExecutor(FusedExecutor):
                         K.bn_bwd_coeffs(bn1.sa, bn1.sb, bn1.mean, bn1.rstd, bn1.scale, blk.count,
                                         dgamma=bn1.dgamma, dbeta=bn1.dbeta)
                     continue
-                if bn1.trainable:
-                    K.bn_bwd_coeffs(bn1.sa, bn1.sb, bn1.mean, bn1.rstd, bn1.scale, blk.count,
-                                    dgamma=bn1.dgamma, dbeta=bn1.dbeta, A=blk.c1A, B=blk.c1B, C0=blk.c1C)
-                else:
-                    blk.c1A.copy_(bn1.scale); blk.c1B.zero_(); blk.c1C.zero_()
-                K.affine2(blk.dpre1, dl.y1, blk.dy1, 4 * GROWTH, blk.c1A, blk.c1B, blk.c1C)
+                K.bn_bwd_apply(0 if bn1.trainable else 1, blk.dpre1, dl.y1, blk.dy1, 4 * GROWTH, blk.count,
+                               sa=bn1.sa, sb=bn1.sb, mean=bn1.mean, rstd=bn1.rstd, scale=bn1.scale,
+                               dgamma=bn1.dgamma, dbeta=bn1.dbeta)
                 w1 = dl.name + "_1_conv/kernel"
                 bn0 = dl.bn0
                 if dl.i_c1 in tr:
@@ -306,10 +312,7 @@ class DenseNetExecutor(FusedExecutor):
                 K.bn_bwd_coeffs(bn.sa, bn.sb, bn.mean, bn.rstd, bn.scale, float(p.s0.numel() // 64),
                                 dgamma=bn.dgamma, dbeta=bn.dbeta)
             return
-        if bn.trainable:
-            K.bn_bwd_coeffs(bn.sa, bn.sb, bn.mean, bn.rstd, bn.scale, float(p.s0.numel() // 64),
-                            dgamma=bn.dgamma, dbeta=bn.dbeta, A=p.cA, B=p.cB, C0=p.cC)
-        else:
-            p.cA.copy_(bn.scale); p.cB.zero_(); p.cC.zero_()
-        K.affine2(p.dpre_stem, p.s0, p.ds0, 64, p.cA, p.cB, p.cC)
+        K.bn_bwd_apply(0 if bn.trainable else 1, p.dpre_stem, p.s0, p.ds0, 64, float(p.s0.numel() // 64),
+                       sa=bn.sa, sb=bn.sb, mean=bn.mean, rstd=bn.rstd, scale=bn.scale,
+                       dgamma=bn.dgamma, dbeta=bn.dbeta)
         OC.conv_wgrad_raw(p.g_stem, p.x16, p.ds0, self.gw("conv1/conv/kernel"))

@@ -207,17 +207,18 @@ class MobileNetV2Executor(FusedExecutor):
 
     # -------------------------------------------------------------------------------------------------
     def _bn_bwd(self, bn: BNState, count: float, coefs, need_dx: bool) -> None:
-        """sa/sb of ``bn`` are filled: emit parameter gradients and (optionally) the dx coefficients."""
-        A, B, C0 = coefs
-        if bn.trainable:
-            if need_dx:
-                K.bn_bwd_coeffs(bn.sa, bn.sb, bn.mean, bn.rstd, bn.scale, count, dgamma=bn.dgamma,
-                                dbeta=bn.dbeta, A=A, B=B, C0=C0)
-            else:
-                K.bn_bwd_coeffs(bn.sa, bn.sb, bn.mean, bn.rstd, bn.scale, count, dgamma=bn.dgamma,
-                                dbeta=bn.dbeta)
-        elif need_dx:
-            A.copy_(bn.scale); B.zero_(); C0.zero_()
+        """sa/sb of ``bn`` are filled. If the input gradient is needed, the parameter gradients are
+        emitted by the fused apply kernel that follows (:meth:`_bn_apply`); otherwise only dgamma/dbeta."""
+        if need_dx:
+            self._pending = (bn, count)
+        elif bn.trainable:
+            K.bn_bwd_coeffs(bn.sa, bn.sb, bn.mean, bn.rstd, bn.scale, count, dgamma=bn.dgamma,
+                            dbeta=bn.dbeta)
+
+    def _bn_apply(self, g, x, out, channels) -> None:
+        bn, count = self._pending
+        K.bn_bwd_apply(0 if bn.trainable else 1, g, x, out, channels, count, sa=bn.sa, sb=bn.sb,
+                       mean=bn.mean, rstd=bn.rstd, scale=bn.scale, dgamma=bn.dgamma, dbeta=bn.dbeta)
 
     def _backward(self, p) -> None:
         ft, tr = self.first_trainable, self.trainable
@@ -227,7 +228,7 @@ class MobileNetV2Executor(FusedExecutor):
         self._bn_bwd(p.bn_c, self._cnt(p.c_raw), p.c_c, need)
         if not need:
             return
-        K.affine2(p.dpre_c, p.c_raw, p.dc_raw, 1280, *p.c_c)
+        self._bn_apply(p.dpre_c, p.c_raw, p.dc_raw, 1280)
         if p.i_c in tr:
             OC.conv_wgrad_raw(p.gc, last.out, p.dc_raw, self.gw("Conv_1/kernel"))
         if not last.bwd:
@@ -250,7 +251,7 @@ class MobileNetV2Executor(FusedExecutor):
                     prev.dout.copy_(b.dout)
                     continue
                 return
-            K.affine2(b.dout, b.p_raw, b.dp_raw, b.cout, *b.c_p)
+            self._bn_apply(b.dout, b.p_raw, b.dp_raw, b.cout)
             if b.i_p in tr:
                 OC.conv_wgrad_raw(b.gp, b.d_raw, b.dp_raw, self.gw(b.prefix + "project/kernel"),
                                   pro_scale=b.bn_d.scale, pro_shift=b.bn_d.shift, pro_act=ACT_RELU6)
@@ -263,7 +264,7 @@ class MobileNetV2Executor(FusedExecutor):
                 self._bn_bwd(b.bn_d, self._cnt(b.d_raw), b.c_d, need)
                 stop = not need
             if not stop:
-                K.affine2(b.dpre_d, b.d_raw, b.dd_raw, b.cexp, *b.c_d)
+                self._bn_apply(b.dpre_d, b.d_raw, b.dd_raw, b.cexp)
                 dw_in, dw_bn = (b.e_raw, b.bn_e) if b.has_expand else (p.s_raw, p.bn_stem)
                 if b.i_d in tr:
                     K.dwconv_wgrad(b.gd, dw_in, b.dd_raw, self.gw(b.prefix + "depthwise/depthwise_kernel"),
@@ -278,7 +279,7 @@ class MobileNetV2Executor(FusedExecutor):
                         need = ft <= b.i_e
                         self._bn_bwd(b.bn_e, self._cnt(b.e_raw), b.c_e, need)
                         if need:
-                            K.affine2(b.dpre_e, b.e_raw, b.de_raw, b.cexp, *b.c_e)
+                            self._bn_apply(b.dpre_e, b.e_raw, b.de_raw, b.cexp)
                             if b.i_e in tr:
                                 OC.conv_wgrad_raw(b.ge, xin, b.de_raw, self.gw(b.prefix + "expand/kernel"))
                             if prev is not None and prev.bwd:
@@ -290,7 +291,7 @@ class MobileNetV2Executor(FusedExecutor):
                         need = ft <= p.i_stem
                         self._bn_bwd(p.bn_stem, self._cnt(p.s_raw), p.c_stem, need)
                         if need:
-                            K.affine2(p.dpre_stem, p.s_raw, p.ds_raw, 32, *p.c_stem)
+                            self._bn_apply(p.dpre_stem, p.s_raw, p.ds_raw, 32)
                             OC.conv_wgrad_raw(p.g_stem, p.x16, p.ds_raw, self.gw("Conv1/kernel"))
                         return
             # the main branch stopped inside this block; only a residual can carry gradient on

@@ -108,7 +108,20 @@ class ParamStore:
     def shadow_view(self, name: str) -> torch.Tensor:
         return self.storage_view(name, "shadow")
 
+    # Change counters let executors cache values derived from weights (folded BatchNorm scale/shift):
+    # ``version`` moves on every update, ``ext_version`` only when weights are written from outside the
+    # optimizer (set_weights / load / broadcast / federated averaging), i.e. when frozen layers may change.
+    version = 0
+    ext_version = 0
+
+    def touch(self, external: bool = False) -> None:
+        self.version += 1
+        if external:
+            self.ext_version += 1
+
     def refresh_shadow(self) -> None:
+        """Call after writing the master weights from outside the optimizer."""
+        self.touch(external=True)
         if self.shadow is not None:
             self.shadow.copy_(self.master)
 

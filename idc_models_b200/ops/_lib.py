@@ -32,7 +32,16 @@ class ConvFused(C.Structure):
         ("pro_scale", vp), ("pro_shift", vp), ("pro_act", C.c_int),
         ("epi_scale", vp), ("epi_shift", vp), ("epi_act", C.c_int),
         ("aux", vp), ("aux_pitch", C.c_int), ("aux_coff", C.c_int),
-        ("stat_a", vp), ("stat_b", vp),
+        ("stat_a", vp), ("stat_b", vp), ("bn", vp),
+    ]
+
+
+class BnInline(C.Structure):
+    _fields_ = [
+        ("sum", vp), ("sq", vp), ("gamma", vp), ("beta", vp),
+        ("count", C.c_float), ("eps", C.c_float), ("momentum", C.c_float),
+        ("scale_out", vp), ("shift_out", vp), ("mean_out", vp), ("rstd_out", vp),
+        ("moving_mean", vp), ("moving_var", vp),
     ]
 
 

@@ -80,7 +80,7 @@ def _chk(t: torch.Tensor, dtype, name: str) -> None:
 def conv_fprop_raw(g: ConvGeom, x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, *, x_coff: int = 0,
                    y_coff: int = 0, pro_scale=None, pro_shift=None, pro_act: int = ACT_NONE,
                    epi_scale=None, epi_shift=None, epi_act: int = ACT_NONE, residual=None,
-                   res_coff: int = 0, stat_sum=None, stat_sq=None) -> None:
+                   res_coff: int = 0, stat_sum=None, stat_sq=None, bn=None) -> None:
     """y[..., y_coff:y_coff+cout] = epi(conv(pro(x[..., x_coff:x_coff+cin]), w)) on the GPU."""
     _chk(x, torch.bfloat16, "x"); _chk(w, torch.bfloat16, "w"); _chk(y, torch.bfloat16, "y")
     for t, n in ((pro_scale, "pro_scale"), (pro_shift, "pro_shift"), (epi_scale, "epi_scale"),
@@ -92,7 +92,8 @@ def conv_fprop_raw(g: ConvGeom, x: torch.Tensor, w: torch.Tensor, y: torch.Tenso
     f = _lib.ConvFused(_lib.ptr(pro_scale), _lib.ptr(pro_shift), pro_act, _lib.ptr(epi_scale),
                        _lib.ptr(epi_shift), epi_act, _lib.ptr(residual),
                        residual.shape[-1] if residual is not None else 0, res_coff,
-                       _lib.ptr(stat_sum), _lib.ptr(stat_sq))
+                       _lib.ptr(stat_sum), _lib.ptr(stat_sq),
+                       C.cast(C.pointer(bn), C.c_void_p) if bn is not None else C.c_void_p(0))
     lib = _lib.cuda_lib()
     _lib.check(lib.idcb_conv_fprop(C.byref(d), _lib.ptr(x), _lib.ptr(w), _lib.ptr(y), C.byref(f),
                                    _lib.stream()))
@@ -130,6 +131,15 @@ def conv_wgrad_raw(g: ConvGeom, x: torch.Tensor, dy: torch.Tensor, dw: torch.Ten
     _lib.check(lib.idcb_conv_wgrad(C.byref(d), _lib.ptr(x), _lib.ptr(dy), _lib.ptr(dw),
                                    _lib.ptr(pro_scale), _lib.ptr(pro_shift), pro_act, _lib.stream()))
     _lib.count_launch()
+
+
+def bn_inline(sum_, sq, gamma, beta, count, eps, momentum, scale_out, shift_out, mean_out, rstd_out,
+              moving_mean=None, moving_var=None) -> _lib.BnInline:
+    """Description of a training-mode BatchNorm to be finalised inside the consuming conv kernel."""
+    p = _lib.ptr
+    return _lib.BnInline(p(sum_), p(sq), p(gamma), p(beta), float(count), float(eps), float(momentum),
+                         p(scale_out), p(shift_out), p(mean_out), p(rstd_out), p(moving_mean),
+                         p(moving_var))
 
 
 # ---------------------------------------------------------------------------------------------

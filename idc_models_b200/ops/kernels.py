@@ -88,6 +88,17 @@ def affine2(g, x, out, channels, A, B, C0, g_coff=0, x_coff=0, o_coff=0):
           C.c_int(channels))
 
 
+def bn_bwd_apply(mode, g, x, out, channels, count, *, sa=None, sb=None, mean=None, rstd=None, scale=None,
+                 dgamma=None, dbeta=None, g_coff=0, x_coff=0, o_coff=0):
+    """BatchNorm backward in one launch (see include/idcb200.h): mode 0 training BN, 1 frozen BN,
+    2 DenseNet shared-buffer slice (sa=S1, sb=S2)."""
+    _call(_lib.cuda_lib().idcb_bn_bwd_apply, C.c_int(mode), _p(g),
+          C.c_int(1 if g.dtype == torch.float32 else 0), C.c_int(g.shape[-1]), C.c_int(g_coff), _p(x),
+          C.c_int(x.shape[-1]), C.c_int(x_coff), _p(out), C.c_int(out.shape[-1]), C.c_int(o_coff), _p(sa),
+          _p(sb), _p(mean), _p(rstd), _p(scale), C.c_float(count), _p(dgamma), _p(dbeta),
+          C.c_longlong(_rows(x)), C.c_int(channels))
+
+
 def channel_stats(x, channels, sum_, sq, coff=0):
     _call(_lib.cuda_lib().idcb_channel_stats, _p(x), C.c_int(x.shape[-1]), C.c_int(coff),
           C.c_longlong(_rows(x)), C.c_int(channels), _p(sum_), _p(sq))

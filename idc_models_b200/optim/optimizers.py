@@ -64,6 +64,8 @@ class Optimizer:
         """w <- update(w, grad_scale * g) over the bound trainable ranges."""
         st = self.store
         self.iterations += 1
+        if hasattr(st, "touch"):
+            st.touch()
         lr = self._step_lr()
         p1, p2, eps = self._params()
         for b, e in (ranges if ranges is not None else self.ranges):

@@ -49,6 +49,24 @@ typedef struct idcb_conv_desc {
  *   a   = pro_act(pro_scale[c] * x + pro_shift[c])          (BatchNorm + ReLU folded into the load)
  *   y   = epi_act(epi_scale[n] * acc + epi_shift[n]) + aux  (bias / frozen BN / ReLU / residual)
  *   stat_a[n] += sum_p y,  stat_b[n] += sum_p y^2           (batch statistics for the next BN)   */
+/* Training-mode BatchNorm folded into the conv that consumes it: the kernel turns the per-channel
+ * batch sums (accumulated by the producer's epilogue) into scale/shift itself, so no separate
+ * finalisation launch is needed; CTA (0,0) publishes scale/shift/mean/rstd for the backward pass and
+ * applies the Keras moving-statistics update (momentum convention, unbiased variance). */
+typedef struct idcb_bn_inline {
+    const float* sum;
+    const float* sq;
+    const float* gamma;
+    const float* beta;
+    float count, eps, momentum;
+    float* scale_out;
+    float* shift_out;
+    float* mean_out;
+    float* rstd_out;
+    float* moving_mean;          /* optional (NULL = do not touch) */
+    float* moving_var;
+} idcb_bn_inline;
+
 typedef struct idcb_conv_fused {
     const float* pro_scale;
     const float* pro_shift;
@@ -60,6 +78,7 @@ typedef struct idcb_conv_fused {
     int aux_pitch, aux_coff;
     float* stat_a;
     float* stat_b;
+    const idcb_bn_inline* bn;    /* optional: prologue = BatchNorm(batch statistics) + pro_act */
 } idcb_conv_fused;
 
 /* Fused epilogue of dgrad.
@@ -134,6 +153,14 @@ int idcb_affine_act(const void* x, int x_pitch, int x_coff, void* y, int y_pitch
 int idcb_affine2(const void* g, int g_is_float, int g_pitch, int g_coff, const void* x, int x_pitch,
                  int x_coff, void* out, int o_pitch, int o_coff, const float* A, const float* B,
                  const float* C0, long long M, int C, void* stream);
+/* bn_bwd_coeffs / bn_shared_coeffs + affine2 in ONE launch (coefficients derived per thread):
+ *   mode 0: training BN backward  out = scale*(g - sa/N - xhat*dgamma/N), emits dgamma += , dbeta +=
+ *   mode 1: frozen BN backward    out = scale*g
+ *   mode 2: DenseNet shared slice out = g - S1/N - xhat*S2/N   (sa = S1, sb = S2)              */
+int idcb_bn_bwd_apply(int mode, const void* g, int g_is_float, int g_pitch, int g_coff, const void* x,
+                      int x_pitch, int x_coff, void* out, int o_pitch, int o_coff, const float* sa,
+                      const float* sb, const float* mean, const float* rstd, const float* scale,
+                      float count, float* dgamma, float* dbeta, long long M, int C, void* stream);
 int idcb_channel_stats(const void* x, int pitch, int coff, long long M, int C, float* sum, float* sq,
                        void* stream);
 /* sum_g[c] += sum_p g, sum_gx[c] += sum_p g*x — BN backward sums for a dpre that is already in memory */
