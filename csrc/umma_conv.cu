@@ -390,24 +390,33 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             }
         }
         // issue the 4 row loads of k-block kb; returns the channel (or -1) and a validity mask
+        // (tap, channel) cursor of this thread's 16-byte chunk; issue() is called with kb = 0, 1, 2, ...
+        // so the cursor advances incrementally (no per-k-block divisions on the critical path)
+        int cur_c, cur_kh, cur_kw;
+        {
+            const int tap0 = kBMN ? 0 : static_cast<int>(fdiv(j * 8, p.d_cin));
+            cur_c = j * 8 - tap0 * p.Cin;
+            cur_kh = fdiv(tap0, p.d_kw);
+            cur_kw = tap0 - cur_kh * p.KW;
+        }
         auto issue = [&](int kb, uint4 (&v)[4], uint32_t& okmask) -> int {
-            int tap, c;
+            (void)kb;
+            const int kh = cur_kh, kw = cur_kw;
+            int c = (cur_kh < p.KH && cur_c < p.Cin) ? cur_c : -1;
+            // advance the cursor by one k-block
+            cur_c += kBK;
             if (kBMN) {
-                tap = fdiv(kb, p.d_cb);
-                c = (kb - tap * cblocks) * kBK + j * 8;
-                if (c >= p.Cin) c = -1;
+                // dgrad walks whole 64-wide blocks per tap (the tail block of a tap is zero padded)
+                if (cur_c >= cblocks * kBK) {
+                    cur_c -= cblocks * kBK;
+                    if (++cur_kw == p.KW) { cur_kw = 0; ++cur_kh; }
+                }
             } else {
-                const int kidx = kb * kBK + j * 8;
-                if (kidx < ktot) {
-                    tap = fdiv(kidx, p.d_cin);
-                    c = kidx - tap * p.Cin;
-                } else {
-                    tap = 0;
-                    c = -1;
+                while (cur_c >= p.Cin) {
+                    cur_c -= p.Cin;
+                    if (++cur_kw == p.KW) { cur_kw = 0; ++cur_kh; }
                 }
             }
-            const int kh = fdiv(tap, p.d_kw);
-            const int kw = tap - kh * p.KW;
             const int delta = (kh * p.W + kw) * p.x_pitch + c;
             okmask = 0;
 #pragma unroll
@@ -781,6 +790,17 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 // ---------------------------------------------------------------------------------------------
 static long long* g_dbg = nullptr;
 
+// N-tile width: the widest tile that still leaves enough CTAs to spread a small problem over the chip
+// (a 128-row x 128-column tile of a tiny layer would otherwise run its whole MMA chain on one SM).
+static int pick_bn(int M, int N) {
+    if (N <= 32) return 32;
+    const int mt = ceil_div(M, kBM);
+    const int target = num_sms() / 2;
+    if (N > 64 && mt * ceil_div(N, 128) >= target) return 128;
+    if (mt * ceil_div(N, 64) >= target) return 64;
+    return N <= 64 && mt * 1 >= target ? 64 : 32;
+}
+
 static int pick_stages(int num_kb) {
     int s = num_kb < kMaxStages ? num_kb : kMaxStages;
     return s < 1 ? 1 : s;
@@ -889,7 +909,7 @@ extern "C" int idcb_conv_fprop(const idcb_conv_desc* d, const void* x, const voi
         a.stat_a = f->stat_a; a.stat_b = f->stat_b;
         IDCB_REQUIRE((a.pro_scale == nullptr) == (a.pro_shift == nullptr),
                      "conv_fprop: prologue scale and shift must be given together");
-        if (f->bn != nullptr) {
+        if (f->bn != nullptr) {  // training-mode BatchNorm finalised in-kernel
             const idcb_bn_inline* b = f->bn;
             IDCB_REQUIRE(a.pro_scale == nullptr, "conv_fprop: give either pro_scale/shift or bn, not both");
             IDCB_REQUIRE(b->sum && b->sq && b->gamma && b->beta && b->scale_out && b->shift_out &&
@@ -905,7 +925,7 @@ extern "C" int idcb_conv_fprop(const idcb_conv_desc* d, const void* x, const voi
         }
     }
     CUtensorMap tm;
-    const int kbn = d->cout <= 32 ? 32 : (d->cout <= 64 ? 64 : 128);
+    const int kbn = pick_bn(a.M, d->cout);
     if (make_tmap_2d_bf16(&tm, w, d->cout, (uint64_t)d->kh * d->kw * d->cin,
                           (uint64_t)d->kh * d->kw * d->cin, kbn, 64))
         return 1;
@@ -952,11 +972,16 @@ extern "C" int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const vo
     }
     IDCB_REQUIRE(a.y != nullptr || a.gacc != nullptr, "conv_dgrad: no output given");
     CUtensorMap tm;
-    const int kbn = d->cin <= 64 ? 64 : 128;
+    const int kbn = pick_bn(a.M, d->cin);
     // weight view [Cout rows][taps*Cin cols]; MN-major boxes are 64 cols x 64 rows
     if (make_tmap_2d_bf16(&tm, w, d->cout, (uint64_t)d->kh * d->kw * d->cin,
                           (uint64_t)d->kh * d->kw * d->cin, 64, 64))
         return 1;
+    if (kbn == 32) {
+        if (mode == 0) return launch_gemm<32, true, 0>(tm, a, st);
+        if (mode == 1) return launch_gemm<32, true, 1>(tm, a, st);
+        return launch_gemm<32, true, 2>(tm, a, st);
+    }
     if (kbn == 64) {
         if (mode == 0) return launch_gemm<64, true, 0>(tm, a, st);
         if (mode == 1) return launch_gemm<64, true, 1>(tm, a, st);
