@@ -44,7 +44,7 @@ class Dataset:
 
     @staticmethod
     def from_tensor_slices(tensors) -> "Dataset":
-        if isinstance(tensors, (tuple, list)):
+        if isinstance(tensors, tuple):
             n = len(tensors[0])
             return Dataset(lambda: (tuple(t[i] for t in tensors) for i in range(n)), n)
         n = len(tensors)

@@ -1,0 +1,70 @@
+"""Integration on CPU, 2 replicas over gloo: north-star config #1 (MobileNetV2, synthetic IDC patches, global
+batch 32): replicas stay bit-identical and the 2-replica loss equals the single-replica loss on the same
+global batch (SURVEY.md section 4 "Integration, CPU 2 replicas")."""
+import os
+import socket
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+WORKER = r'''
+import os, sys, json, torch
+sys.path.insert(0, %r)
+from idc_models_b200.models.applications import build_transfer_model
+from idc_models_b200.optim.optimizers import RMSprop
+from idc_models_b200.parallel.strategy import MirroredStrategy, CentralStorageStrategy
+from idc_models_b200.parallel.world import World
+kind = sys.argv[1]
+world = World.from_env("cpu")
+strategy = (CentralStorageStrategy if kind == "central" else MirroredStrategy)(world=world)
+with strategy.scope():
+    m = build_transfer_model("mobilenet_v2", device="cpu", seed=world.rank)   # different seeds: sync must fix it
+    # frozen base (phase 1 of the transfer scripts): BatchNorm runs on moving statistics, so the result
+    # must not depend on how the global batch is split (trainable BN uses per-replica batch statistics
+    # by design, like MirroredStrategy)
+    m.compile(optimizer=RMSprop(lr=1e-3), loss="bce", metrics=["accuracy"])
+g = torch.Generator().manual_seed(0)
+x = torch.rand(32, 50, 50, 3, generator=g); y = (torch.rand(32, generator=g) > 0.5).float()
+h = m.fit([(x, y)] * 2, epochs=1, verbose=0)
+chk = float(m.store.master.double().sum())
+outs = world.all_gather_object((chk, h.history["loss"][0], strategy.num_replicas_in_sync))
+if world.rank == 0:
+    print("RESULT " + json.dumps(outs))
+world.shutdown()
+''' % str(ROOT)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _run(kind, nproc):
+    script = ROOT / "build" / "_dist_worker.py"
+    script.parent.mkdir(exist_ok=True)
+    script.write_text(WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script), kind]
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    import json
+    line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1]
+    return json.loads(line[len("RESULT "):])
+
+
+@pytest.mark.parametrize("kind", ["mirrored", "central"])
+def test_two_cpu_replicas_stay_identical_and_match_single_replica(kind):
+    two = _run(kind, 2)
+    one = _run(kind, 1)
+    assert two[0][2] == 2 and one[0][2] == 1
+    assert two[0][0] == two[1][0], "replica weight checksums differ"
+    assert abs(two[0][1] - one[0][1]) < 5e-4, f"2-replica loss {two[0][1]} vs single-replica {one[0][1]}"
+    assert abs(two[0][0] - one[0][0]) < 1e-3 * max(1.0, abs(one[0][0]))
