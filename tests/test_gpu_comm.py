@@ -61,7 +61,7 @@ def test_fedavg_reduce_matches_weighted_delta_mean():
     for r in range(world):
         c = torch.randn(k_local, n, device="cuda")
         if r == 1:
-            c[2, 100] = float("inf")            # this client must be dropped
+            c[2, 300] = float("inf")            # this client must be dropped
         wts = torch.tensor([3000., 1000., 2500.], device="cuda") * (r + 1)
         clients[r].tensor.copy_(c.reshape(-1))
         weights[r].tensor[:k_local].copy_(wts)

@@ -19,7 +19,7 @@ WORKER = r'''
 import sys, json, torch
 sys.path.insert(0, %r)
 from idc_models_b200.models.applications import build_transfer_model
-from idc_models_b200.optim.optimizers import RMSprop
+from idc_models_b200.optim.optimizers import SGD
 from idc_models_b200.parallel.strategy import MirroredStrategy
 from idc_models_b200.parallel.world import World
 world = World.from_env()
@@ -29,7 +29,7 @@ for comm in ("nccl", "fused"):
     with strategy.scope():
         m = build_transfer_model("densenet_tiny", device=world.device, seed=0)
         m.base.trainable = True
-        m.compile(optimizer=RMSprop(lr=1e-3), loss="bce", metrics=["accuracy"])
+        m.compile(optimizer=SGD(learning_rate=1e-2), loss="bce", metrics=["accuracy"])   # linear in g: tight check
     g = torch.Generator().manual_seed(0)
     gb = 32 * world.size
     x = torch.rand(gb, 50, 50, 3, generator=g).to(world.device); y = (torch.rand(gb, generator=g) > 0.5).float().to(world.device)
@@ -66,4 +66,5 @@ def test_fused_allreduce_matches_nccl_path_across_processes():
     for o in outs:
         assert o["fused"][:2] == outs[0]["fused"][:2], "fused replicas are not bit-identical"
         # NCCL ring order vs owner-computes order differ in fp32 rounding only
-        assert abs(o["fused"][0] - o["nccl"][0]) < 1e-3 * max(1.0, abs(o["nccl"][1])) * 1e-2
+        assert abs(o["fused"][0] - o["nccl"][0]) < 1e-4 * max(1.0, abs(o["nccl"][1]))
+    print("multicast (NVLS) used by the fused path:", outs[0]["fused"][2])
