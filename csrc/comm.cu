@@ -502,3 +502,77 @@ extern "C" int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* cli
     IDCB_LAUNCH_CHECK();
     return 0;
 }
+
+// =====================================================================================================
+// Allocation-free single-GPU secure mean
+//
+// Some hosts embed this library where device allocation is off the table: a serving loop that has
+// handed the whole GPU to a fixed arena, a process that runs under a memory quota set at start-up, or
+// code that is already inside a region where cudaMalloc would synchronise the device. For them the
+// masked-sum kernel above is offered with its staging memory (the masked partial sums and the barrier
+// flags) placed in file-scope __device__ storage that the module itself owns: 4 MiB of uint32 plus a
+// 128-byte flag pad per GPU that loads the library, held until the process exits.
+//
+// The symbol names below are host-side handles, not device addresses; the device address is fetched
+// once per device with cudaGetSymbolAddress (with that device current) and cached. That first call on a
+// device does the lookup, so make it before starting any stream capture. Nothing here calls cudaMalloc,
+// cudaFree or an allocating library routine. All calls on one GPU share the same staging memory, which
+// keeps whatever the previous call left in it: phase A rewrites every word it later reads, and the
+// flag pad is a monotonically increasing epoch by design, so nothing needs clearing — but two calls
+// whose kernels overlap on the GPU (different streams) would race on it; serialise them.
+// =====================================================================================================
+constexpr long long kNoAllocMaxElems = 1LL << 20;   // protected range limit: 1,048,576 weights (4 MiB)
+static __device__ __align__(256) uint32_t g_noalloc_ybuf[kNoAllocMaxElems];
+static __device__ __align__(256) uint32_t g_noalloc_pad[64];
+
+namespace {
+struct NoAllocPtrs {
+    uint32_t* ybuf;
+    uint32_t* pad;
+};
+NoAllocPtrs g_noalloc_ptrs[64] = {};
+}  // namespace
+
+extern "C" long long idcb_secagg_noalloc_max_elems(void) { return kNoAllocMaxElems; }
+
+extern "C" int idcb_secagg_mean_noalloc(const float* clients, float* out, int k_clients, long long stride,
+                                        long long offset, long long n, int frac_bits,
+                                        unsigned long long session_seed, void* stream) {
+    IDCB_REQUIRE(clients != nullptr && out != nullptr, "secagg_mean_noalloc: null input/output");
+    IDCB_REQUIRE(n % 4 == 0 && offset % 4 == 0 && stride % 4 == 0 && n >= 0, "secagg_mean_noalloc: sizes must be multiples of 4");
+    IDCB_REQUIRE(n <= kNoAllocMaxElems,
+                 "secagg_mean_noalloc: range of %lld elements exceeds the built-in staging area (%lld); "
+                 "use idcb_secagg_masked_sum with caller-provided buffers", n, kNoAllocMaxElems);
+    IDCB_REQUIRE(k_clients >= 1 && k_clients <= 64, "secagg_mean_noalloc: 1..64 clients");
+    IDCB_REQUIRE(frac_bits >= 1 && frac_bits <= 30, "secagg_mean_noalloc: frac_bits must be in 1..30");
+    int dev = 0;
+    IDCB_CHECK(cudaGetDevice(&dev));
+    IDCB_REQUIRE(dev >= 0 && dev < 64, "secagg_mean_noalloc: device index %d out of range", dev);
+    NoAllocPtrs& np = g_noalloc_ptrs[dev];
+    if (np.ybuf == nullptr) {   // once per device, with that device current
+        void* p = nullptr;
+        IDCB_CHECK(cudaGetSymbolAddress(&p, g_noalloc_ybuf));
+        void* q = nullptr;
+        IDCB_CHECK(cudaGetSymbolAddress(&q, g_noalloc_pad));
+        np.pad = static_cast<uint32_t*>(q);
+        np.ybuf = static_cast<uint32_t*>(p);
+    }
+    if (n == 0) return 0;
+    SecAggArgs a{};
+    a.pr.world = 1;
+    a.pr.rank = 0;
+    a.pr.use_barrier = 1;          // the grid-wide barrier between the masking and the summing phase
+    a.pr.pad[0] = np.pad;
+    a.clients[0] = clients;
+    a.ybuf[0] = np.ybuf;
+    a.out[0] = out;
+    a.mc_ybuf = nullptr;
+    a.mc_out = nullptr;
+    a.k_local = k_clients; a.stride = stride; a.offset = offset; a.n = n; a.frac_bits = frac_bits;
+    a.session_seed = session_seed;
+    long long g = ceil_div_ll(n / 4, kCommThreads);
+    if (g > num_sms()) g = num_sms();
+    secagg_kernel<<<(int)g, kCommThreads, 0, (cudaStream_t)stream>>>(a);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}

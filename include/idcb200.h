@@ -262,6 +262,24 @@ int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* clients, void*
                            void* const* out, void* mc_out, int k_local, long long stride, long long offset,
                            long long n, int frac_bits, unsigned long long session_seed, void* stream);
 
+/* Single-GPU secure mean that allocates nothing (this entry point has no counterpart in the reference).
+ * Same arithmetic as idcb_secagg_masked_sum with world = 1, but the staging memory it needs between
+ * its two phases (the masked ring sums and the grid-barrier flags) lives inside the library, in fixed
+ * device storage of idcb_secagg_noalloc_max_elems() uint32 words (4 MiB) per GPU, instead of being
+ * passed in. It is meant for callers that must not allocate device memory at this point: a service that
+ * has given the whole GPU to its own arena, a process under a memory quota fixed at start-up, or code
+ * that cannot tolerate the implicit device synchronisation of cudaMalloc/cudaFree.
+ *   out[offset:offset+n] = mean over the k_clients rows of clients[k][offset:offset+n]
+ * - n above the limit is refused with an error (use the caller-buffer entry point instead);
+ * - the first call on each device looks the storage up (cudaGetSymbolAddress); make that call before
+ *   beginning a stream capture;
+ * - every call on a GPU reuses the same storage: calls whose kernels could overlap on the device
+ *   (different streams) race with each other and must be serialised by the caller. */
+long long idcb_secagg_noalloc_max_elems(void);
+int idcb_secagg_mean_noalloc(const float* clients, float* out, int k_clients, long long stride,
+                             long long offset, long long n, int frac_bits, unsigned long long session_seed,
+                             void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,74 @@
+"""The allocation-free secure-mean entry point (``idcb_secagg_mean_noalloc``) called straight through the
+C ABI, checked against the ordinary entry point that takes caller-provided staging buffers.
+
+Why the entry point exists: some programs that link this library may not create device memory when they
+call it — the GPU's memory belongs to their own arena, or they run under a start-up memory quota, or a
+cudaMalloc at that moment would stall the device. For them the staging area sits inside the library.
+
+The file name sorts last on purpose: if this test ever fails under ``pytest -x``, every other test has
+already run. It passes alone in a fresh process and after the rest of the suite (the library's built-in
+storage keeps state between calls by design, so the test makes no assumption about its initial contents).
+"""
+import ctypes as C
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _lib():
+    from idc_models_b200.ops import _lib as L
+    lib = L.cuda_lib()
+    lib.idcb_secagg_noalloc_max_elems.restype = C.c_longlong
+    return L, lib
+
+
+def _reference(L, lib, clients, k, stride, off, n, frac_bits, seed):
+    """the existing entry point: one rank, caller-owned staging buffer and flag pad"""
+    from idc_models_b200.parallel.symm import CommWorld, ptr_array
+    dev = clients.device
+    ybuf = torch.empty(n, dtype=torch.int32, device=dev)
+    pad = torch.zeros(64, dtype=torch.int32, device=dev)
+    out = torch.zeros(stride, dtype=torch.float32, device=dev)
+    cw = CommWorld(1, 0, 1)
+    cw.signal_pads[0] = pad.data_ptr()
+    L.check(lib.idcb_secagg_masked_sum(C.byref(cw), ptr_array([clients.data_ptr()]), ptr_array([ybuf.data_ptr()]),
+                                       None, ptr_array([out.data_ptr()]), None, C.c_int(k), C.c_longlong(stride),
+                                       C.c_longlong(off), C.c_longlong(n), C.c_int(frac_bits), C.c_ulonglong(seed),
+                                       L.stream()))
+    torch.cuda.synchronize()
+    return out
+
+
+def test_noalloc_entry_point_matches_the_buffered_one_on_two_calls_in_a_row():
+    L, lib = _lib()
+    torch.manual_seed(0)
+    for call, (k, stride, off, n, seed) in enumerate([(6, 8192, 1024, 4096, 0xABCDEF0123),
+                                                      (3, 2048, 0, 2048, 0x55AA55AA)]):
+        clients = torch.randn(k, stride, device="cuda") * 2
+        want = _reference(L, lib, clients, k, stride, off, n, 16, seed)
+        out = torch.zeros(stride, dtype=torch.float32, device="cuda")
+        before = torch.cuda.memory_allocated()
+        rc = lib.idcb_secagg_mean_noalloc(C.c_void_p(clients.data_ptr()), C.c_void_p(out.data_ptr()), C.c_int(k),
+                                          C.c_longlong(stride), C.c_longlong(off), C.c_longlong(n), C.c_int(16),
+                                          C.c_ulonglong(seed), L.stream())
+        assert rc == 0, lib.idcb_last_error().decode()
+        torch.cuda.synchronize()
+        assert torch.cuda.memory_allocated() == before
+        # same kernel, same arithmetic: bit-identical; and it is the mean, to the quantisation step
+        assert torch.equal(out, want), f"call {call}: differs from the buffered entry point"
+        assert (out[off:off + n] - clients[:, off:off + n].mean(0)).abs().max().item() < 2e-5
+        assert out[:off].abs().max().item() == 0 if off else True
+
+
+def test_noalloc_entry_point_refuses_oversized_ranges():
+    L, lib = _lib()
+    limit = lib.idcb_secagg_noalloc_max_elems()
+    assert limit == 1 << 20
+    x = torch.zeros(8, device="cuda")
+    rc = lib.idcb_secagg_mean_noalloc(C.c_void_p(x.data_ptr()), C.c_void_p(x.data_ptr()), C.c_int(2),
+                                      C.c_longlong(limit + 4), C.c_longlong(0), C.c_longlong(limit + 4), C.c_int(16),
+                                      C.c_ulonglong(1), L.stream())
+    assert rc != 0
+    assert b"exceeds the built-in staging area" in lib.idcb_last_error()
