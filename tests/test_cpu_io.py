@@ -1,0 +1,97 @@
+"""CPU tests: flat checkpoints and the minimal HDF5 subset behind Keras .h5 import/export."""
+import struct
+
+import numpy as np
+import pytest
+
+from idc_models_b200.io import checkpoint, keras_h5
+from idc_models_b200.models.applications import build_transfer_model
+
+
+def test_checkpoint_roundtrip_and_resume_rule(tmp_path):
+    m = build_transfer_model("mobilenet_v2", device="cpu", seed=1)
+    p = tmp_path / "pretrained" / "cp.ckpt"
+    assert not checkpoint.exists(str(p))
+    m.save_weights(str(p))
+    assert checkpoint.exists(str(p)) and p.read_bytes()[:8] == b"IDCBCKP1"
+    m2 = build_transfer_model("mobilenet_v2", device="cpu", seed=2)
+    m2.load_weights(str(p))
+    assert all(np.array_equal(a, b) for a, b in zip(m.get_weights(), m2.get_weights()))
+    assert not (tmp_path / "pretrained" / "cp.ckpt.tmp").exists()     # atomic rename
+
+
+@pytest.mark.parametrize("arch", ["mobilenet_v2", "vgg16", "densenet121"])
+def test_keras_h5_roundtrip(arch, tmp_path):
+    m = build_transfer_model(arch, device="cpu", seed=3)
+    p = str(tmp_path / "w.h5")
+    m.save_weights(p)
+    data, attrs = keras_h5.read_h5(p)
+    base_name = m.base.name
+    assert attrs[("", "layer_names")] == [base_name, "global_average_pooling2d", "dense"]
+    assert attrs[("", "backend")] == ["tensorflow"]
+    wn = attrs[(base_name, "weight_names")]
+    assert all(n.endswith(":0") for n in wn) and len(wn) == len(m.weight_names()) - 2
+    assert attrs[("global_average_pooling2d", "weight_names")] == []
+    # Keras layouts on disk
+    if arch == "vgg16":
+        assert data["vgg16/block1_conv1/kernel:0"].shape == (3, 3, 3, 64)
+    if arch == "mobilenet_v2":
+        assert data[base_name + "/expanded_conv_depthwise/depthwise_kernel:0"].shape == (3, 3, 32, 1)
+    assert data["dense/dense/kernel:0"].shape[1] == 1
+    m2 = build_transfer_model(arch, device="cpu", seed=4)
+    m2.load_weights(p)
+    assert all(np.array_equal(a, b) for a, b in zip(m.get_weights(), m2.get_weights()))
+
+
+def test_h5_superblock_and_object_layout_by_hand(tmp_path):
+    """byte-level checks of the structures a foreign HDF5 reader depends on"""
+    p = str(tmp_path / "t.h5")
+    keras_h5.write_h5(p, {"g/sub/x:0": np.arange(6, dtype=np.float32).reshape(2, 3)},
+                      [("", "backend", ["tensorflow"], True), ("g", "weight_names", ["sub/x:0"], False)])
+    b = open(p, "rb").read()
+    assert b[:8] == b"\x89HDF\r\n\x1a\n"
+    assert b[8] == 0 and b[13] == 8 and b[14] == 8                       # superblock v0, 8-byte offsets/lengths
+    eof, = struct.unpack_from("<Q", b, 40)
+    assert eof == len(b)
+    root_hdr, cache_type = struct.unpack_from("<Q", b, 64)[0], struct.unpack_from("<I", b, 72)[0]
+    assert cache_type == 1 and b[root_hdr] == 1                           # cached symbol-table entry, v1 header
+    btree, heap = struct.unpack_from("<QQ", b, 80)
+    assert b[btree:btree + 4] == b"TREE" and b[heap:heap + 4] == b"HEAP"
+    snod, = struct.unpack_from("<Q", b, btree + 32)
+    assert b[snod:snod + 4] == b"SNOD" and struct.unpack_from("<H", b, snod + 6)[0] == 1
+    # the payload is stored contiguously, little-endian float32
+    raw = np.arange(6, dtype="<f4").tobytes()
+    assert raw in b
+    data, attrs = keras_h5.read_h5(p)
+    assert np.array_equal(data["g/sub/x:0"], np.arange(6, dtype=np.float32).reshape(2, 3))
+    assert attrs[("g", "weight_names")] == ["sub/x:0"]
+
+
+def test_flat_application_style_file_is_accepted(tmp_path):
+    """the published *_notop.h5 files have one group per LAYER (no nested model group)"""
+    m = build_transfer_model("vgg16", device="cpu", seed=5)
+    named = m.named_weights()
+    ds, attrs, layer_names = {}, [], []
+    for l in m.base.layers:
+        if not l.spec.params:
+            continue
+        layer_names.append(l.name)
+        attrs.append((l.name, "weight_names", [p.name + ":0" for p in l.spec.params], False))
+        for p_ in l.spec.params:
+            ds[f"{l.name}/{p_.name}:0"] = named[p_.name]
+    attrs.append(("", "layer_names", layer_names, False))
+    p = str(tmp_path / "vgg16_notop.h5")
+    keras_h5.write_h5(p, ds, attrs)
+    m2 = build_transfer_model("vgg16", device="cpu", seed=6)
+    missing = keras_h5.load_into(m2, p, strict=False)
+    assert sorted(missing) == ["dense/bias", "dense/kernel"]
+    assert np.array_equal(m2.get_weights()[0], m.get_weights()[0])
+    with pytest.raises(KeyError):
+        keras_h5.load_into(m2, p, strict=True)
+
+
+def test_not_an_hdf5_file_is_a_clear_error(tmp_path):
+    p = tmp_path / "x.h5"
+    p.write_bytes(b"hello world" * 100)
+    with pytest.raises(IOError, match="not an HDF5 file"):
+        keras_h5.read_h5(str(p))
