@@ -183,21 +183,39 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(Allreduce
     long long lo, hi;
     shard_bounds(a.n >> 2, pr.world, pr.rank, lo, hi);
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi;
-         i += (long long)gridDim.x * blockDim.x) {
+    // kU independent 16-byte reductions in flight per thread: the NVLink round trip (~2-4 us through
+    // the switch) is hidden by memory-level parallelism, not by occupancy
+    constexpr int kU = 4;
+    const long long tstride = (long long)gridDim.x * blockDim.x;
+    for (long long i0 = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < hi; i0 += tstride * kU) {
+      float4 gg[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = i0 + u * tstride;
+        gg[u] = zero;
+        if (i >= hi) continue;
         const long long e = i << 2;
-        float4 g;
         if (a.mc_grad != nullptr) {
-            g = mc_ld_reduce_f4(a.mc_grad + e);
-            mc_st_f4(a.mc_grad + e, zero);   // this shard of every rank's bucket is consumed: re-zero it
+            gg[u] = mc_ld_reduce_f4(a.mc_grad + e);
         } else {
-            g = zero;
             for (int q = 0; q < pr.world; ++q) {
                 const int p = (pr.rank + q) % pr.world;   // stagger peers so ranks do not gang up on one
                 const float4 v = ld_sys_f4(a.grad[p] + e);
-                g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
-                st_sys_f4(a.grad[p] + e, zero);
+                gg[u].x += v.x; gg[u].y += v.y; gg[u].z += v.z; gg[u].w += v.w;
             }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long i = i0 + u * tstride;
+        if (i >= hi) continue;
+        const long long e = i << 2;
+        float4 g = gg[u];
+        // this shard of every rank's bucket is consumed: re-zero it everywhere
+        if (a.mc_grad != nullptr) {
+            mc_st_f4(a.mc_grad + e, zero);
+        } else {
+            for (int q = 0; q < pr.world; ++q) st_sys_f4(a.grad[(pr.rank + q) % pr.world] + e, zero);
         }
         g.x *= a.grad_scale; g.y *= a.grad_scale; g.z *= a.grad_scale; g.w *= a.grad_scale;
         float4 w = *reinterpret_cast<const float4*>(a.master[pr.rank] + e);
@@ -220,6 +238,7 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(Allreduce
                 if (a.shadow[p]) st_sys_u2(a.shadow[p] + e, wb);
             }
         }
+      }
     }
     // every rank must have received all shards (and had its bucket re-zeroed) before anyone goes on
     grid_and_world_barrier(pr, e0 + 2);
