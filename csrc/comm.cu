@@ -159,7 +159,17 @@ struct AllreduceOptArgs {
     long long n;                        // elements in the range (multiple of 4)
     int kind;
     float lr, p1, p2, eps, grad_scale;
+    int owner;                          // -1: every rank owns 1/N (mirrored); r: rank r owns everything
+                                        //     (central storage: reduce-to-owner + broadcast)
+    const float* scal[kMaxWorld];       // optional: per-rank 4-float slots (loss sum, correct, count, -)
+    float* scal_out;                    //           their sum over ranks, piggy-backed on the barrier (8.3)
 };
+
+__device__ __forceinline__ float ld_sys_f32(const float* p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
 
 __device__ __forceinline__ float opt_step(int kind, float w, float g, float& s1, float& s2,
                                           float lr, float p1, float p2, float eps) {
@@ -182,6 +192,15 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(Allreduce
     grid_and_world_barrier(pr, e0 + 1);
     long long lo, hi;
     shard_bounds(a.n >> 2, pr.world, pr.rank, lo, hi);
+    if (a.owner >= 0) {
+        lo = 0;
+        hi = pr.rank == a.owner ? (a.n >> 2) : 0;
+    }
+    if (a.scal_out != nullptr && blockIdx.x == 0 && threadIdx.x < 4) {
+        float t = 0.f;
+        for (int p = 0; p < pr.world; ++p) t += ld_sys_f32(a.scal[p] + threadIdx.x);
+        a.scal_out[threadIdx.x] = t;
+    }
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
     // kU independent 16-byte reductions in flight per thread: the NVLink round trip (~2-4 us through
     // the switch) is hidden by memory-level parallelism, not by occupancy
@@ -434,9 +453,15 @@ using namespace idcb;
 extern "C" int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad, void* const* master,
                                     void* const* shadow, void* mc_grad, void* mc_master, void* mc_shadow,
                                     float* s1, float* s2, long long n, int kind, float lr, float p1, float p2,
-                                    float eps, float grad_scale, void* stream) {
+                                    float eps, float grad_scale, int owner, void* const* scal, float* scal_out,
+                                    void* stream) {
     AllreduceOptArgs a{};
     if (fill_peers(a.pr, w)) return 1;
+    IDCB_REQUIRE(owner >= -1 && owner < w->world, "allreduce_optim: bad owner rank %d", owner);
+    IDCB_REQUIRE((scal == nullptr) == (scal_out == nullptr), "allreduce_optim: scalar slots and output go together");
+    a.owner = owner;
+    a.scal_out = scal_out;
+    for (int p = 0; p < w->world && scal != nullptr; ++p) a.scal[p] = static_cast<const float*>(scal[p]);
     IDCB_REQUIRE(n % 4 == 0, "allreduce_optim: range length must be a multiple of 4");
     IDCB_REQUIRE(kind >= 0 && kind <= 2, "allreduce_optim: unknown optimizer kind %d", kind);
     for (int p = 0; p < w->world; ++p) {

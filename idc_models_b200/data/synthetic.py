@@ -76,3 +76,33 @@ def synthetic_batch(batch: int, image_shape=(50, 50, 3), n_classes: int = 2, see
     if str(device) != "cpu":
         x, y = x.to(device), y.to(device)
     return x, y
+
+
+class DeviceSyntheticIDC:
+    """An endless-epoch iterable of synthetic IDC batches generated ON the GPU by a Philox kernel
+    (csrc/small_cnn.cu:synth_patches_kernel): no host pipeline, no H2D copy. Every rank that
+    uses the same ``seed`` produces the same global batches, so data-parallel replicas can slice them."""
+
+    def __init__(self, steps_per_epoch: int, batch_size: int, image_shape=(50, 50, 3), seed: int = 0, device="cuda"):
+        self.steps, self.batch, self.shape, self.seed = steps_per_epoch, batch_size, tuple(image_shape), seed
+        self.device = torch.device(device)
+        self._epoch = 0
+
+    def __len__(self):
+        return self.steps
+
+    def __iter__(self):
+        import ctypes as C
+        from ..ops import _lib
+        lib = _lib.cuda_lib()
+        h, w, c = self.shape
+        base = self._epoch * self.steps
+        self._epoch += 1
+        for i in range(self.steps):
+            x = torch.empty(self.batch, h, w, c, dtype=torch.float32, device=self.device)
+            y = torch.empty(self.batch, dtype=torch.float32, device=self.device)
+            _lib.check(lib.idcb_synth_patches(C.c_void_p(x.data_ptr()), C.c_void_p(y.data_ptr()), C.c_longlong(self.batch),
+                                              C.c_int(h), C.c_int(w), C.c_int(c), C.c_ulonglong(self.seed),
+                                              C.c_uint(base + i), _lib.stream()))
+            _lib.count_launch()
+            yield x, y

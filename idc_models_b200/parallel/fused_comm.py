@@ -45,6 +45,8 @@ class FusedComm:
         store.grad = self.grad.tensor[:n]
         store.shadow = self.shadow.tensor[:n]
         store.touch(external=True)
+        self.scal = self.alloc.alloc(4, torch.float32)
+        self.scal_out = torch.zeros(4, dtype=torch.float32, device=world.device)
         torch.cuda.synchronize()
         world.barrier()
 
@@ -52,8 +54,13 @@ class FusedComm:
     def uses_multicast(self) -> bool:
         return bool(self.master.mc_ptr and self.grad.mc_ptr and self.shadow.mc_ptr)
 
-    def allreduce_apply(self, optimizer, grad_scale: float = 1.0) -> None:
-        """One launch per contiguous trainable range (normally one)."""
+    def allreduce_apply(self, optimizer, grad_scale: float = 1.0, owner: int = -1, scalars=None):
+        """One launch per contiguous trainable range (normally one). ``owner`` >= 0 selects the central-
+        storage variant (that rank alone reduces, updates and broadcasts). ``scalars`` (a 4-float device
+        tensor) is summed over ranks on the kernel's barrier; the sum is returned."""
+        want_scalars = scalars is not None
+        if want_scalars:
+            self.scal.tensor[:4].copy_(scalars.reshape(-1)[:4])
         optimizer.iterations += 1
         self.store.touch()
         lr = optimizer._step_lr()
@@ -73,11 +80,15 @@ class FusedComm:
                 vp(s1.data_ptr() + 4 * b if s1 is not None else 0),
                 vp(s2.data_ptr() + 4 * b if s2 is not None else 0),
                 C.c_longlong(e - b), C.c_int(KIND[optimizer.kind]), C.c_float(lr), C.c_float(p1),
-                C.c_float(p2), C.c_float(eps), C.c_float(grad_scale), _lib.stream()))
+                C.c_float(p2), C.c_float(eps), C.c_float(grad_scale), C.c_int(owner),
+                self.scal.ptrs() if scalars is not None else None,
+                vp(self.scal_out.data_ptr()) if scalars is not None else vp(0), _lib.stream()))
             _lib.count_launch()
+            scalars = None      # reduce the metric slots once, with the first range
+        return self.scal_out if want_scalars else None
 
 
-def allreduce_apply_emulated(emu, rank_bufs, opt_states, n, kind, lr, p1, p2, eps, grad_scale) -> None:
+def allreduce_apply_emulated(emu, rank_bufs, opt_states, n, kind, lr, p1, p2, eps, grad_scale, owner=-1) -> None:
     """Single-process emulation used by the 1-GPU tests: ``rank_bufs`` = dict(grad/master/shadow ->
     list[SymmBuffer] per rank); runs the kernel once per emulated rank with barriers disabled."""
     lib = _lib.cuda_lib()
@@ -89,5 +100,5 @@ def allreduce_apply_emulated(emu, rank_bufs, opt_states, n, kind, lr, p1, p2, ep
             rank_bufs["shadow"][r].ptrs(), vp(0), vp(0), vp(0),
             vp(s1.data_ptr() if s1 is not None else 0), vp(s2.data_ptr() if s2 is not None else 0),
             C.c_longlong(n), C.c_int(KIND[kind]), C.c_float(lr), C.c_float(p1), C.c_float(p2),
-            C.c_float(eps), C.c_float(grad_scale), _lib.stream()))
+            C.c_float(eps), C.c_float(grad_scale), C.c_int(owner), None, vp(0), _lib.stream()))
         _lib.count_launch()

@@ -129,6 +129,10 @@ class CentralStorageStrategy(Strategy):
         if not w.is_distributed:
             optimizer.apply(grad_scale)
             return
+        if self.comm == "fused":
+            # same kernel, one owner: reduce-to-owner + update + broadcast over NVLink
+            self._fused_comm(store).allreduce_apply(optimizer, grad_scale, owner=self.owner)
+            return
         # gradients -> owner ; owner applies ; fresh variables -> everyone
         for b, e in optimizer.ranges:
             w.reduce_to(store.grad[b:e], self.owner)

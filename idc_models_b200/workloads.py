@@ -353,8 +353,8 @@ def main_secure(argv: list) -> dict:
                                  label_as_int=True)
     client_data = labeled_ds.take(TRAIN_SIZE)
     test_data = prepare_for_training(labeled_ds.skip(TRAIN_SIZE).take(TEST_SIZE), BATCH_SIZE, seed=args.seed)
-    # the 10x10 CNN has no fused pipeline yet: run the PyTorch reference executor explicitly on any device
-    model_fn = lambda: create_small_cnn(device, args.seed, lr, executor="reference")  # noqa: E731
+    # CPU: PyTorch reference executor; CUDA: the single-kernel fused pipeline (csrc/small_cnn.cu)
+    model_fn = lambda: create_small_cnn(device, args.seed, lr)  # noqa: E731
 
     def create_clients(all_data, client_ids, percent):
         return [Client(all_data.shard(NUM_CLIENTS, int(i)), int(i), percent, model_fn=model_fn, n_clients=NUM_CLIENTS,

@@ -208,6 +208,21 @@ int idcb_head(const idcb_head_desc* d, const void* x, const float* w, const floa
               const float* labels, float* logits, float* acc, float* dw, float* db, void* dx,
               float* gacc, float* stat_a, float* stat_b, void* stream);
 
+/* ---- the 10x10 secure-FL CNN: forward + loss + metrics + backward in one launch ----------------------- */
+/* create_model() of secure_fed_model.py:84-98. blockIdx.y = client: several clients
+ * (each with its own parameter / gradient block of `param_stride` floats) train in the same launch.
+ * offsets6 = element offsets of conv W, conv b, dense W, dense b, out W, out b inside a block; conv W is
+ * [32][3][3][conv_cin_stride]. Dropout masks are Philox(seed, step, example, feature): reproducible. */
+int idcb_small_cnn_step(const float* x, const float* labels, const float* params, float* grads, float* logits,
+                        float* acc, int n_clients, int batch, int param_stride, const int* offsets6,
+                        int conv_cin_stride, int training, float grad_scale, float drop1, float drop2,
+                        unsigned long long seed, unsigned int step, float threshold, int acc_on_prob,
+                        void* stream);
+/* Device-side synthetic IDC-like patches: Philox noise + class tint, fp32 [n][h][w][c] in [0,1] and 0/1
+ * labels (stands in for the tf.data input pipeline of dist_model_tf_mobile.py:34-65). */
+int idcb_synth_patches(float* x, float* labels, long long n_img, int h, int w, int channels,
+                       unsigned long long seed, unsigned int step, void* stream);
+
 /* ---- optimizers (flat buffers) ------------------------------------------------------------------ */
 #define IDCB_OPT_RMSPROP 0
 #define IDCB_OPT_SGD 1
@@ -235,11 +250,15 @@ typedef struct idcb_comm_world {
  * (dist_model_tf_mobile.py:115-132 under strategy.scope()):
  * rank r reduces the r-th 1/world of grad[*], scales it, applies the optimizer to its shard of the
  * master weights (s1/s2 = local state, only the shard is touched), writes the new fp32 weights and
- * their bf16 cast to every rank, and re-zeroes the consumed gradient shard on every rank. */
+ * their bf16 cast to every rank, and re-zeroes the consumed gradient shard on every rank.
+ * owner = -1: mirrored (sharded ownership). owner = r: CentralStorageStrategy — rank r alone reduces,
+ * updates and broadcasts (dist_model_tf_dense.py:24).
+ * scal/scal_out (optional): per-rank 4-float metric slots summed over ranks on the kernel's first
+ * barrier (loss / correct / count). */
 int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad, void* const* master,
                          void* const* shadow, void* mc_grad, void* mc_master, void* mc_shadow, float* s1,
                          float* s2, long long n, int kind, float lr, float p1, float p2, float eps,
-                         float grad_scale, void* stream);
+                         float grad_scale, int owner, void* const* scal, float* scal_out, void* stream);
 
 /* TFF federated averaging (fed_model.py:207-227): clients[p] is rank p's
  * [k_local][stride] block of trained client models, weights[p] its [k_local] example counts.
