@@ -295,7 +295,7 @@ struct FwdSmem {
 // fprop / dgrad kernel
 // =============================================================================================
 template <int kBN, bool kBMN, int kEpi>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, (kEpi == 2 || kBN > 64) ? 1 : 2)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ ConvArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     using L = FwdSmem<kBN, kBMN>;
@@ -795,7 +795,7 @@ static long long* g_dbg = nullptr;
 static int pick_bn(int M, int N) {
     if (N <= 32) return 32;
     const int mt = ceil_div(M, kBM);
-    const int target = num_sms() / 2;
+    const int target = num_sms() / 8;
     if (N > 64 && mt * ceil_div(N, 128) >= target) return 128;
     if (mt * ceil_div(N, 64) >= target) return 64;
     return N <= 64 && mt * 1 >= target ? 64 : 32;
