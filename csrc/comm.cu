@@ -558,8 +558,8 @@ extern "C" int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* cli
 // 128-byte flag pad per GPU that loads the library, held until the process exits.
 //
 // The symbol names below are host-side handles, not device addresses; the device address is fetched
-// once per device with cudaGetSymbolAddress (with that device current) and cached. That first call on a
-// device does the lookup, so make it before starting any stream capture. Nothing here calls cudaMalloc,
+// once per device with cudaGetSymbolAddress (with that device current) and cached, so only the first
+// call on a device pays for the lookup. Nothing here calls cudaMalloc,
 // cudaFree or an allocating library routine. All calls on one GPU share the same staging memory, which
 // keeps whatever the previous call left in it: phase A rewrites every word it later reads, and the
 // flag pad is a monotonically increasing epoch by design, so nothing needs clearing — but two calls

@@ -78,24 +78,74 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
                  "r"(bytes)
                  : "memory");
 }
+// try_wait parks the thread in hardware until the phase completes or this many nanoseconds pass, so a
+// waiting warp does not burn issue slots the producer warps of the same SM sub-partition need.
+constexpr uint32_t kMbarSuspendNs = 100000u;
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
         "{\n\t.reg .pred P;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, P;\n\t}\n"
         : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(kMbarSuspendNs)
         : "memory");
     return ok != 0;
 }
 // Bounded wait: a protocol bug turns into a trap (launch failure) instead of a hung GPU.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    // try_wait suspends the thread for a hardware-bounded interval by itself, so the spin is counted in
+    // attempts (no clock reads on the hot path); the bound is several seconds of wall time.
     if (mbar_try_wait(bar, parity)) return;
     long long t0 = clock64();
     while (!mbar_try_wait(bar, parity)) {
         if (clock64() - t0 > 4000000000LL) __trap();  // ~2 s at 2 GHz
     }
+}
+
+// Variants addressed by a 32-bit shared-window address (no generic->shared conversion per call).
+__device__ __forceinline__ void mbar_arrive_s(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_s(uint32_t bar, uint32_t parity) {
+    uint32_t spins = 0;
+    for (;;) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred P;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, P;\n\t}\n"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity), "r"(kMbarSuspendNs)
+            : "memory");
+        if (ok) return;
+        if (++spins == (1u << 30)) __trap();
+    }
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr)
+                 : "memory");
+    return v;
+}
+// ---- Ampere-style asynchronous copies (LDGSTS): global -> shared without staging in registers ----
+// 16 bytes, L2-only caching; `bytes` = 16 copies, 0 writes zeros (used for padding / out-of-range chunks).
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory");
+}
+// The mbarrier receives one arrival from this thread once all cp.async it has issued so far have landed
+// (.noinc: the arrival is part of the barrier's expected count, it does not add to it).
+__device__ __forceinline__ void cp_async_mbar_arrive(uint32_t bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, const uint4& v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                 : "memory");
 }
 
 // ---- proxy fences -----------------------------------------------------------------------------
@@ -233,6 +283,23 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
     __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&v);
     return __bfloat1622float2(h);
 }
+// Two fp32 values -> packed bf16x2 with the activation folded into the conversion: ReLU is the
+// cvt's own .relu modifier, ReLU6 adds one packed min (exact: rounding is monotonic and 0 / 6 are
+// representable). `lo` lands in the low half.
+template <int kAct>
+__device__ __forceinline__ uint32_t pack_act_bf16x2(float lo, float hi) {
+    uint32_t r;
+    if (kAct == 0) {
+        asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    } else {
+        asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+        if (kAct == 2) asm("min.bf16x2 %0, %0, %1;" : "+r"(r) : "r"(0x40C040C0u));  // 6.0 | 6.0
+    }
+    return r;
+}
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+
 __device__ __forceinline__ float apply_act(float v, int act) {
     if (act == 1) return fmaxf(v, 0.f);
     if (act == 2) return fminf(fmaxf(v, 0.f), 6.f);

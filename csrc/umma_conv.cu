@@ -42,11 +42,15 @@ namespace idcb {
 
 constexpr int kBM = 128;      // UMMA M (rows of the accumulator = TMEM lanes)
 constexpr int kBK = 64;       // K elements per pipeline stage (one 128-byte swizzle row)
-constexpr int kMaxStages = 4;
+constexpr int kMaxStages = 8;
 constexpr int kWorkers = 256;  // 8 producer / epilogue warps
 constexpr int kThreads = kWorkers + 64;
 constexpr int kTmaWarp = 8, kMmaWarp = 9;
-constexpr int kFullArrivals = 8 + 1;    // 8 producer warps + the TMA thread
+constexpr int kFullArrivalsPro = 8 + 1;          // transform path: one arrival per producer warp + the TMA thread
+constexpr int kFullArrivalsCp = kWorkers + 1;    // copy path: every producer thread's cp.async arrival + TMA
+constexpr int kRaw = 4;                          // k-blocks of raw activations in flight per CTA (transform path)
+constexpr int kBarBytes = 256;                    // barrier block: full/empty/acc/raw_full/raw_empty + TMEM slot
+constexpr int kRawBytes = kBM * 128;             // one k-block of raw 16-byte chunks, [chunk row i][thread]
 constexpr int kATileBytes = kBM * 128;  // 16 KiB
 
 // n / d for n*d < 2^64 with one 64-bit multiply-high (magic == 0 encodes d == 1)
@@ -135,18 +139,20 @@ __device__ __forceinline__ float warp_column_sums(float (&v)[kW], int lane) {
     return v[0];
 }
 
+template <int kAct>
+__device__ __forceinline__ void transform8_act(uint4& q, const float4& s0, const float4& s1,
+                                               const float4& h0, const float4& h1) {
+    q.x = pack_act_bf16x2<kAct>(fmaf(bf16_lo(q.x), s0.x, h0.x), fmaf(bf16_hi(q.x), s0.y, h0.y));
+    q.y = pack_act_bf16x2<kAct>(fmaf(bf16_lo(q.y), s0.z, h0.z), fmaf(bf16_hi(q.y), s0.w, h0.w));
+    q.z = pack_act_bf16x2<kAct>(fmaf(bf16_lo(q.z), s1.x, h1.x), fmaf(bf16_hi(q.z), s1.y, h1.y));
+    q.w = pack_act_bf16x2<kAct>(fmaf(bf16_lo(q.w), s1.z, h1.z), fmaf(bf16_hi(q.w), s1.w, h1.w));
+}
+// a = act(scale[c] * x + shift[c]) on 8 packed bf16 channels (act is warp-uniform)
 __device__ __forceinline__ void transform8(uint4& q, const float4& s0, const float4& s1,
                                            const float4& h0, const float4& h1, int act) {
-    uint32_t* w = reinterpret_cast<uint32_t*>(&q);
-    float2 f;
-    f = unpack_bf16x2(w[0]);
-    w[0] = pack_bf16x2(apply_act(fmaf(f.x, s0.x, h0.x), act), apply_act(fmaf(f.y, s0.y, h0.y), act));
-    f = unpack_bf16x2(w[1]);
-    w[1] = pack_bf16x2(apply_act(fmaf(f.x, s0.z, h0.z), act), apply_act(fmaf(f.y, s0.w, h0.w), act));
-    f = unpack_bf16x2(w[2]);
-    w[2] = pack_bf16x2(apply_act(fmaf(f.x, s1.x, h1.x), act), apply_act(fmaf(f.y, s1.y, h1.y), act));
-    f = unpack_bf16x2(w[3]);
-    w[3] = pack_bf16x2(apply_act(fmaf(f.x, s1.z, h1.z), act), apply_act(fmaf(f.y, s1.w, h1.w), act));
+    if (act == 1) transform8_act<1>(q, s0, s1, h0, h1);
+    else if (act == 2) transform8_act<2>(q, s0, s1, h0, h1);
+    else transform8_act<0>(q, s0, s1, h0, h1);
 }
 
 template <int kW>
@@ -294,21 +300,137 @@ struct FwdSmem {
 // =============================================================================================
 // fprop / dgrad kernel
 // =============================================================================================
+// Thread layout of conv_gemm_kernel.
+//   warps 0-7   workers: epilogue, and (a) dgrad: issue the asynchronous A copies themselves,
+//                        (b) fprop with a BatchNorm prologue: transform raw chunks into operand tiles
+//   warps 8-11  fprop only: loaders. They do nothing but issue cp.async and let the copies signal an
+//               mbarrier on completion, so no thread that must later wait, fence or release-arrive ever has
+//               copies in flight (measured: an mbarrier.arrive with release semantics, like a MEMBAR, does
+//               not retire until the issuing thread's outstanding copies have landed, which turned every
+//               k-block of a register- or cp.async-pipelined producer into a full memory round trip).
+//   then the TMA warp (weights) and the MMA warp.
+template <bool kBMN>
+struct GemmCfg {
+    static constexpr int kWork = 256;                      // worker threads
+    static constexpr int kLoad = kBMN ? 0 : 128;           // dedicated loader threads
+    static constexpr int kNT = kWork + kLoad + 64;         // + TMA warp + MMA warp
+    static constexpr int kTmaWarp = (kWork + kLoad) / 32, kMmaWarp = kTmaWarp + 1;
+    static constexpr int kIssuers = kBMN ? kWork : kLoad;  // threads whose copies feed a k-block
+};
+
+// One thread's share of the implicit-GEMM A operand: 16-byte chunk j of rows rb + i * kStep (i < kR) of
+// every k-block. Holds, per row, the element offset of the window origin and a bit mask over the taps whose
+// input position is inside the image (zero padding and rows past M are simply cleared bits), plus a
+// (tap, channel) cursor that advances one k-block per call — so the main loop does no divisions, coordinate
+// arithmetic or bounds checks.
+template <int kR, int kStep, bool kBMN>
+struct Gather {
+    int roff[kR];
+    uint32_t vlo[kR], vhi[kR];   // tap-validity bits 0..31 / 32..48
+    int cur_c, cur_tap, cur_kw, cur_off, row_wrap, span;
+
+    __device__ __forceinline__ void init(const ConvArgs& p, int m0, int t) {
+        const int j = t & 7, rb = t >> 3;
+#pragma unroll
+        for (int i = 0; i < kR; ++i) {
+            const int m = m0 + i * kStep + rb;
+            roff[i] = 0;
+            unsigned long long vm = 0ull;
+            if (m < p.M) {
+                const int b = fdiv(m, p.d_hw);
+                const int rem = m - b * (p.Ho * p.Wo);
+                const int ho = fdiv(rem, p.d_wo);
+                const int wo = rem - ho * p.Wo;
+                const int hb = ho * p.stride - p.pad_t;
+                const int wb = wo * p.stride - p.pad_l;
+                roff[i] = ((b * p.H + hb) * p.W + wb) * p.x_pitch + p.x_coff;
+                // valid kw form one contiguous run [kw_lo, kw_hi); likewise kh
+                const int kw_lo = max(0, -wb), kw_hi = min(p.KW, p.W - wb);
+                const int kh_lo = max(0, -hb), kh_hi = min(p.KH, p.H - hb);
+                if (kw_hi > kw_lo) {
+                    const unsigned long long wm = ((1ull << kw_hi) - 1ull) & ~((1ull << kw_lo) - 1ull);
+#pragma unroll 1
+                    for (int kh = kh_lo; kh < kh_hi; ++kh) vm |= wm << (kh * p.KW);
+                }
+            }
+            vlo[i] = static_cast<uint32_t>(vm);
+            vhi[i] = static_cast<uint32_t>(vm >> 32);
+        }
+        cur_tap = kBMN ? 0 : static_cast<int>(fdiv(j * 8, p.d_cin));
+        cur_c = j * 8 - cur_tap * p.Cin;
+        const int kh0 = fdiv(cur_tap, p.d_kw);
+        cur_kw = cur_tap - kh0 * p.KW;
+        cur_off = (kh0 * p.W + cur_kw) * p.x_pitch;
+        row_wrap = (p.W - p.KW) * p.x_pitch;
+        span = ((p.Cin + kBK - 1) / kBK) * kBK;
+    }
+    // Row mask of the next k-block (bit i: row i's chunk holds data rather than zeros); `c` = the chunk's first
+    // channel, `base` = element offset to add to roff[i]. Advances the cursor.
+    __device__ __forceinline__ uint32_t next(const ConvArgs& p, int taps, int& c, int& base) {
+        c = cur_c;
+        const int tap = cur_tap;
+        const bool cvalid = tap < taps && c < p.Cin;
+        base = cur_off + c;
+        cur_c += kBK;
+        if (kBMN) {
+            // dgrad walks whole 64-wide blocks per tap (the tail block of a tap is zero padded)
+            if (cur_c >= span) {
+                cur_c -= span;
+                ++cur_tap;
+                cur_off += p.x_pitch;
+                if (++cur_kw == p.KW) { cur_kw = 0; cur_off += row_wrap; }
+            }
+        } else {
+            while (cur_c >= p.Cin) {
+                cur_c -= p.Cin;
+                ++cur_tap;
+                cur_off += p.x_pitch;
+                if (++cur_kw == p.KW) { cur_kw = 0; cur_off += row_wrap; }
+            }
+        }
+        const uint32_t tb_lo = (cvalid && tap < 32) ? 1u << tap : 0u;
+        const uint32_t tb_hi = (cvalid && tap >= 32) ? 1u << (tap - 32) : 0u;
+        uint32_t okmask = 0;
+#pragma unroll
+        for (int i = 0; i < kR; ++i)
+            if (((vlo[i] & tb_lo) | (vhi[i] & tb_hi)) != 0u) okmask |= 1u << i;
+        return okmask;
+    }
+    // Start the asynchronous copies (LDGSTS) of the next k-block to dst0 + i * dstep; chunks without data are
+    // zero-filled.
+    __device__ __forceinline__ void issue(const ConvArgs& p, int taps, uint32_t dst0, uint32_t dstep) {
+        int c, base;
+        const uint32_t ok = next(p, taps, c, base);
+#pragma unroll
+        for (int i = 0; i < kR; ++i) {
+            const bool v = (ok >> i) & 1u;
+            cp_async16(dst0 + i * dstep, p.x + (v ? base + roff[i] : 0), v ? 16u : 0u);
+        }
+    }
+};
+
 template <int kBN, bool kBMN, int kEpi>
-__global__ void __launch_bounds__(kThreads, (kEpi == 2 || kBN > 64) ? 1 : 2)
+__global__ void __launch_bounds__(GemmCfg<kBMN>::kNT, (!kBMN || kEpi == 2 || kBN > 64) ? 1 : 2)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ ConvArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     using L = FwdSmem<kBN, kBMN>;
+    using G = GemmCfg<kBMN>;
+    constexpr int kWork = G::kWork, kNT = G::kNT;
+    constexpr int kTmaWarp = G::kTmaWarp, kMmaWarp = G::kMmaWarp;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
     const int nstages = p.stages;
     uint8_t* a_tiles = smem;
     uint8_t* b_tiles = smem + nstages * kATileBytes;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + nstages * L::kBTileBytes);
+    const bool has_pro = !kBMN && (p.pro_scale != nullptr || p.bn_sum != nullptr);
+    uint8_t* raw_tiles = b_tiles + nstages * L::kBTileBytes;   // raw staging ring, present only with a prologue
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(raw_tiles + (has_pro ? kRaw * kRawBytes : 0));
     uint64_t* empty_bar = full_bar + kMaxStages;
     uint64_t* acc_bar = empty_bar + kMaxStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
-    float* s_scale = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full_bar) + 96);  // 16-B aligned
+    uint64_t* raw_full = acc_bar + 2;
+    uint64_t* raw_empty = raw_full + kRaw;
+    float* s_scale = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full_bar) + kBarBytes);
     float* s_shift = s_scale + ((p.Cin + 3) & ~3);
 
     const int warp = threadIdx.x >> 5;
@@ -319,44 +441,38 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     const int cblocks = (p.Cin + kBK - 1) / kBK;                 // dgrad: k-blocks per tap
     const int ktot = taps * p.Cin;                              // fprop: linearised K extent
     const int num_kb = kBMN ? taps * cblocks : (ktot + kBK - 1) / kBK;
-    const bool has_pro = p.pro_scale != nullptr || p.bn_sum != nullptr;
     if (threadIdx.x == 0) IDCB_STAMP(0);
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nstages; ++s) {
-            mbar_init(&full_bar[s], kFullArrivals);
+            // transform path: one arrival per warp of the owning worker group; copy path: one per issuing thread; + TMA
+            mbar_init(&full_bar[s], has_pro ? kWork / 32 + 1 : G::kIssuers + 1);
             mbar_init(&empty_bar[s], 1);  // one tcgen05.commit
         }
         mbar_init(acc_bar, 1);
+        if (has_pro) {
+            for (int s = 0; s < kRaw; ++s) {
+                mbar_init(&raw_full[s], G::kLoad);      // every loader thread's copies
+                mbar_init(&raw_empty[s], kWork / 32);   // every warp of the group that owns the k-block has read it
+            }
+        }
         mbar_fence_init();
     }
     if (warp == kTmaWarp && lane == 0) tma_prefetch_desc(&tmap_w);
     if (warp == kMmaWarp) tmem_alloc<kBN < 32 ? 32 : kBN>(tmem_slot);
     if (p.bn_sum != nullptr) {
-        const bool publish = blockIdx.x == 0 && blockIdx.y == 0;
+        // BatchNorm finalised from the batch sums by every CTA for itself (the publication of the
+        // coefficients and the moving-statistics update happen at the very end of the kernel)
         const float inv = 1.f / p.bn_count;
-        for (int c = threadIdx.x; c < p.Cin; c += kThreads) {
+        for (int c = threadIdx.x; c < p.Cin; c += kNT) {
             const float mean = p.bn_sum[c] * inv;
             const float var = fmaxf(p.bn_sq[c] * inv - mean * mean, 0.f);
-            const float rstd = rsqrtf(var + p.bn_eps);
-            const float sc = p.bn_gamma[c] * rstd;
-            const float sh = p.bn_beta[c] - mean * sc;
+            const float sc = p.bn_gamma[c] * rsqrtf(var + p.bn_eps);
             s_scale[c] = sc;
-            s_shift[c] = sh;
-            if (publish) {
-                p.bn_scale_out[c] = sc;
-                p.bn_shift_out[c] = sh;
-                p.bn_mean_out[c] = mean;
-                p.bn_rstd_out[c] = rstd;
-                if (p.bn_mmean != nullptr) {
-                    const float unbiased = p.bn_count > 1.f ? var * (p.bn_count / (p.bn_count - 1.f)) : var;
-                    p.bn_mmean[c] = p.bn_mmean[c] * p.bn_momentum + mean * (1.f - p.bn_momentum);
-                    p.bn_mvar[c] = p.bn_mvar[c] * p.bn_momentum + unbiased * (1.f - p.bn_momentum);
-                }
-            }
+            s_shift[c] = p.bn_beta[c] - mean * sc;
         }
     } else if (has_pro) {
-        for (int c = threadIdx.x; c < p.Cin; c += kThreads) {
+        for (int c = threadIdx.x; c < p.Cin; c += kNT) {
             s_scale[c] = p.pro_scale[c];
             s_shift[c] = p.pro_shift[c];
         }
@@ -367,116 +483,98 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     const uint32_t tmem_base = *tmem_slot;
     if (threadIdx.x == 0) IDCB_STAMP(1);
 
-    if (warp < 8) {
-        // ===================== A producers =====================
+    if (warp < kWork / 32) {
         const int j = threadIdx.x & 7;       // 16-byte chunk inside the 128-byte row
-        const int rbase = threadIdx.x >> 3;  // 0..31
-        int hb[4], wb[4], roff[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int m = m0 + i * 32 + rbase;
-            if (m < p.M) {
-                const int b = fdiv(m, p.d_hw);
-                const int rem = m - b * (p.Ho * p.Wo);
-                const int ho = fdiv(rem, p.d_wo);
-                const int wo = rem - ho * p.Wo;
-                hb[i] = ho * p.stride - p.pad_t;
-                wb[i] = wo * p.stride - p.pad_l;
-                roff[i] = ((b * p.H + hb[i]) * p.W + wb[i]) * p.x_pitch + p.x_coff;
-            } else {
-                hb[i] = -(1 << 20);
-                wb[i] = -(1 << 20);
-                roff[i] = 0;
-            }
-        }
-        // issue the 4 row loads of k-block kb; returns the channel (or -1) and a validity mask
-        // (tap, channel) cursor of this thread's 16-byte chunk; issue() is called with kb = 0, 1, 2, ...
-        // so the cursor advances incrementally (no per-k-block divisions on the critical path)
-        int cur_c, cur_kh, cur_kw;
-        {
-            const int tap0 = kBMN ? 0 : static_cast<int>(fdiv(j * 8, p.d_cin));
-            cur_c = j * 8 - tap0 * p.Cin;
-            cur_kh = fdiv(tap0, p.d_kw);
-            cur_kw = tap0 - cur_kh * p.KW;
-        }
-        auto issue = [&](int kb, uint4 (&v)[4], uint32_t& okmask) -> int {
-            (void)kb;
-            const int kh = cur_kh, kw = cur_kw;
-            int c = (cur_kh < p.KH && cur_c < p.Cin) ? cur_c : -1;
-            // advance the cursor by one k-block
-            cur_c += kBK;
-            if (kBMN) {
-                // dgrad walks whole 64-wide blocks per tap (the tail block of a tap is zero padded)
-                if (cur_c >= cblocks * kBK) {
-                    cur_c -= cblocks * kBK;
-                    if (++cur_kw == p.KW) { cur_kw = 0; ++cur_kh; }
-                }
-            } else {
-                while (cur_c >= p.Cin) {
-                    cur_c -= p.Cin;
-                    if (++cur_kw == p.KW) { cur_kw = 0; ++cur_kh; }
+        const int rbase = threadIdx.x >> 3;  // this thread owns tile rows rbase + 32 * i
+        const uint32_t full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
+        const uint32_t tile_off = sw128_offset(rbase, j);   // row i adds i * 4096 (raw slots use the same layout)
+        if (kBMN) {
+            // ===================== dgrad: the workers issue the A copies =====================
+            // The chunks land directly in the swizzled operand tile; the stage's "full" barrier hears from
+            // every thread when its copies have completed. Nothing here waits for data, so up to `nstages`
+            // k-blocks of global traffic are in flight per CTA.
+            Gather<4, 32, kBMN> g;
+            g.init(p, m0, threadIdx.x);
+            const uint32_t a_base = smem_u32(a_tiles) + tile_off;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                if (kb >= nstages) mbar_wait_s(empty0 + stage * 8, phase ^ 1);   // first pass: slots start empty
+                g.issue(p, taps, a_base + stage * kATileBytes, 4096);
+                cp_async_mbar_arrive(full0 + stage * 8);
+                if (threadIdx.x == 0 && kb == 0) IDCB_STAMP(2);
+                if (++stage == nstages) {
+                    stage = 0;
+                    phase ^= 1;
                 }
             }
-            const int delta = (kh * p.W + kw) * p.x_pitch + c;
-            okmask = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const unsigned hi = static_cast<unsigned>(hb[i] + kh);
-                const unsigned wi = static_cast<unsigned>(wb[i] + kw);
-                const bool ok = c >= 0 && hi < static_cast<unsigned>(p.H) && wi < static_cast<unsigned>(p.W);
-                v[i] = make_uint4(0u, 0u, 0u, 0u);
-                if (ok) {
-                    okmask |= 1u << i;
-                    v[i] = __ldg(reinterpret_cast<const uint4*>(p.x + (roff[i] + delta)));
+        } else if (has_pro) {
+            // ===================== fprop with a prologue: transform raw chunks into operand tiles ==========
+            // a = act(scale[c] * x + shift[c]) in registers between the raw ring (filled by the loader warps)
+            // and the swizzled operand tile. These threads never have global traffic in flight, so their
+            // release-arrive on the "full" barrier retires at once.
+            // The worker warps can be split into kGroups groups that take alternate k-blocks (more time per
+            // group for its dependent wait -> load -> transform -> store -> arrive chain); one group is fastest.
+            constexpr int kGroups = 1, kGT = kWork / kGroups, kGR = 1024 / kGT;   // (2 groups of 128 threads measured: no gain)
+            const int grp = threadIdx.x / kGT, gt = threadIdx.x % kGT;
+            Gather<kGR, kGT / 8, kBMN> g;   // used for its (tap, channel) cursor and padding masks only
+            g.init(p, m0, gt);
+            const uint32_t goff = sw128_offset(gt >> 3, gt & 7);   // row i adds i * kGT * 16
+            const uint32_t a_base = smem_u32(a_tiles) + goff;
+            const uint32_t raw_base = smem_u32(raw_tiles) + goff;
+            const uint32_t rfull0 = smem_u32(raw_full), rempty0 = smem_u32(raw_empty);
+            const int pro_act = p.pro_act;
+            int stage = 0, slot = 0;
+            uint32_t phase = 0, rphase = 0;
+            auto advance = [&]() {
+                if (++stage == nstages) { stage = 0; phase ^= 1; }
+                if (++slot == kRaw) { slot = 0; rphase ^= 1; }
+            };
+            for (int kb = 0; kb < num_kb; ++kb) {
+                int c, base;
+                const uint32_t ok = g.next(p, taps, c, base);
+                if ((kb & (kGroups - 1)) != grp) {   // the other group's k-block
+                    advance();
+                    continue;
                 }
-            }
-            return c;
-        };
-        // register-resident software pipeline: kDepth k-blocks of global loads in flight per thread
-        constexpr int kDepth = 3;
-        int stage = 0;
-        uint32_t phase = 0;
-        uint4 v[kDepth][4];
-        uint32_t ok[kDepth];
-        int cch[kDepth];
+                mbar_wait_s(rfull0 + slot * 8, rphase);
+                uint4 v[kGR];
 #pragma unroll
-        for (int d = 0; d < kDepth; ++d) {
-            ok[d] = 0;
-            cch[d] = -1;
-            if (d < num_kb) cch[d] = issue(d, v[d], ok[d]);
-        }
-        for (int kb0 = 0; kb0 < num_kb; kb0 += kDepth) {
+                for (int i = 0; i < kGR; ++i) v[i] = ld_shared_v4(raw_base + slot * kRawBytes + i * (kGT * 16));
+                if (ok != 0) {
+                    const float4 s0 = *reinterpret_cast<const float4*>(s_scale + c);
+                    const float4 s1 = *reinterpret_cast<const float4*>(s_scale + c + 4);
+                    const float4 h0 = *reinterpret_cast<const float4*>(s_shift + c);
+                    const float4 h1 = *reinterpret_cast<const float4*>(s_shift + c + 4);
+                    if (pro_act == 1) {
 #pragma unroll
-            for (int d = 0; d < kDepth; ++d) {
-                const int kb = kb0 + d;
-                if (kb < num_kb) {  // warp-uniform
-                    if (has_pro && ok[d] != 0) {
-                        const int c = cch[d];
-                        const float4 s0 = *reinterpret_cast<const float4*>(s_scale + c);
-                        const float4 s1 = *reinterpret_cast<const float4*>(s_scale + c + 4);
-                        const float4 h0 = *reinterpret_cast<const float4*>(s_shift + c);
-                        const float4 h1 = *reinterpret_cast<const float4*>(s_shift + c + 4);
+                        for (int i = 0; i < kGR; ++i)
+                            if (ok & (1u << i)) transform8_act<1>(v[i], s0, s1, h0, h1);
+                    } else if (pro_act == 2) {
 #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            if (ok[d] & (1u << i)) transform8(v[d][i], s0, s1, h0, h1, p.pro_act);
+                        for (int i = 0; i < kGR; ++i)
+                            if (ok & (1u << i)) transform8_act<2>(v[i], s0, s1, h0, h1);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < kGR; ++i)
+                            if (ok & (1u << i)) transform8_act<0>(v[i], s0, s1, h0, h1);
                     }
-                    if (threadIdx.x == 0 && kb == 0) IDCB_STAMP(2);
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    uint8_t* a_tile = a_tiles + stage * kATileBytes;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        *reinterpret_cast<uint4*>(a_tile + sw128_offset(i * 32 + rbase, j)) = v[d][i];
-                    fence_proxy_async_smem();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&full_bar[stage]);
-                    if (++stage == nstages) {
-                        stage = 0;
-                        phase ^= 1;
-                    }
-                    if (kb + kDepth < num_kb) cch[d] = issue(kb + kDepth, v[d], ok[d]);
                 }
+                if (threadIdx.x == 0 && kb == 0) IDCB_STAMP(2);
+                if (kb >= nstages) mbar_wait_s(empty0 + stage * 8, phase ^ 1);
+                const uint32_t a_dst = a_base + stage * kATileBytes;
+#pragma unroll
+                for (int i = 0; i < kGR; ++i) st_shared_v4(a_dst + i * (kGT * 16), v[i]);
+                // (the generic->async proxy fence for these stores is issued by the MMA thread after its wait)
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive_s(full0 + stage * 8);
+                    mbar_arrive_s(rempty0 + slot * 8);   // the raw slot may be refilled
+                }
+                advance();
             }
         }
+        // (fprop without a prologue: the loader warps feed the operand tiles directly; nothing to do here)
 
         // ===================== epilogue =====================
         if (threadIdx.x == 0) IDCB_STAMP(3);
@@ -484,7 +582,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         tc_fence_after();
         if (threadIdx.x == 0) IDCB_STAMP(6);
         constexpr int kHalf = kBN / 2;               // columns per warp
-        constexpr int kW = kHalf >= 32 ? 32 : 16;    // slab width
+        constexpr int kW = (kHalf >= 32 && (kBMN || kBN < 128)) ? 32 : 16;    // slab width (register budget)
         const int quad = warp & 3;
         const int half = warp >> 2;
         const int m = m0 + quad * 32 + lane;
@@ -497,6 +595,60 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             epilogue_slab<kEpi, kW>(p, t_row + cc, m, mvalid, nb, lane);
         }
         tc_fence_before();
+        // Publication of the BatchNorm coefficients for the backward pass + moving-statistics update: one CTA,
+        // after everything latency-critical (global stores in flight would stall any later release/fence).
+        if (!kBMN && p.bn_sum != nullptr && blockIdx.x == 0 && blockIdx.y == 0) {
+            const float inv = 1.f / p.bn_count;
+            for (int c = threadIdx.x; c < p.Cin; c += kWork) {
+                const float mean = p.bn_sum[c] * inv;
+                const float var = fmaxf(p.bn_sq[c] * inv - mean * mean, 0.f);
+                const float rstd = rsqrtf(var + p.bn_eps);
+                p.bn_scale_out[c] = s_scale[c];
+                p.bn_shift_out[c] = s_shift[c];
+                p.bn_mean_out[c] = mean;
+                p.bn_rstd_out[c] = rstd;
+                if (p.bn_mmean != nullptr) {
+                    const float unbiased = p.bn_count > 1.f ? var * (p.bn_count / (p.bn_count - 1.f)) : var;
+                    p.bn_mmean[c] = p.bn_mmean[c] * p.bn_momentum + mean * (1.f - p.bn_momentum);
+                    p.bn_mvar[c] = p.bn_mvar[c] * p.bn_momentum + unbiased * (1.f - p.bn_momentum);
+                }
+            }
+        }
+    } else if (warp < kTmaWarp) {
+        // ===================== fprop loader warps: asynchronous copies only =====================
+        const int lt = threadIdx.x - kWork;
+        Gather<8, 16, kBMN> g;
+        g.init(p, m0, lt);
+        const uint32_t tile_off = sw128_offset(lt >> 3, lt & 7);   // row i adds i * 2048
+        if (has_pro) {
+            const uint32_t raw_base = smem_u32(raw_tiles) + tile_off;
+            const uint32_t rfull0 = smem_u32(raw_full), rempty0 = smem_u32(raw_empty);
+            int slot = 0;
+            uint32_t rphase = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                if (kb >= kRaw) mbar_wait_s(rempty0 + slot * 8, rphase ^ 1);
+                g.issue(p, taps, raw_base + slot * kRawBytes, 2048);
+                cp_async_mbar_arrive(rfull0 + slot * 8);
+                if (++slot == kRaw) {
+                    slot = 0;
+                    rphase ^= 1;
+                }
+            }
+        } else {
+            const uint32_t a_base = smem_u32(a_tiles) + tile_off;
+            const uint32_t full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                if (kb >= nstages) mbar_wait_s(empty0 + stage * 8, phase ^ 1);
+                g.issue(p, taps, a_base + stage * kATileBytes, 2048);
+                cp_async_mbar_arrive(full0 + stage * 8);
+                if (++stage == nstages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
     } else if (warp == kTmaWarp) {
         // ===================== TMA producer for the weight operand =====================
         if (lane == 0) {
@@ -533,6 +685,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             uint32_t phase = 0;
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&full_bar[stage], phase);
+                if (kb == 0) IDCB_STAMP(12);
+                // The producers' generic-proxy st.shared are ordered before this point by their release
+                // arrive; the generic->async proxy fence that must sit on that causality path is issued
+                // here, by the thread whose tcgen05.mma reads the tile (it has no loads in flight to drain).
+                fence_proxy_async_smem();
                 tc_fence_after();
                 if (kb == 0) IDCB_STAMP(4);
                 const uint32_t a_addr = smem_u32(a_tiles + stage * kATileBytes);
@@ -595,7 +752,9 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     const int nstages = p.stages;
     uint8_t* a_tiles = smem;  // [64 pos][128 k'] as two 8 KiB chunks
     uint8_t* b_tiles = smem + nstages * kATileBytes;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(b_tiles + nstages * kBTile);
+    const bool has_pro = p.pro_scale != nullptr;
+    uint8_t* raw_tiles = b_tiles + nstages * kBTile;   // staging ring, present only with a prologue
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(raw_tiles + (has_pro ? kRaw * kRawBytes : 0));
     uint64_t* empty_bar = full_bar + kMaxStages;
     uint64_t* acc_bar = empty_bar + kMaxStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
@@ -614,7 +773,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nstages; ++s) {
-            mbar_init(&full_bar[s], kFullArrivals);
+            mbar_init(&full_bar[s], has_pro ? kFullArrivalsPro : kFullArrivalsCp);
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(acc_bar, 1);
@@ -644,7 +803,6 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         const int c = cvalid ? kidx - tap * p.Cin : 0;
         const int kh = fdiv(tap, p.d_kw);
         const int kw = tap - kh * p.KW;
-        const bool has_pro = p.pro_scale != nullptr;
         float4 s0 = make_float4(1.f, 1.f, 1.f, 1.f), s1 = s0;
         float4 h0 = make_float4(0.f, 0.f, 0.f, 0.f), h1 = h0;
         if (has_pro && cvalid) {
@@ -653,62 +811,112 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
             h0 = make_float4(p.pro_shift[c], p.pro_shift[c + 1], p.pro_shift[c + 2], p.pro_shift[c + 3]);
             h1 = make_float4(p.pro_shift[c + 4], p.pro_shift[c + 5], p.pro_shift[c + 6], p.pro_shift[c + 7]);
         }
-        const int tap_off = (kh - p.pad_t) * p.W + (kw - p.pad_l);
-        auto issue = [&](int kb, uint4 (&v)[4], uint32_t& okmask) {
-            okmask = 0;
+        // Position cursor per row: (ho, wo) of the output position, the element offset of the input
+        // pixel this thread's tap reads for it, and the position index. One k-block = 64 positions, so the
+        // cursor advances by a fixed (images, rows, columns) step with two carries — no divisions and no
+        // coordinate rebuild per k-block.
+        const int hw = p.Ho * p.Wo;
+        const int s_b = 64 / hw, s_ho = (64 - s_b * hw) / p.Wo, s_wo = 64 - s_b * hw - s_ho * p.Wo;
+        const int step_off = ((s_b * p.H + s_ho * p.stride) * p.W + s_wo * p.stride) * p.x_pitch;
+        const int wrapw_off = (p.stride * p.W - p.Wo * p.stride) * p.x_pitch;
+        const int wraph_off = (p.H * p.W - p.Ho * p.stride * p.W) * p.x_pitch;
+        const int ch = kh - p.pad_t, cw = kw - p.pad_l;
+        int r_ho[4], r_wo[4], r_off[4], r_m[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int m = kb_begin * 64 + i * 16 + rbase;
+            const int b = fdiv(m, p.d_hw);
+            const int rem = m - b * hw;
+            r_ho[i] = fdiv(rem, p.d_wo);
+            r_wo[i] = rem - r_ho[i] * p.Wo;
+            r_m[i] = m;
+            r_off[i] = ((b * p.H + r_ho[i] * p.stride + ch) * p.W + r_wo[i] * p.stride + cw) * p.x_pitch + p.x_coff + c;
+        }
+        const int st = p.stride;
+        // asynchronous copies of this thread's 4 chunks of the next k-block to dst0 + i * dstride
+        auto issue = [&](uint32_t dst0, uint32_t dstride) -> uint32_t {
+            uint32_t okmask = 0;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
-                const int m = kb * 64 + i * 16 + rbase;
-                v[i] = make_uint4(0u, 0u, 0u, 0u);
-                if (cvalid && m < p.M) {
-                    const int b = fdiv(m, p.d_hw);
-                    const int rem = m - b * (p.Ho * p.Wo);
-                    const int ho = fdiv(rem, p.d_wo);
-                    const int wo = rem - ho * p.Wo;
-                    const unsigned hi = static_cast<unsigned>(ho * p.stride - p.pad_t + kh);
-                    const unsigned wi = static_cast<unsigned>(wo * p.stride - p.pad_l + kw);
-                    if (hi < static_cast<unsigned>(p.H) && wi < static_cast<unsigned>(p.W)) {
-                        okmask |= 1u << i;
-                        const int off = ((b * p.H + ho * p.stride) * p.W + wo * p.stride + tap_off) * p.x_pitch +
-                                        p.x_coff + c;
-                        v[i] = __ldg(reinterpret_cast<const uint4*>(p.x + off));
-                    }
-                }
+                const unsigned hi = static_cast<unsigned>(r_ho[i] * st + ch);
+                const unsigned wi = static_cast<unsigned>(r_wo[i] * st + cw);
+                const bool ok = cvalid && r_m[i] < p.M && hi < static_cast<unsigned>(p.H) && wi < static_cast<unsigned>(p.W);
+                if (ok) okmask |= 1u << i;
+                cp_async16(dst0 + i * dstride, ok ? static_cast<const void*>(p.x + r_off[i]) : static_cast<const void*>(p.x),
+                           ok ? 16u : 0u);
+                // advance this row's cursor by 64 positions
+                r_m[i] += 64;
+                r_wo[i] += s_wo;
+                r_ho[i] += s_ho;
+                r_off[i] += step_off;
+                if (r_wo[i] >= p.Wo) { r_wo[i] -= p.Wo; ++r_ho[i]; r_off[i] += wrapw_off; }
+                if (r_ho[i] >= p.Ho) { r_ho[i] -= p.Ho; r_off[i] += wraph_off; }
             }
+            return okmask;
         };
-        constexpr int kDepth = 3;
         int stage = 0;
         uint32_t phase = 0;
-        uint4 v[kDepth][4];
-        uint32_t ok[kDepth];
+        const uint32_t a_base = smem_u32(a_tiles) + half * 8192 + sw128_offset(rbase, j);   // row i adds i * 2048
+        const uint32_t full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
+        if (!has_pro) {
+            // copy path (see conv_gemm_kernel): chunks land directly in the operand tile
+            for (int kb = kb_begin; kb < kb_end; ++kb) {
+                if (kb - kb_begin >= nstages) mbar_wait_s(empty0 + stage * 8, phase ^ 1);
+                issue(a_base + stage * kATileBytes, 2048);
+                cp_async_mbar_arrive(full0 + stage * 8);
+                if (++stage == nstages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        } else {
+            // transform path: private staging ring, kRaw k-blocks ahead
+            const uint32_t raw_base = smem_u32(raw_tiles) + threadIdx.x * 16;   // chunk i at + i * 4096
+            const int pro_act = p.pro_act;
+            uint32_t okh[kRaw];
 #pragma unroll
-        for (int d = 0; d < kDepth; ++d) {
-            ok[d] = 0;
-            if (kb_begin + d < kb_end) issue(kb_begin + d, v[d], ok[d]);
-        }
-        for (int kb0 = kb_begin; kb0 < kb_end; kb0 += kDepth) {
+            for (int d = 0; d < kRaw; ++d) {
+                okh[d] = 0;
+                if (kb_begin + d < kb_end) okh[d] = issue(raw_base + d * kRawBytes, 4096);
+                cp_async_commit();
+            }
+            for (int kb0 = kb_begin; kb0 < kb_end; kb0 += kRaw) {
 #pragma unroll
-            for (int d = 0; d < kDepth; ++d) {
-                const int kb = kb0 + d;
-                if (kb < kb_end) {  // warp-uniform
-                    if (has_pro) {
+                for (int d = 0; d < kRaw; ++d) {
+                    const int kb = kb0 + d;
+                    if (kb < kb_end) {  // warp-uniform
+                        cp_async_wait<kRaw - 1>();
+                        uint4 v[4];
 #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            if (ok[d] & (1u << i)) transform8(v[d][i], s0, s1, h0, h1, p.pro_act);
+                        for (int i = 0; i < 4; ++i) v[i] = ld_shared_v4(raw_base + d * kRawBytes + i * 4096);
+                        if (okh[d] != 0) {
+                            if (pro_act == 1) {
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+                                    if (okh[d] & (1u << i)) transform8_act<1>(v[i], s0, s1, h0, h1);
+                            } else if (pro_act == 2) {
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+                                    if (okh[d] & (1u << i)) transform8_act<2>(v[i], s0, s1, h0, h1);
+                            } else {
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+                                    if (okh[d] & (1u << i)) transform8_act<0>(v[i], s0, s1, h0, h1);
+                            }
+                        }
+                        if (kb - kb_begin >= nstages) mbar_wait_s(empty0 + stage * 8, phase ^ 1);
+                        const uint32_t a_dst = a_base + stage * kATileBytes;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) st_shared_v4(a_dst + i * 2048, v[i]);
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_s(full0 + stage * 8);
+                        if (++stage == nstages) {
+                            stage = 0;
+                            phase ^= 1;
+                        }
+                        if (kb + kRaw < kb_end) okh[d] = issue(raw_base + d * kRawBytes, 4096);
+                        cp_async_commit();
                     }
-                    mbar_wait(&empty_bar[stage], phase ^ 1);
-                    uint8_t* a_tile = a_tiles + stage * kATileBytes + half * 8192;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        *reinterpret_cast<uint4*>(a_tile + sw128_offset(i * 16 + rbase, j)) = v[d][i];
-                    fence_proxy_async_smem();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&full_bar[stage]);
-                    if (++stage == nstages) {
-                        stage = 0;
-                        phase ^= 1;
-                    }
-                    if (kb + kDepth < kb_end) issue(kb + kDepth, v[d], ok[d]);
                 }
             }
         }
@@ -759,6 +967,10 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
             uint32_t phase = 0;
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&full_bar[stage], phase);
+                // The producers' generic-proxy st.shared are ordered before this point by their release
+                // arrive; the generic->async proxy fence that must sit on that causality path is issued
+                // here, by the thread whose tcgen05.mma reads the tile (it has no loads in flight to drain).
+                fence_proxy_async_smem();
                 tc_fence_after();
                 const uint32_t a_addr = smem_u32(a_tiles + stage * kATileBytes);
                 const uint32_t b_addr = smem_u32(b_tiles + stage * kBTile);
@@ -795,14 +1007,23 @@ static long long* g_dbg = nullptr;
 static int pick_bn(int M, int N) {
     if (N <= 32) return 32;
     const int mt = ceil_div(M, kBM);
-    const int target = num_sms() / 8;
+    static const int div = [] { const char* e = getenv("IDCB_CONV_TILE_DIV"); int v = e ? atoi(e) : 2; return v > 0 ? v : 2; }();
+    const int target = num_sms() / div;
     if (N > 64 && mt * ceil_div(N, 128) >= target) return 128;
     if (mt * ceil_div(N, 64) >= target) return 64;
     return N <= 64 && mt * 1 >= target ? 64 : 32;
 }
 
-static int pick_stages(int num_kb) {
-    int s = num_kb < kMaxStages ? num_kb : kMaxStages;
+// Pipeline depth. Global->shared copy latency is ~2k cycles here, so the number of k-blocks in flight sets
+// the per-k-block rate: the copy path takes as many operand stages as fit (they ARE its copies in flight),
+// the transform path keeps its depth in the raw staging ring (kRaw) and needs only a short operand ring.
+static int pick_stages(int num_kb, bool has_pro, int stage_bytes, int other_bytes, long long ctas = 0) {
+    // measured: a deeper operand ring helps the copy path of small grids (fewer, latency-bound CTAs); large
+    // grids do better with 4 stages and two co-resident CTAs per SM; the transform path gains nothing past 4
+    int cap = (has_pro || ctas > 2 * num_sms()) ? 4 : kMaxStages;
+    const int fit = (220 * 1024 - other_bytes) / stage_bytes;
+    if (cap > fit) cap = fit;
+    int s = num_kb < cap ? num_kb : cap;
     return s < 1 ? 1 : s;
 }
 
@@ -811,9 +1032,11 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     using L = FwdSmem<kBN, kBMN>;
     const int taps = a.KH * a.KW;
     const int num_kb = kBMN ? taps * ceil_div(a.Cin, kBK) : ceil_div(taps * a.Cin, kBK);
-    const int extra = 96 + 2 * (int)sizeof(float) * (a.Cin + 4) + 64;
-    a.stages = pick_stages(num_kb);
-    const size_t smem = 1024 + a.stages * L::kStageBytes + extra;
+    const int extra = kBarBytes + 2 * (int)sizeof(float) * (a.Cin + 4) + 64;
+    const bool has_pro = !kBMN && (a.pro_scale != nullptr || a.bn_sum != nullptr);
+    a.stages = pick_stages(num_kb, has_pro, L::kStageBytes, 1024 + (has_pro ? kRaw * kRawBytes : 0) + extra,
+                           kBMN ? 1LL * ceil_div(a.M, kBM) * ceil_div(a.Cout, kBN) : 0);
+    const size_t smem = 1024 + a.stages * L::kStageBytes + (has_pro ? kRaw * kRawBytes : 0) + extra;
     IDCB_REQUIRE(smem <= 227 * 1024, "conv: Cin=%d needs %zu bytes of shared memory", a.Cin, smem);
     IDCB_REQUIRE(1LL * a.B * a.H * a.W * a.x_pitch < (1LL << 31), "conv: input tensor too large for 32-bit offsets");
     a.d_hw = make_fdiv(a.Ho * a.Wo);
@@ -830,7 +1053,7 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     }
     dim3 grid(ceil_div(a.M, kBM), ceil_div(a.Cout, kBN), 1);
     a.dbg = g_dbg;
-    kern<<<grid, kThreads, smem, st>>>(tm, a);
+    kern<<<grid, GemmCfg<kBMN>::kNT, smem, st>>>(tm, a);
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -839,8 +1062,9 @@ template <int kBN>
 static int launch_wgrad(const CUtensorMap& tm, WgradArgs& a, cudaStream_t st) {
     constexpr int kBTile = ((kBN + 63) / 64) * 8192;
     const int extra = (2 * kMaxStages + 1) * 8 + 16 + 64;
-    a.stages = pick_stages(a.kb_per_split);
-    const size_t smem = 1024 + a.stages * (kATileBytes + kBTile) + extra;
+    a.stages = pick_stages(a.kb_per_split, a.pro_scale != nullptr, kATileBytes + kBTile,
+                           1024 + (a.pro_scale != nullptr ? kRaw * kRawBytes : 0) + extra);
+    const size_t smem = 1024 + a.stages * (kATileBytes + kBTile) + (a.pro_scale != nullptr ? kRaw * kRawBytes : 0) + extra;
     IDCB_REQUIRE(1LL * a.B * a.H * a.W * a.x_pitch < (1LL << 31), "conv: input tensor too large for 32-bit offsets");
     a.d_hw = make_fdiv(a.Ho * a.Wo);
     a.d_wo = make_fdiv(a.Wo);

@@ -109,7 +109,10 @@ def weighted_delta_mean(w0: torch.Tensor, clients: torch.Tensor, weights: torch.
 
 
 class FederatedAveragingProcess:
-    def __init__(self, model_fn, client_optimizer_fn, server_optimizer_fn=None, strategy=None):
+    def __init__(self, model_fn, client_optimizer_fn, server_optimizer_fn=None, strategy=None, comm: str = "fused"):
+        if comm not in ("fused", "nccl"):
+            raise ValueError("comm must be 'fused' (one kernel over peer memory) or 'nccl' (library all-reduce baseline)")
+        self.comm = comm
         self.model_fn = model_fn
         self.client_optimizer_fn = client_optimizer_fn
         sopt = server_optimizer_fn() if server_optimizer_fn is not None else SGD(learning_rate=1.0)
@@ -136,14 +139,14 @@ class FederatedAveragingProcess:
         n = net.store.master.numel()
         world = net.strategy.world
         if self._block is None or self._block[0].tensor.numel() < k_local * n:
-            if net.device.type == "cuda":
+            if net.device.type == "cuda" and self.comm == "fused":
                 from ..parallel.symm import SymmAllocator
                 self._symm = SymmAllocator(world)
                 self._block = (self._symm.alloc(k_local * n, torch.float32), self._symm.alloc(max(k_local, 4), torch.float32),
                                self._symm.alloc(n, torch.float32), self._symm.alloc(n, torch.bfloat16))
             else:
                 from ..parallel.symm import SymmBuffer
-                mk = lambda m, dt: SymmBuffer(torch.zeros(m, dtype=dt), [0])  # noqa: E731
+                mk = lambda m, dt: SymmBuffer(torch.zeros(m, dtype=dt, device=net.device), [0])  # noqa: E731
                 self._block = (mk(k_local * n, torch.float32), mk(max(k_local, 4), torch.float32),
                                mk(n, torch.float32), mk(n, torch.bfloat16))
         return self._block
@@ -191,6 +194,8 @@ class FederatedAveragingProcess:
     def _aggregate(self, net, state, clients, weights, gbuf, gshadow, k_local, ranges) -> torch.Tensor:
         n = net.store.master.numel()
         world = net.strategy.world
+        if net.device.type == "cuda" and self.comm == "nccl":
+            return self._aggregate_library(net, state, clients, weights, k_local, ranges)
         if net.device.type != "cuda":
             cl = clients.tensor[:k_local * n].view(k_local, n)
             wt = weights.tensor[:k_local]
@@ -215,8 +220,31 @@ class FederatedAveragingProcess:
         return gbuf.tensor[:n].clone()
 
 
-def build_federated_averaging_process(model_fn, client_optimizer_fn, server_optimizer_fn=None):
-    return FederatedAveragingProcess(model_fn, client_optimizer_fn, server_optimizer_fn)
+    def _aggregate_library(self, net, state, clients, weights, k_local, ranges) -> torch.Tensor:
+        """The baseline the fused kernel is measured against: PyTorch elementwise kernels for the local
+        weighted delta sum + NCCL all-reduce of (sum, weight) + PyTorch kernels for the server update."""
+        n = net.store.master.numel()
+        world = net.strategy.world
+        cl = clients.tensor[:k_local * n].view(k_local, n)
+        wt = weights.tensor[:k_local].clone()
+        new = state.master.clone()
+        for b, e in ranges:
+            finite = torch.isfinite(cl[:, b:e]).all(dim=1)
+            wt = torch.where(finite, wt, torch.zeros_like(wt))
+        tot = wt.sum().reshape(1)
+        if world.is_distributed:
+            world.all_reduce_sum(tot)
+        for b, e in ranges:
+            d = torch.where(wt[:, None] > 0, cl[:, b:e] - state.master[None, b:e], torch.zeros((), device=cl.device))
+            acc = (wt[:, None] * d).sum(dim=0)
+            if world.is_distributed:
+                world.all_reduce_sum(acc)
+            new[b:e] = torch.where(tot > 0, state.master[b:e] + self.server_lr * acc / tot.clamp_min(1e-30), state.master[b:e])
+        return new
+
+
+def build_federated_averaging_process(model_fn, client_optimizer_fn, server_optimizer_fn=None, comm: str = "fused"):
+    return FederatedAveragingProcess(model_fn, client_optimizer_fn, server_optimizer_fn, comm=comm)
 
 
 def build_federated_evaluation(model_fn):

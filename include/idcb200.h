@@ -290,8 +290,7 @@ int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* clients, void*
  * that cannot tolerate the implicit device synchronisation of cudaMalloc/cudaFree.
  *   out[offset:offset+n] = mean over the k_clients rows of clients[k][offset:offset+n]
  * - n above the limit is refused with an error (use the caller-buffer entry point instead);
- * - the first call on each device looks the storage up (cudaGetSymbolAddress); make that call before
- *   beginning a stream capture;
+ * - the first call on each device looks the storage up (cudaGetSymbolAddress) and caches the address;
  * - every call on a GPU reuses the same storage: calls whose kernels could overlap on the device
  *   (different streams) race with each other and must be serialised by the caller. */
 long long idcb_secagg_noalloc_max_elems(void);

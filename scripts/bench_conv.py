@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Micro-benchmark of the conv kernels at DenseNet/VGG shapes (CUDA events, back-to-back launches)."""
+"""Micro-benchmark of the conv kernels at DenseNet/VGG shapes (CUDA events around a graph replay)."""
 import sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
@@ -10,14 +10,24 @@ torch.manual_seed(0)
 dev = "cuda"
 
 
-def bench(fn, iters=50, warm=5):
-    for _ in range(warm):
-        fn()
+def bench(fn, iters=20, warm=2):
+    """GPU-only time per launch: `iters` launches captured in a CUDA graph, replayed between two events
+    (eager ctypes launches cost ~10 us of host time each and would hide the small kernels)."""
+    st = torch.cuda.Stream()
+    gph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(st):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(gph, stream=st):
+            for _ in range(iters):
+                fn()
+    torch.cuda.synchronize()
+    gph.replay()
     torch.cuda.synchronize()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s.record()
-    for _ in range(iters):
-        fn()
+    gph.replay()
     e.record()
     torch.cuda.synchronize()
     return s.elapsed_time(e) * 1000 / iters
