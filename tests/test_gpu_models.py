@@ -113,7 +113,7 @@ def _compare(f, r, batch=64, units=1, tol_logit=0.08, min_cos=0.85, ratio=(0.7, 
     # recognised by a reference norm well below the typical one and are bounded in magnitude only.
     tiny = [t for t in rows if t[3] < floor or (t[3] < 0.25 * median and t[1] < min_cos)]
     for name, _, q, nr in tiny:
-        assert q * nr < max(10 * floor, median), f"{name}: expected a ~zero gradient, got norm {q * nr}"
+        assert q * nr < max(10 * floor, 2 * median), f"{name}: expected a ~zero gradient, got norm {q * nr}"
     rows = [t for t in rows if t not in tiny]
     worst = min(rows, key=lambda t: t[1])
     print(f"{len(rows)} gradient tensors; worst cosine {worst[1]:.4f} at {worst[0]}; "
