@@ -132,14 +132,26 @@ def main() -> int:
     per = args.batch_per_gpu
     gb = per * n
     comm = args.comm
+    comm_note = None
     if comm == "auto":
+        comm = "fused" if n > 1 else "nccl"      # 1 GPU: no collective at all, plain optimizer kernel
+    def build(comm_kind):
+        strategy = MirroredStrategy(world=world, comm=comm_kind)
+        with strategy.scope():
+            model = build_transfer_model(args.model, (50, 50, 3), 1, device=dev, seed=0)
+            model.base.trainable = True          # full-model training, BatchNorm on batch statistics
+            model.compile(optimizer=RMSprop(lr=1e-4), loss=BinaryCrossentropy(from_logits=True),
+                          metrics=["accuracy"])    # the fused path maps its symmetric buffers here
+        return strategy, model
+
+    try:
+        strategy, model = build(comm)
+    except Exception as e:  # noqa: BLE001 - symmetric memory unavailable on this box: say so, use the library path
+        if args.comm != "auto" or comm != "fused":
+            raise
+        comm_note = f"fused path unavailable ({type(e).__name__}: {e}); fell back to nccl"
         comm = "nccl"
-    strategy = MirroredStrategy(world=world, comm=comm)
-    with strategy.scope():
-        model = build_transfer_model(args.model, (50, 50, 3), 1, device=dev, seed=0)
-        model.base.trainable = True          # full-model training, BatchNorm on batch statistics
-        model.compile(optimizer=RMSprop(lr=1e-4), loss=BinaryCrossentropy(from_logits=True),
-                      metrics=["accuracy"])
+        strategy, model = build(comm)
     ex = model.executor
     ex.use_graphs = not args.no_graph
 
@@ -207,14 +219,23 @@ def main() -> int:
         ms_per_step = dev_ms / args.steps
         value = gb * args.steps / (dev_ms / 1e3)
         h2d = per * 50 * 50 * 3 * 4 + per * 4
+        pretty = {"densenet121": "DenseNet-121", "vgg16": "VGG16", "mobilenet_v2": "MobileNetV2"}.get(args.model, args.model)
+        base = None
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline", "measured.json")) as fh:
+                base = json.load(fh).get(args.model, {}).get(str(n))
+        except Exception:  # noqa: BLE001
+            base = None
         out = {
-            "metric": "IDC patches/sec (DenseNet-121 training, fwd+bwd+RMSprop)",
+            "metric": f"IDC patches/sec ({pretty} training, fwd+bwd+RMSprop)",
             "value": round(value, 1), "unit": "patches/s", "n_gpus": n, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "impl": "ours",
+            "scaling": "weak", "vs_baseline": (round(value / base, 3) if base else None), "dtype": "bf16",
+            "data": "synthetic", "impl": "ours",
+            "baseline": ({"value": base, "what": "PyTorch DDP + NCCL + cuDNN, same model/batch/box (BASELINE.md section 3)"}
+                         if base else None),
             "config": {"model": args.model, "global_batch": gb, "per_gpu_batch": per,
-                       "image": "50x50x3", "seq_len": None, "parallelism": f"dp{n}", "comm": comm,
+                       "image": "50x50x3", "seq_len": None, "parallelism": f"dp{n}", "comm": comm, "comm_note": comm_note,
                        "optimizer": "rmsprop", "trainable": "all layers", "cuda_graph": ex.use_graphs,
                        "l2": "flushed between timed steps (256 MiB write)" if flush is not None else "not flushed",
                        "timing": "per-step CUDA events, summed, max over ranks"},

@@ -163,7 +163,7 @@ class FederatedAveragingProcess:
         k_local = max(k_counts)
         clients, weights, gbuf, gshadow = self._client_block(net, k_local)
         weights.tensor.zero_()
-        msum = torch.zeros(3, dtype=torch.float64)
+        msum = torch.zeros(3, dtype=torch.float64, device=net.device)   # accumulated on the device: no sync per step
         for k, ds in enumerate(mine):
             net.store.master.copy_(state.master)
             net.store.stats.copy_(state.stats)
@@ -177,16 +177,15 @@ class FederatedAveragingProcess:
             for x, y in ds:
                 stats, _ = net.executor.train_batch(x, y, x.shape[0])
                 net.optimizer.apply(1.0)
-                msum += stats.detach().to("cpu", torch.float64)
+                msum += stats.detach()[:3].to(torch.float64)
                 n_ex += int(x.shape[0])
             clients.tensor[k * n:(k + 1) * n].copy_(net.store.master)
             weights.tensor[k] = float(n_ex)
         ranges = net.store.ranges(net.trainable_layer_indices())
         new_master = self._aggregate(net, state, clients, weights, gbuf, gshadow, k_local, ranges)
         if world.is_distributed:
-            t = msum.to(net.device)
-            world.all_reduce_sum(t)
-            msum = t.cpu()
+            world.all_reduce_sum(msum)
+        msum = msum.cpu()
         cnt = max(float(msum[2]), 1.0)
         metrics = (float(msum[1]) / cnt, float(msum[0]) / cnt)
         return ServerState(new_master, state.stats.clone(), net), metrics

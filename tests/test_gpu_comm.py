@@ -120,3 +120,34 @@ def test_secagg_masked_sum_matches_host_oracle(world, k_local):
         # a single GPU's partial sum is still masked: it must not equal the plain quantised partial sum
         plain = np.rint(w[:k_local, off:off + n].astype(np.float64) * 65536).astype(np.int64).sum(0).astype(np.uint32)
         assert np.mean(ybuf[0].tensor.cpu().numpy().view(np.uint32)[:n] == plain) < 0.01
+
+
+def test_fused_secure_federation_single_gpu():
+    """8 resident clients train concurrently (one launch per step), aggregate through the masked ring sum and
+    adopt the mean; percent selects the protected tensor prefix (secure_fed_model.py:115-121)."""
+    from idc_models_b200.fed.secure_fused import FusedSecureFederation
+    from idc_models_b200.parallel.world import World
+    from idc_models_b200.workloads import create_small_cnn
+    world = World.from_env("cuda")
+    for percent, comm in ((1.0, "fused"), (0.5, "fused"), (0.0, "fused"), (1.0, "nccl")):
+        tpl = create_small_cnn(world.device, seed=0, lr=1e-3)
+        fed = FusedSecureFederation(world, 8, percent, template=tpl, batch_size=16, seed=1, comm=comm)
+        assert fed.n_protected_tensors == int(6 * percent)
+        g = torch.Generator(device="cuda").manual_seed(5)
+        for j in range(8):
+            fed.set_client_data(j, torch.rand(40, 10, 10, 3, device="cuda", generator=g),
+                                (torch.rand(40, device="cuda", generator=g) > 0.5).float())
+        before = fed.params.tensor[:8 * fed.stride].clone()
+        stats = fed.client_fit(2)
+        assert stats.shape == (8, 3) and torch.all(stats[:, 2] == 40)
+        after = fed.params.tensor[:8 * fed.stride].view(8, fed.stride)
+        assert not torch.equal(before.view(8, -1), after)            # every client moved ...
+        assert not torch.equal(after[0], after[1])                   # ... along its own data
+        want = after.double().mean(0).float()
+        got = fed.aggregate().clone()
+        torch.cuda.synchronize()
+        assert (got - want).abs().max().item() < 2.0 ** -15, (percent, comm)
+        fed.client_update()
+        assert torch.equal(fed.params.tensor[:fed.stride], got)
+        loss, acc = fed.evaluate(torch.rand(64, 10, 10, 3), (torch.rand(64) > 0.5).float(), steps=4)
+        assert 0.0 < loss < 5.0 and 0.0 <= acc <= 1.0

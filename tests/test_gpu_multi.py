@@ -68,3 +68,93 @@ def test_fused_allreduce_matches_nccl_path_across_processes():
         # NCCL ring order vs owner-computes order differ in fp32 rounding only
         assert abs(o["fused"][0] - o["nccl"][0]) < 1e-4 * max(1.0, abs(o["nccl"][1]))
     print("multicast (NVLS) used by the fused path:", outs[0]["fused"][2])
+
+
+FED_WORKER = r'''
+import sys, json, torch
+sys.path.insert(0, %r)
+from idc_models_b200.parallel.world import World
+from idc_models_b200.workloads import create_small_cnn
+from idc_models_b200.fed.secure_fused import FusedSecureFederation
+world = World.from_env()
+dev = world.device
+res = {}
+# ---- secure federation: fused kernel vs library path vs float mean, percent = 1.0 and 0.5 -----------------
+for percent in (1.0, 0.5):
+    outs = {}
+    for comm in ("fused", "nccl"):
+        tpl = create_small_cnn(dev, seed=0, lr=1e-3)
+        fed = FusedSecureFederation(world, 4 * world.size, percent, template=tpl, batch_size=16, seed=3, comm=comm)
+        g = torch.Generator(device=dev).manual_seed(10 + world.rank)
+        for j in range(fed.k_local):
+            fed.set_client_data(j, torch.rand(48, 10, 10, 3, device=dev, generator=g),
+                                (torch.rand(48, device=dev, generator=g) > 0.5).float())
+        fed.client_fit(1)
+        k, n = fed.k_local, fed.stride
+        local = fed.params.tensor[:k * n].view(k, n).double().sum(0)
+        world.all_reduce_sum(local)
+        want = (local / fed.n_clients).float()
+        got = fed.aggregate().clone()
+        torch.cuda.synchronize()
+        outs[comm] = ((got - want).abs().max().item(), got.double().sum().item())
+        fed.client_update()
+        assert torch.equal(fed.params.tensor[:n], fed.out.tensor[:n])
+    res["secure_%%s" %% percent] = outs
+# ---- FedAvg: fused kernel vs library aggregation on identical client blocks ---------------------------------
+from idc_models_b200.fed import fedavg as F
+from idc_models_b200.models.applications import build_transfer_model
+from idc_models_b200.optim.optimizers import RMSprop
+from idc_models_b200.parallel.strategy import FederatedStrategy
+strategy = FederatedStrategy(world)
+sums = {}
+for comm in ("fused", "nccl"):
+    def model_fn():
+        with strategy.scope():
+            m = build_transfer_model("mobilenet_v2_tiny", (50, 50, 3), 1, device=dev, seed=0)
+            m.base.trainable = True
+        return F.from_keras_model(m, loss="bce", metrics=["accuracy"])
+    fed = F.build_federated_averaging_process(model_fn, client_optimizer_fn=lambda: RMSprop(lr=1e-3), comm=comm)
+    g = torch.Generator(device=dev).manual_seed(50 + world.rank)
+    data = []
+    for cid in range(2 * world.size):
+        if cid %% world.size != world.rank:
+            data.append([]); continue
+        n_ex = 32 + 16 * (cid %% 3)          # unequal client weights
+        x = torch.rand(n_ex, 50, 50, 3, device=dev, generator=g); y = (torch.rand(n_ex, device=dev, generator=g) > 0.5).float()
+        data.append([(x[s:s + 16], y[s:s + 16]) for s in range(0, n_ex, 16)])
+    state = fed.initialize()
+    for _ in range(2):
+        state, metrics = fed.next(state, data)
+    torch.cuda.synchronize()
+    sums[comm] = (state.master.double().sum().item(), state.master.double().abs().sum().item(), metrics[1])
+res["fedavg"] = sums
+allres = world.all_gather_object(res)
+if world.rank == 0:
+    print("RESULT " + json.dumps(allres))
+world.barrier()
+world.shutdown()
+''' % str(ROOT)
+
+
+@pytest.mark.skipif(NGPU < 2, reason="needs at least 2 GPUs")
+def test_federated_kernels_across_processes():
+    """FedAvg weighted mean and the secure masked sum over NVLink peer memory: every rank receives the same
+    model; fused == library path; secure mean == float mean within the fixed-point step."""
+    script = ROOT / "build" / "_fed_worker.py"
+    script.parent.mkdir(exist_ok=True)
+    script.write_text(FED_WORKER)
+    n = min(NGPU, 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
+           "127.0.0.1", "--master-port", str(_free_port()), str(script)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-5000:]
+    outs = json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][7:])
+    print(outs[0])
+    for o in outs:
+        for key in ("secure_1.0", "secure_0.5"):
+            for comm in ("fused", "nccl"):
+                assert o[key][comm][0] < 2.0 ** -15, (key, comm, o[key][comm])
+                assert o[key][comm][1] == outs[0][key][comm][1], "ranks disagree on the aggregated model"
+        f, l = o["fedavg"]["fused"], o["fedavg"]["nccl"]
+        assert f[:2] == outs[0]["fedavg"]["fused"][:2], "ranks disagree on the FedAvg server model"
+        assert abs(f[0] - l[0]) < 1e-3 * max(1.0, l[1]), (f, l)
