@@ -102,6 +102,7 @@ def main() -> int:
     ap.add_argument("--comm", default="auto", help="auto|fused|nccl")
     ap.add_argument("--no-graph", action="store_true", help="launch kernels eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-l2-flush", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="launch the fused all-reduce after the backward pass instead of from inside it")
     args = ap.parse_args()
     if args.impl == "reference":
         return _reference_arm()
@@ -137,6 +138,7 @@ def main() -> int:
         comm = "fused" if n > 1 else "nccl"      # 1 GPU: no collective at all, plain optimizer kernel
     def build(comm_kind):
         strategy = MirroredStrategy(world=world, comm=comm_kind)
+        strategy.overlap = not args.no_overlap
         with strategy.scope():
             model = build_transfer_model(args.model, (50, 50, 3), 1, device=dev, seed=0)
             model.base.trainable = True          # full-model training, BatchNorm on batch statistics
@@ -236,6 +238,7 @@ def main() -> int:
                          if base else None),
             "config": {"model": args.model, "global_batch": gb, "per_gpu_batch": per,
                        "image": "50x50x3", "seq_len": None, "parallelism": f"dp{n}", "comm": comm, "comm_note": comm_note,
+                       "allreduce_overlapped_with_backward": bool(getattr(strategy, "_overlap", None)),
                        "optimizer": "rmsprop", "trainable": "all layers", "cuda_graph": ex.use_graphs,
                        "l2": "flushed between timed steps (256 MiB write)" if flush is not None else "not flushed",
                        "timing": "per-step CUDA events, summed, max over ranks"},

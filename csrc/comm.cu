@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(Allreduce
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
     // kU independent 16-byte reductions in flight per thread: the NVLink round trip (~2-4 us through
     // the switch) is hidden by memory-level parallelism, not by occupancy
-    constexpr int kU = 4;
+    constexpr int kU = 8;
     const long long tstride = (long long)gridDim.x * blockDim.x;
     for (long long i0 = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < hi; i0 += tstride * kU) {
       float4 gg[kU];
@@ -230,10 +230,11 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(Allreduce
         if (i >= hi) continue;
         const long long e = i << 2;
         float4 g = gg[u];
-        // this shard of every rank's bucket is consumed: re-zero it everywhere
-        if (a.mc_grad != nullptr) {
-            mc_st_f4(a.mc_grad + e, zero);
-        } else {
+        // The consumed bucket must be zero again before the next backward accumulates into it. With live
+        // barriers every rank clears its OWN bucket after the closing barrier (HBM speed, nothing on NVLink);
+        // broadcasting zeros from here would add (N-1)/N of the bucket to every GPU's inbound traffic.
+        // Only the single-process emulation (no barriers, ranks run one after another) clears per shard.
+        if (!pr.use_barrier) {
             for (int q = 0; q < pr.world; ++q) st_sys_f4(a.grad[(pr.rank + q) % pr.world] + e, zero);
         }
         g.x *= a.grad_scale; g.y *= a.grad_scale; g.z *= a.grad_scale; g.w *= a.grad_scale;
@@ -261,6 +262,10 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(Allreduce
     }
     // every rank must have received all shards (and had its bucket re-zeroed) before anyone goes on
     grid_and_world_barrier(pr, e0 + 2);
+    if (pr.use_barrier) {
+        float4* mine = reinterpret_cast<float4*>(a.grad[pr.rank]);
+        for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < (a.n >> 2); i += tstride) mine[i] = zero;
+    }
     store_epoch(pr, e0 + 2, pr.pad[pr.rank] + 18);
 }
 
@@ -437,10 +442,15 @@ static int fill_peers(Peers& pr, const idcb_comm_world* w) {
     return 0;
 }
 
+// Optional cap on the CTAs of the communication kernels (0 = one per SM). A bucket that is reduced while
+// the backward pass is still running should leave most SM issue slots and memory ports to the convolutions.
+static int g_comm_max_ctas = 0;
+
 static int comm_grid(long long n4, int world) {
     long long per = ceil_div_ll(n4, world);
     long long g = ceil_div_ll(per, kCommThreads);
-    const int cap = num_sms();    // persistent and co-resident: the in-kernel barriers need every CTA live
+    int cap = num_sms();    // persistent and co-resident: the in-kernel barriers need every CTA live
+    if (g_comm_max_ctas > 0 && g_comm_max_ctas < cap) cap = g_comm_max_ctas;
     if (g > cap) g = cap;
     if (g < 1) g = 1;
     return static_cast<int>(g);
@@ -449,6 +459,11 @@ static int comm_grid(long long n4, int world) {
 }  // namespace idcb
 
 using namespace idcb;
+
+extern "C" int idcb_comm_set_max_ctas(int max_ctas) {
+    g_comm_max_ctas = max_ctas > 0 ? max_ctas : 0;
+    return 0;
+}
 
 extern "C" int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad, void* const* master,
                                     void* const* shadow, void* mc_grad, void* mc_master, void* mc_shadow,

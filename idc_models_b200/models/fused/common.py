@@ -58,6 +58,35 @@ class FusedExecutor:
         self.use_graphs = False
         self.capturing = False
         self._graphs: dict = {}
+        # Set by a data-parallel strategy that overlaps the gradient all-reduce with the backward pass
+        # (parallel/fused_comm.py:OverlapSchedule): begin() / ready(offset) / end() / key().
+        self.grad_hook = None
+
+    # ---- gradient-readiness protocol (buckets leave while backward continues) -----------
+    def grad_ready_offsets(self) -> list:
+        """Flat-store offsets, in the order the backward pass reaches them, such that when offset ``o`` is
+        announced every parameter gradient at offsets >= ``o`` is final. Static per architecture (every
+        rank derives the same bucket plan from it, also a rank whose local batch is empty)."""
+        return []
+
+    def grads_ready(self, offset: int) -> None:
+        if self.grad_hook is not None and self._hook_live:
+            self.grad_hook.ready(int(offset))
+
+    _hook_live = False
+
+    def _run_hooked(self, plan, training: bool, grad_scale: float) -> None:
+        hook = self.grad_hook if training else None
+        if hook is None:
+            self.run(plan, training, grad_scale)
+            return
+        hook.begin()
+        self._hook_live = True
+        try:
+            self.run(plan, training, grad_scale)
+        finally:
+            self._hook_live = False
+        hook.end()
 
     # ---- trainable bookkeeping -----------------------------------------------------------------
     def prepare(self) -> None:
@@ -109,14 +138,16 @@ class FusedExecutor:
 
     def _execute(self, plan, training: bool, grad_scale: float) -> None:
         # frozen-layer BatchNorm folds are baked into a captured graph, so the key carries the
-        # external-write counter of the weights
-        key = (id(plan), training, grad_scale, self.net.store.ext_version)
+        # external-write counter of the weights (and the overlap schedule's frozen scalars)
+        hook = self.grad_hook if training else None
+        hk = hook.key() if hook is not None else None
+        key = (id(plan), training, grad_scale, self.net.store.ext_version, hk)
         if self.use_graphs:
             g = self._graphs.get(key)
             if g is None:
                 # warm-up run (module loading, function attributes), then capture
-                self.run(plan, training, grad_scale)
-                if training:
+                self._run_hooked(plan, training, grad_scale)
+                if training and hook is None:
                     self.net.store.grad.zero_()
                 torch.cuda.synchronize()
                 g = torch.cuda.CUDAGraph()
@@ -124,10 +155,15 @@ class FusedExecutor:
                 self.capturing = True
                 try:
                     with torch.cuda.graph(g):
-                        self.run(plan, training, grad_scale)
+                        self._run_hooked(plan, training, grad_scale)
                 finally:
                     self.capturing = False
                 self._graphs[key] = (g, _lib.launches() - n0)
+                if hook is not None:
+                    # the warm-up run WAS this step (it reduced the gradients and applied the optimizer on
+                    # every rank); the captured graph is first replayed by the next step
+                    hook.consumed = True
+                    return
                 if training:
                     self.net.store.grad.zero_()
                 g.replay()
@@ -136,7 +172,9 @@ class FusedExecutor:
             g[0].replay()
             _lib.count_launch(g[1])
         else:
-            self.run(plan, training, grad_scale)
+            self._run_hooked(plan, training, grad_scale)
+        if hook is not None:
+            hook.consumed = True
 
     def train_batch(self, x, y, global_batch: int):
         b = x.shape[0]

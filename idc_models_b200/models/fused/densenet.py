@@ -236,7 +236,24 @@ class DenseNetExecutor(FusedExecutor):
         K.bn_bwd_apply(2, blk.G, blk.buf, out, c_n, blk.count, sa=s1, sb=s2, mean=bn.mean[c_lo:c_lo + c_n],
                        rstd=bn.rstd[c_lo:c_lo + c_n], g_coff=c_lo, x_coff=c_lo)
 
+    def grad_ready_offsets(self) -> list:
+        """after dense block bi's backward, every gradient at or above the block's first parameter is final"""
+        net = self.net
+        st = net.store
+        offs = []
+        bi = 1
+        while True:
+            names = [pp.name for l in net.layers if l.spec.name.startswith(f"conv{bi + 1}_block1_") for pp in l.spec.params]
+            if not names:
+                break
+            offs.append(min(st.slots[n].offset for n in names))
+            bi += 1
+        self._block_offsets = offs            # index = dense block number (0-based)
+        return list(reversed(offs))
+
     def _backward(self, p) -> None:
+        if not hasattr(self, "_block_offsets"):
+            self.grad_ready_offsets()
         ft = self.first_trainable
         tr = self.trainable
         sc = p.scratch
@@ -299,6 +316,7 @@ class DenseNetExecutor(FusedExecutor):
                                   bwd_scale=bn0.scale, bwd_shift=bn0.shift, bwd_act=ACT_RELU, gacc=blk.G,
                                   stat_a=bn0.sa, stat_b=bn0.sb)
                 self._consumer_bn_backward(blk, bn0)
+            self.grads_ready(self._block_offsets[bi])
         # ---- stem ---------------------------------------------------------------------------------------
         if not p.stem_bwd:
             return

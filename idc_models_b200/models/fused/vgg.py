@@ -68,6 +68,12 @@ class ChainExecutor(FusedExecutor):
                 st["dy"] = torch.zeros_like(st["y"])
         return p
 
+    def grad_ready_offsets(self) -> list:
+        st = self.net.store
+        offs = [st.slots[l.spec.params[0].name].offset for l in self.net.layers
+                if l.spec.kind == "conv" and l.index in self.trainable]
+        return sorted(offs, reverse=True)
+
     def run(self, p, training: bool, grad_scale: float) -> None:
         net = self.net
         p.acc.zero_()
@@ -131,3 +137,5 @@ class ChainExecutor(FusedExecutor):
                                           stat_a=db)
                     else:
                         OC.conv_dgrad_raw(g, st["dy"], self.w16(wname), prev["dy"], mode=0)
+                # this layer's weight gradient and (written by its consumer earlier) bias gradient are final
+                self.grads_ready(self.net.store.slots[wname].offset)

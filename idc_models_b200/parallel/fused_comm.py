@@ -87,6 +87,104 @@ class FusedComm:
             scalars = None      # reduce the metric slots once, with the first range
         return self.scal_out if want_scalars else None
 
+    def allreduce_range(self, optimizer, b: int, e: int, grad_scale: float = 1.0) -> None:
+        """One launch over the flat range [b, e) with the optimizer's CURRENT scalars; no step bookkeeping
+        (used by :class:`OverlapSchedule`, which may run inside a captured graph)."""
+        if e <= b:
+            return
+        lr = optimizer._step_lr()
+        p1, p2, eps = optimizer._params()
+        lib = _lib.cuda_lib()
+        cw = self.alloc.comm_world()
+        mc = self.uses_multicast
+        s1, s2 = optimizer.s1, optimizer.s2
+        _lib.check(lib.idcb_allreduce_optim(
+            C.byref(cw), self.grad.ptrs(b), self.master.ptrs(b), self.shadow.ptrs(b),
+            self.grad.mc(b) if mc else vp(0), self.master.mc(b) if mc else vp(0),
+            self.shadow.mc(b) if mc else vp(0),
+            vp(s1.data_ptr() + 4 * b if s1 is not None else 0),
+            vp(s2.data_ptr() + 4 * b if s2 is not None else 0),
+            C.c_longlong(e - b), C.c_int(KIND[optimizer.kind]), C.c_float(lr), C.c_float(p1),
+            C.c_float(p2), C.c_float(eps), C.c_float(grad_scale), C.c_int(-1), None, vp(0), _lib.stream()))
+        _lib.count_launch()
+
+
+class OverlapSchedule:
+    """Bucketed launch of the fused all-reduce+optimizer kernel WHILE the backward pass runs (SURVEY 8.1,
+    7.2 step 5). The executor announces "every gradient at flat offset >= o is final" as its backward walks
+    down the network; each announcement that closes a planned bucket forks a side stream off the compute
+    stream (an event edge, also inside a captured CUDA graph), launches the kernel for that bucket there, and
+    the compute stream joins the side stream when the step ends. The bucket plan is derived from the
+    executor's static offset list, so every rank — also one whose local batch is empty — launches the same
+    kernels in the same order (the in-kernel barriers pair up launch by launch).
+
+    Hyper-parameters are kernel arguments and are therefore frozen into a captured graph: the schedule is
+    offered for optimizers whose per-step scalars do not change (SGD, RMSprop with a constant learning rate);
+    ``key()`` makes the executor re-capture if they do."""
+
+    def __init__(self, fused: FusedComm, optimizer, executor, grad_scale: float = 1.0,
+                 min_bucket: int = 1 << 19, max_ctas: int = 0):
+        self.fused, self.optimizer, self.grad_scale = fused, optimizer, float(grad_scale)
+        if optimizer.kind == "adam":
+            raise ValueError("overlap needs step-invariant optimizer scalars (Adam's bias correction changes per step)")
+        if len(optimizer.ranges) != 1:
+            raise ValueError("overlap needs one contiguous trainable range")
+        self.lo, self.hi = optimizer.ranges[0]
+        # plan: merge announcements until a bucket holds at least min_bucket elements
+        self.plan = []           # [(announce_offset, b, e)] in launch order
+        top = self.hi
+        for o in executor.grad_ready_offsets():
+            o = max(self.lo, min(int(o) & ~3, top))
+            if top - o >= min_bucket and o > self.lo:
+                self.plan.append((o, o, top))
+                top = o
+        self.plan.append((self.lo, self.lo, top))      # whatever is left goes when the backward is done
+        import os
+        self.overlap_ctas = int(os.environ.get("IDCB_OVERLAP_CTAS", "48"))
+        self.side = torch.cuda.Stream(device=fused.world.device, priority=-1)
+        self._next = 0
+        self._forked = False
+        self.consumed = False        # set by the executor once a training step has launched (or replayed) the buckets
+
+    def key(self):
+        o = self.optimizer
+        return (o.kind, o._step_lr(), o._params(), self.grad_scale, len(self.plan))
+
+    def begin(self) -> None:
+        self._next = 0
+        self._forked = False
+
+    def _launch(self, b: int, e: int, last: bool = False) -> None:
+        cur = torch.cuda.current_stream()
+        self.side.wait_stream(cur)                      # bucket's gradients are complete on the compute stream
+        lib = _lib.cuda_lib()
+        # buckets that run next to the backward kernels use few CTAs; the last one has the GPU to itself
+        lib.idcb_comm_set_max_ctas(C.c_int(0 if last else self.overlap_ctas))
+        with torch.cuda.stream(self.side):
+            self.fused.allreduce_range(self.optimizer, b, e, self.grad_scale)
+        lib.idcb_comm_set_max_ctas(C.c_int(0))
+        self._forked = True
+
+    def ready(self, offset: int) -> None:
+        while self._next < len(self.plan) - 1 and offset <= self.plan[self._next][0]:
+            _, b, e = self.plan[self._next]
+            self._launch(b, e)
+            self._next += 1
+
+    def end(self) -> None:
+        """launch what is left (at least the bottom bucket) and join the side stream"""
+        while self._next < len(self.plan):
+            _, b, e = self.plan[self._next]
+            self._launch(b, e, last=True)
+            self._next += 1
+        if self._forked:
+            torch.cuda.current_stream().wait_stream(self.side)
+
+    def run_all(self) -> None:
+        """a rank with an empty local batch: same launches, nothing to overlap with"""
+        self.begin()
+        self.end()
+
 
 def allreduce_apply_emulated(emu, rank_bufs, opt_states, n, kind, lr, p1, p2, eps, grad_scale, owner=-1) -> None:
     """Single-process emulation used by the 1-GPU tests: ``rank_bufs`` = dict(grad/master/shadow ->

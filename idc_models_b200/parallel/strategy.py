@@ -77,6 +77,16 @@ class Strategy:
             optimizer.apply(grad_scale)
             return
         if self.comm == "fused":
+            sched = getattr(self, "_overlap", None)
+            if sched is not None and sched.optimizer is optimizer:
+                # the kernels were launched from inside the backward pass (or are launched now, by a rank whose
+                # local batch was empty); only the host-side step bookkeeping is left
+                if not sched.consumed:
+                    sched.run_all()
+                sched.consumed = False
+                optimizer.iterations += 1
+                store.touch()
+                return
             self._fused_comm(store).allreduce_apply(optimizer, grad_scale)
             return
         for b, e in optimizer.ranges:
@@ -88,6 +98,29 @@ class Strategy:
             from .fused_comm import FusedComm
             self._fused = FusedComm(self.world, store)
         return self._fused
+
+    overlap = True      # fused path only: launch gradient buckets from inside the backward pass when possible
+    overlap_min_bucket = 1 << 19    # elements; smaller announcements are merged (launch + barrier latency per bucket)
+
+    def after_compile(self, net) -> None:
+        self._overlap = None
+        if self.overlap and self.comm == "fused":
+            self.enable_overlap(net, self.overlap_min_bucket)
+
+    def enable_overlap(self, net, min_bucket: int = 1 << 19) -> bool:
+        """Overlap the gradient all-reduce with the backward pass of ``net`` (compiled, fused executor).
+        Returns False (and changes nothing) where that is not possible."""
+        from .fused_comm import OverlapSchedule
+        ex = net.executor
+        if self.comm != "fused" or not self.world.is_distributed or not hasattr(ex, "grad_ready_offsets"):
+            return False
+        try:
+            sched = OverlapSchedule(self._fused_comm(net.store), net.optimizer, ex, 1.0, min_bucket)
+        except ValueError:
+            return False
+        self._overlap = sched
+        ex.grad_hook = sched
+        return True
 
     def prepare_store(self, store) -> None:
         """Called by ``compile`` before the optimizer and executor bind to the flat buffers: the fused

@@ -77,6 +77,12 @@ def compile_model(net, optimizer, loss, metrics) -> None:
     net.store.grad.zero_()
     net._dirty = False
     net.executor.prepare()
+    # a strategy may hook into the executor's backward pass (gradient all-reduce overlapped with it)
+    if hasattr(net.executor, "grad_hook"):
+        net.executor.grad_hook = None
+    after = getattr(net.strategy, "after_compile", None)
+    if after is not None:
+        after(net)
 
 
 def _check_compiled(net):
@@ -219,3 +225,8 @@ def rebind_optimizer(net, optimizer) -> None:
         opt = opt.clone()
     net.optimizer = opt.bind(net.store, net.store.ranges(net.trainable_layer_indices()))
     net.store.grad.zero_()
+    if hasattr(net.executor, "grad_hook"):
+        net.executor.grad_hook = None
+    after = getattr(net.strategy, "after_compile", None)
+    if after is not None:
+        after(net)              # an overlap schedule is tied to the optimizer object

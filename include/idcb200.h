@@ -265,6 +265,9 @@ int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad, void* cons
  *   global[offset:offset+n] += server_lr * sum_k n_k (w_k - global) / sum_k n_k        on every rank
  * idcb_fedavg_finite_flags zeroes the weight of a local client whose range holds a non-finite value
  * (TFF drops such a client's update). */
+/* Cap on the CTAs used by the communication kernels (0 = one per SM, the default). Used for gradient buckets
+ * that are reduced while the backward pass is still running (SURVEY 8.1 "tile by tile as buckets become ready"). */
+int idcb_comm_set_max_ctas(int max_ctas);
 int idcb_fedavg_finite_flags(const float* clients, long long stride, long long offset, long long n,
                              int k_local, float* weights, void* stream);
 int idcb_fedavg_reduce(const idcb_comm_world* w, void* const* clients, void* const* weights,
