@@ -76,6 +76,8 @@ def _common_flags(ap: argparse.ArgumentParser) -> None:
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--steps-per-epoch", type=int, default=None, help="cap the steps of every epoch (smoke runs)")
     ap.add_argument("--graphs", action="store_true", help="replay the fused step as a CUDA graph")
+    ap.add_argument("--native-loader", action="store_true",
+                    help="serve the cached training set from the C++ loader (threads + pinned ring + async H2D)")
 
 
 def _device(args) -> str:
@@ -151,7 +153,12 @@ def main_transfer(cfg: TransferConfig, argv: list) -> dict:
         train_ds = labeled_ds.take(TRAIN_SIZE)
         validation_ds = labeled_ds.skip(TRAIN_SIZE).take(VALIDATION_SIZE)
         test_ds = labeled_ds.skip(TRAIN_SIZE + VALIDATION_SIZE).take(TEST_SIZE)
-        train_batches = prepare_for_training(train_ds, BATCH_SIZE, seed=args.seed)
+        if args.native_loader:
+            from .data.loader import NativeLoader
+            train_batches = NativeLoader.from_dataset(train_ds, BATCH_SIZE, 1000, seed=args.seed,
+                                                      device=device if device.startswith("cuda") else None)
+        else:
+            train_batches = prepare_for_training(train_ds, BATCH_SIZE, seed=args.seed)
         validation_batches = prepare_for_training(validation_ds, BATCH_SIZE, seed=args.seed)
         test_batches = prepare_for_training(test_ds, BATCH_SIZE, seed=args.seed)  # built, never used (as upstream)
         del test_batches
