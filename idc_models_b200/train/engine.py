@@ -21,6 +21,7 @@ import time
 import torch
 
 from ..optim import optimizers as O
+from ..utils.trace import JsonlLogger, nvtx_range
 from . import losses as L
 from . import metrics as M
 
@@ -152,26 +153,34 @@ def fit(net, data, epochs, initial_epoch, validation_data, callbacks, verbose, s
         cb.set_model(net)
         cb.on_train_begin()
     net.stop_training = False
+    jlog = JsonlLogger(getattr(net, "log_jsonl", None), net.strategy.world.rank)
     for epoch in range(initial_epoch, epochs):
         t0 = time.time()
         for cb in callbacks:
             cb.on_epoch_begin(epoch)
         accum = _Accum(net)
         nb = 0
-        for x, y in _as_batches(data):
-            n = x.shape[0]
-            sl = net.strategy.local_slice(n)
-            xs, ys = x[sl], y[sl]
-            stats, logits = net.executor.train_batch(xs, ys, n)
-            net.strategy.reduce_and_apply(net.store, net.optimizer, 1.0)
-            accum.add(stats, logits, ys)
-            nb += 1
-            if steps_per_epoch is not None and nb >= steps_per_epoch:
-                break
+        seen = 0
+        with nvtx_range(f"epoch {epoch}"):
+            for x, y in _as_batches(data):
+                n = x.shape[0]
+                sl = net.strategy.local_slice(n)
+                xs, ys = x[sl], y[sl]
+                with nvtx_range("train_step"):
+                    stats, logits = net.executor.train_batch(xs, ys, n)
+                    net.strategy.reduce_and_apply(net.store, net.optimizer, 1.0)
+                accum.add(stats, logits, ys)
+                nb += 1
+                seen += n
+                if steps_per_epoch is not None and nb >= steps_per_epoch:
+                    break
         logs = accum.result()
+        dt = max(time.time() - t0, 1e-9)
         if validation_data is not None:
             logs.update(_evaluate(net, validation_data, validation_steps, prefix="val_"))
         hist._append(epoch, logs)
+        jlog.log("epoch", epoch=epoch, steps=nb, examples=seen, train_seconds=round(dt, 4),
+                 examples_per_s=round(seen / dt, 1), **{k: float(v) for k, v in logs.items()})
         for cb in callbacks:
             cb.on_epoch_end(epoch, logs)
         if verbose and net.strategy.world.rank == 0:

@@ -76,6 +76,7 @@ def _common_flags(ap: argparse.ArgumentParser) -> None:
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--steps-per-epoch", type=int, default=None, help="cap the steps of every epoch (smoke runs)")
     ap.add_argument("--graphs", action="store_true", help="replay the fused step as a CUDA graph")
+    ap.add_argument("--log-jsonl", default=None, help="append one JSON record per epoch / round to this file")
     ap.add_argument("--native-loader", action="store_true",
                     help="serve the cached training set from the C++ loader (threads + pinned ring + async H2D)")
 
@@ -174,6 +175,7 @@ def main_transfer(cfg: TransferConfig, argv: list) -> dict:
         model.compile(optimizer=RMSprop(lr=base_learning_rate), loss=loss(), metrics=["accuracy"])
     if args.graphs and device.startswith("cuda"):
         model.executor.use_graphs = True
+    model.log_jsonl = args.log_jsonl
 
     loss0, accuracy0 = model.evaluate(validation_batches, steps=args.validation_steps)
     with Timer("Pre-training with " + str(num_devices) + " devices"):
