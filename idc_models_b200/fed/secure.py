@@ -79,7 +79,15 @@ class Client:
 
     def __init__(self, data, num: int, p: float, *, model_fn, n_clients: int, batch_size: int = 32,
                  train_size: int | None = None, test_size: int | None = None, session_seed: int = 0,
-                 frac_bits: int = FRAC_BITS, prepare=None):
+                 frac_bits: int = FRAC_BITS, prepare=None, protect: str = "mask", keypair=None):
+        """``protect='mask'`` (default): pairwise masks in the fixed-point ring. ``protect='paillier'``: the
+        reference's own mechanism — element-wise Paillier ciphertexts under one shared ``keypair``
+        (secure_fed_model.py:79,109-121) — kept as the parity path; it is orders of magnitude slower."""
+        if protect not in ("mask", "paillier"):
+            raise ValueError("protect must be 'mask' or 'paillier'")
+        if protect == "paillier" and keypair is None:
+            raise ValueError("protect='paillier' needs the shared (public_key, private_key) pair")
+        self.protect, self.keypair = protect, keypair
         from ..data.dataset import prepare_for_training
         self.model = model_fn()
         prep = prepare or (lambda ds: prepare_for_training(ds, batch_size))
@@ -106,6 +114,11 @@ class Client:
         npro = self.n_protected(len(weights))
         if npro == 0:
             return out
+        if self.protect == "paillier":
+            enc = np.vectorize(self.keypair[0].encrypt, otypes=[object])     # secure_fed_model.py:109-110,117
+            for i in range(npro):
+                out[i] = enc(np.asarray(weights[i], np.float64))
+            return out
         flat = np.concatenate([np.asarray(w, np.float32).reshape(-1) for w in weights[:npro]])
         # the mask routine works on the full client matrix; build this client's row only
         mat = np.zeros((self.n_clients, flat.size), np.float32)
@@ -123,7 +136,10 @@ class Client:
         """Recover the mean of the protected tensors from the server's ring sums."""
         out = []
         for w in weights:
-            if isinstance(w, MaskedTensor):
+            if isinstance(w, np.ndarray) and w.dtype == object:
+                dec = np.vectorize(self.keypair[1].decrypt, otypes=[np.float64])   # secure_fed_model.py:112-113,121
+                out.append(dec(w).astype(np.float32))
+            elif isinstance(w, MaskedTensor):
                 if not w.is_sum:
                     raise ValueError("dec_model expects the server's aggregated ring sums")
                 out.append(dequantise_mean(w.values, w.n_clients, self.frac_bits).reshape(w.shape))
@@ -176,6 +192,13 @@ class Server:
         for tensors in zip(*client_weights):
             if isinstance(tensors[0], MaskedTensor):
                 ave.append(MaskedTensor(ring_sum([t.values for t in tensors]), tensors[0].shape, self.n_clients, True))
+            elif isinstance(tensors[0], np.ndarray) and tensors[0].dtype == object:
+                # ciphertext arrays: the reference's np.array(w).mean(axis=0) works because EncryptedNumber has
+                # + and scalar / (secure_fed_model.py:160-168); the server holds no key
+                acc = tensors[0]
+                for t in tensors[1:]:
+                    acc = acc + t
+                ave.append(acc / float(self.n_clients))
             else:
                 ave.append(np.mean(np.stack([np.asarray(t, np.float64) for t in tensors]), axis=0).astype(np.float32))
         return ave

@@ -345,10 +345,18 @@ def main_secure(argv: list) -> dict:
     ap.add_argument("--clients", type=int, default=2)
     ap.add_argument("--epochs", type=int, default=5)
     ap.add_argument("--verbose", type=int, default=1)
+    ap.add_argument("--protect", default="mask", choices=["mask", "paillier"],
+                    help="mask: pairwise Philox masks in a fixed-point ring (default); paillier: the reference's "
+                         "element-wise Paillier ciphertexts (parity path, slow)")
+    ap.add_argument("--paillier-bits", type=int, default=2048)
     args = ap.parse_args(argv)
     np.random.seed(0)
     device = _device(args)
     NUM_CLIENTS = args.clients
+    keypair = None
+    if args.protect == "paillier":
+        from .fed.paillier import generate_paillier_keypair
+        keypair = generate_paillier_keypair(args.paillier_bits)      # one pair shared by all clients (upstream :79)
     DATASET_SIZE = args.dataset_size or 30000
     TRAIN_SIZE = int(0.8 * DATASET_SIZE)
     TEST_SIZE = int(0.2 * DATASET_SIZE)
@@ -368,7 +376,7 @@ def main_secure(argv: list) -> dict:
     def create_clients(all_data, client_ids, percent):
         return [Client(all_data.shard(NUM_CLIENTS, int(i)), int(i), percent, model_fn=model_fn, n_clients=NUM_CLIENTS,
                        batch_size=BATCH_SIZE, train_size=CLIENT_TRAIN_SIZE, test_size=CLIENT_TEST_SIZE,
-                       session_seed=args.seed) for i in client_ids]
+                       session_seed=args.seed, protect=args.protect, keypair=keypair) for i in client_ids]
 
     clients = create_clients(client_data, np.arange(NUM_CLIENTS), args.percent)
     server = Server(NUM_CLIENTS)

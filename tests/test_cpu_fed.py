@@ -96,3 +96,46 @@ def test_percent_selects_the_tensor_prefix_and_round_trip_matches_float_mean():
         assert np.abs(a - b).max() < 1e-4
     with pytest.raises(RuntimeError):
         secure.Server(3).aggregate(sent[:2])          # a missing client must abort the round
+
+
+def test_paillier_homomorphic_mean_matches_float_mean():
+    """the reference's protection mechanism (secure_fed_model.py:79,109-121,160-168) restated on Python ints"""
+    import numpy as np
+    from idc_models_b200.fed.paillier import generate_paillier_keypair
+    pk, sk = generate_paillier_keypair(512, seed=1)
+    a, b, c = 0.37251, -1.25, 3.0e-4
+    ea, eb, ec = pk.encrypt(a), pk.encrypt(b), pk.encrypt(c)
+    assert abs(sk.decrypt(ea) - a) < 1e-9 and abs(sk.decrypt(eb) - b) < 1e-9
+    assert abs(sk.decrypt(ea + eb) - (a + b)) < 1e-9
+    assert abs(sk.decrypt((ea + eb + ec) / 3) - (a + b + c) / 3) < 1e-9
+    assert abs(sk.decrypt(ea * -2.5) - a * -2.5) < 1e-9
+    assert ea.c != pk.encrypt(a).c                                  # probabilistic encryption
+    # object arrays, as Client.enc_model / Server.aggregate use them
+    w1, w2 = np.random.RandomState(0).randn(3, 2), np.random.RandomState(1).randn(3, 2)
+    enc = np.vectorize(pk.encrypt, otypes=[object])
+    dec = np.vectorize(sk.decrypt, otypes=[np.float64])
+    assert np.allclose(dec((enc(w1) + enc(w2)) / 2.0), (w1 + w2) / 2, atol=1e-9)
+
+
+def test_secure_clients_paillier_path_equals_mask_path():
+    import numpy as np
+    from idc_models_b200.fed.paillier import generate_paillier_keypair
+    from idc_models_b200.fed.secure import Client, Server
+    from idc_models_b200.data.dataset import Dataset
+    kp = generate_paillier_keypair(512, seed=2)
+    rs = np.random.RandomState(0)
+    weights = [[rs.randn(2, 3).astype(np.float32), rs.randn(3).astype(np.float32), rs.randn(4).astype(np.float32)]
+               for _ in range(3)]
+    ds = Dataset.from_tensor_slices((np.zeros((4, 2, 2, 3), np.float32), np.zeros(4, np.float32)))
+    results = {}
+    for protect in ("mask", "paillier"):
+        clients = [Client(ds, i, 0.67, model_fn=lambda: None, n_clients=3, protect=protect, keypair=kp) for i in range(3)]
+        assert clients[0].n_protected(3) == 2
+        updates = [c.enc_model(weights[i]) for i, c in enumerate(clients)]
+        assert not isinstance(updates[0][2], np.ndarray) or updates[0][2].dtype != object     # third tensor in the clear
+        ave = Server(3).aggregate(updates)
+        results[protect] = clients[1].dec_model(ave)
+    want = [np.mean([w[i] for w in weights], axis=0) for i in range(3)]
+    for got in results.values():
+        for g, w in zip(got, want):
+            assert np.allclose(g, w, atol=2e-5)
