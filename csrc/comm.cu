@@ -270,6 +270,49 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(Allreduce
 }
 
 // =====================================================================================================
+// BatchNorm moving statistics: MEAN over replicas when they are read (checkpoint / evaluate). Under
+// MirroredStrategy they are ON_READ variables: every replica updates its own copy from its own batches and
+// the copies are averaged on read. Owner-computes like the kernels above: rank r
+// averages its 1/N of the buffer out of every peer and writes the result back into every peer.
+// =====================================================================================================
+struct StatMeanArgs {
+    Peers pr;
+    float* stats[kMaxWorld];
+    float* mc;
+    long long n;
+};
+
+__global__ void __launch_bounds__(kCommThreads) stat_mean_kernel(StatMeanArgs a) {
+    const Peers& pr = a.pr;
+    const uint32_t e0 = load_epoch(pr);
+    grid_and_world_barrier(pr, e0 + 1);
+    long long lo, hi;
+    shard_bounds(a.n >> 2, pr.world, pr.rank, lo, hi);
+    const float inv = 1.f / static_cast<float>(pr.world);
+    const long long tstride = (long long)gridDim.x * blockDim.x;
+    for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi; i += tstride) {
+        const long long e = i << 2;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (a.mc != nullptr) {
+            acc = mc_ld_reduce_f4(a.mc + e);
+        } else {
+            for (int q = 0; q < pr.world; ++q) {
+                const float4 v = ld_sys_f4(a.stats[(pr.rank + q) % pr.world] + e);
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+        }
+        acc.x *= inv; acc.y *= inv; acc.z *= inv; acc.w *= inv;
+        if (a.mc != nullptr) {
+            mc_st_f4(a.mc + e, acc);
+        } else {
+            for (int q = 0; q < pr.world; ++q) st_sys_f4(a.stats[(pr.rank + q) % pr.world] + e, acc);
+        }
+    }
+    grid_and_world_barrier(pr, e0 + 2);
+    store_epoch(pr, e0 + 2, pr.pad[pr.rank] + 18);
+}
+
+// =====================================================================================================
 // K16: FedAvg  w <- w + lr_s * sum_k n_k (w_k - w) / sum_k n_k     over all clients on all GPUs
 // =====================================================================================================
 struct FedAvgArgs {
@@ -493,6 +536,23 @@ extern "C" int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad,
     a.lr = lr; a.p1 = p1; a.p2 = p2; a.eps = eps; a.grad_scale = grad_scale;
     if (n == 0) return 0;
     allreduce_optim_kernel<<<comm_grid(n / 4, w->world), kCommThreads, 0, (cudaStream_t)stream>>>(a);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_stat_mean(const idcb_comm_world* w, void* const* stats, void* mc_stats, long long n,
+                              void* stream) {
+    StatMeanArgs a{};
+    if (fill_peers(a.pr, w)) return 1;
+    IDCB_REQUIRE(n % 4 == 0, "stat_mean: length must be a multiple of 4");
+    for (int p = 0; p < w->world; ++p) {
+        a.stats[p] = static_cast<float*>(stats[p]);
+        IDCB_REQUIRE(a.stats[p] != nullptr, "stat_mean: null peer pointer for rank %d", p);
+    }
+    a.mc = static_cast<float*>(mc_stats);
+    a.n = n;
+    if (n == 0) return 0;
+    stat_mean_kernel<<<comm_grid(n / 4, w->world), kCommThreads, 0, (cudaStream_t)stream>>>(a);
     IDCB_LAUNCH_CHECK();
     return 0;
 }

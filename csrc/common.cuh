@@ -122,6 +122,10 @@ __device__ __forceinline__ void mbar_wait_s(uint32_t bar, uint32_t parity) {
         if (++spins == (1u << 30)) __trap();
     }
 }
+// 16-byte fire-and-forget fp32 vector reduction into global memory (REDG.E.ADD.F32x4)
+__device__ __forceinline__ void red_add_f32x4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
     uint4 v;
     asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr)

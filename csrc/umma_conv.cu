@@ -5,19 +5,20 @@
 //   idcb_conv_dgrad : dx = epilogue( conv^T( dy, W ) )            (stride 1 only)
 //   idcb_conv_wgrad : dW += prologue(x)^T (*) dy                   (split over positions)
 //
-// Data flow per CTA (320 threads):
-//   warps 0-7  : A-operand producers. They gather the im2col rows straight from global memory
-//                (zero padding, channel-prefix views of a DenseNet concat buffer, and the fused
-//                BatchNorm scale/shift + ReLU/ReLU6 prologue happen here, in registers), write the
-//                128-byte-swizzled operand tile into shared memory, fence it to the async proxy and
-//                arrive on the stage's "full" mbarrier. The loads of k-block i+1 are issued before
-//                k-block i is transformed and stored, so two k-blocks of global traffic are in flight
-//                per CTA. After the main loop the same eight warps are the epilogue: tcgen05.ld the fp32
-//                accumulators out of TMEM (warp w owns TMEM lanes 32*(w%4).. and column half w/4),
-//                apply the fused epilogue and store.
-//   warp 8     : TMA producer for the second operand (weights, or dy for wgrad).
-//   warp 9     : allocates TMEM, then one lane issues tcgen05.mma (UMMA 128 x N x 16, bf16 -> fp32)
-//                and tcgen05.commit to recycle the stage / publish the accumulator.
+// Data flow per CTA:
+//   warps 0-7  : workers. dgrad: issue the asynchronous copies (cp.async, zero-fill for padding) of the
+//                im2col rows straight into the 128-byte-swizzled operand tile. fprop / wgrad with a BatchNorm
+//                scale/shift + ReLU/ReLU6 prologue: read raw chunks from a staging ring, apply the prologue in
+//                registers, store the operand tile and arrive on the stage's "full" mbarrier. After the main
+//                loop the same eight warps are the epilogue: tcgen05.ld the fp32 accumulators out of TMEM
+//                (warp w owns TMEM lanes 32*(w%4).. and column half w/4), apply the fused epilogue and store.
+//   warps 8-11 : (fprop, wgrad) loaders: nothing but cp.async + cp.async.mbarrier.arrive, into the operand
+//                tile (no prologue) or the raw ring (prologue). No thread that waits, fences or release-arrives
+//                ever owns copies in flight (see GemmCfg).
+//   next warp  : TMA producer for the second operand (weights, or dy for wgrad).
+//   last warp  : allocates TMEM, then one lane issues the generic->async proxy fence, tcgen05.mma
+//                (UMMA 128 x N x 16, bf16 -> fp32) and tcgen05.commit to recycle the stage / publish the
+//                accumulator.
 //
 // The problems of this workload are tiny (DenseNet-121 at 50x50: M = 128..21632 rows, K = 64..1152),
 // so a CTA lives for a few microseconds and what matters is the length of the per-thread dependent
@@ -43,11 +44,6 @@ namespace idcb {
 constexpr int kBM = 128;      // UMMA M (rows of the accumulator = TMEM lanes)
 constexpr int kBK = 64;       // K elements per pipeline stage (one 128-byte swizzle row)
 constexpr int kMaxStages = 8;
-constexpr int kWorkers = 256;  // 8 producer / epilogue warps
-constexpr int kThreads = kWorkers + 64;
-constexpr int kTmaWarp = 8, kMmaWarp = 9;
-constexpr int kFullArrivalsPro = 8 + 1;          // transform path: one arrival per producer warp + the TMA thread
-constexpr int kFullArrivalsCp = kWorkers + 1;    // copy path: every producer thread's cp.async arrival + TMA
 constexpr int kRaw = 4;                          // k-blocks of raw activations in flight per CTA (transform path)
 constexpr int kBarBytes = 256;                    // barrier block: full/empty/acc/raw_full/raw_empty + TMEM slot
 constexpr int kRawBytes = kBM * 128;             // one k-block of raw 16-byte chunks, [chunk row i][thread]
@@ -191,9 +187,11 @@ __device__ __forceinline__ void load_row_bf16(const __nv_bfloat16* rowptr, bool 
 }
 
 // One kW-column slab of the fused epilogue for the row owned by this thread.
+// es_scale / es_shift (mode 2): the consumer's forward scale/shift for this slab's columns, staged in shared
+// memory by the CTA (zero beyond Cout).
 template <int kEpi, int kW>
 __device__ __forceinline__ void epilogue_slab(const ConvArgs& p, uint32_t taddr, int m, bool mvalid,
-                                              int nb, int lane) {
+                                              int nb, int lane, const float* es_scale, const float* es_shift) {
     float vv[kW];
     tmem_ld_cols<kW>(taddr, vv);
     float xr[kW];
@@ -226,13 +224,16 @@ __device__ __forceinline__ void epilogue_slab(const ConvArgs& p, uint32_t taddr,
         for (int e = 0; e < kW; ++e) vv[e] = xr[e] > 0.f ? vv[e] : 0.f;
     } else {
         // BN + activation backward: dpre = acc * act'(scale*x + shift); xr becomes the G scale
+        const int act = p.bwd_act;
 #pragma unroll
-        for (int e = 0; e < kW; ++e) {
-            const bool nv = nb + e < p.Cout;
-            const float gs = nv ? __ldg(p.bwd_scale + nb + e) : 0.f;
-            const float gh = nv ? __ldg(p.bwd_shift + nb + e) : 0.f;
-            const float pre = fmaf(gs, xr[e], gh);
-            vv[e] = nv ? vv[e] * act_mask(pre, p.bwd_act) : 0.f;
+        for (int g4 = 0; g4 < kW / 4; ++g4) {
+            const float4 gs = *reinterpret_cast<const float4*>(es_scale + g4 * 4);
+            const float4 gh = *reinterpret_cast<const float4*>(es_shift + g4 * 4);
+            // columns beyond Cout carry scale = shift = 0 and a zero accumulator (zero-filled weight tile)
+            vv[g4 * 4 + 0] *= act_mask(fmaf(gs.x, xr[g4 * 4 + 0], gh.x), act);
+            vv[g4 * 4 + 1] *= act_mask(fmaf(gs.y, xr[g4 * 4 + 1], gh.y), act);
+            vv[g4 * 4 + 2] *= act_mask(fmaf(gs.z, xr[g4 * 4 + 2], gh.z), act);
+            vv[g4 * 4 + 3] *= act_mask(fmaf(gs.w, xr[g4 * 4 + 3], gh.w), act);
         }
     }
     uint32_t packed[kW / 2];
@@ -260,12 +261,11 @@ __device__ __forceinline__ void epilogue_slab(const ConvArgs& p, uint32_t taddr,
 #pragma unroll
         for (int g = 0; g < kW / 4; ++g) {
             if (nb + g * 4 < p.Cout) {
-                float4 q = *reinterpret_cast<float4*>(grow + g * 4);
-                q.x = fmaf(__ldg(p.bwd_scale + nb + g * 4 + 0), vv[g * 4 + 0], q.x);
-                q.y = fmaf(__ldg(p.bwd_scale + nb + g * 4 + 1), vv[g * 4 + 1], q.y);
-                q.z = fmaf(__ldg(p.bwd_scale + nb + g * 4 + 2), vv[g * 4 + 2], q.z);
-                q.w = fmaf(__ldg(p.bwd_scale + nb + g * 4 + 3), vv[g * 4 + 3], q.w);
-                *reinterpret_cast<float4*>(grow + g * 4) = q;
+                // fire-and-forget vector reduction: no load of G, nothing to wait for (each element of G is
+                // touched once per kernel, so the result does not depend on arrival order)
+                const float4 gs = *reinterpret_cast<const float4*>(es_scale + g * 4);
+                red_add_f32x4(grow + g * 4, gs.x * vv[g * 4 + 0], gs.y * vv[g * 4 + 1], gs.z * vv[g * 4 + 2],
+                              gs.w * vv[g * 4 + 3]);
             }
         }
     }
@@ -431,7 +431,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     uint64_t* raw_full = acc_bar + 2;
     uint64_t* raw_empty = raw_full + kRaw;
     float* s_scale = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full_bar) + kBarBytes);
-    float* s_shift = s_scale + ((p.Cin + 3) & ~3);
+    float* s_shift = s_scale + (kEpi == 2 ? 128 : ((p.Cin + 3) & ~3));
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -475,6 +475,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         for (int c = threadIdx.x; c < p.Cin; c += kNT) {
             s_scale[c] = p.pro_scale[c];
             s_shift[c] = p.pro_shift[c];
+        }
+    }
+    if (kEpi == 2) {
+        // the consumer's forward scale/shift for this CTA's columns (BN + activation backward in the epilogue)
+        for (int c = threadIdx.x; c < kBN; c += kNT) {
+            const bool nv = n0 + c < p.Cout;
+            s_scale[c] = nv ? p.bwd_scale[n0 + c] : 0.f;
+            s_shift[c] = nv ? p.bwd_shift[n0 + c] : 0.f;
         }
     }
     tc_fence_before();
@@ -592,7 +600,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         for (int cc = half * kHalf; cc < (half + 1) * kHalf; cc += kW) {
             const int nb = n0 + cc;
             if (nb >= p.Cout) break;  // warp-uniform
-            epilogue_slab<kEpi, kW>(p, t_row + cc, m, mvalid, nb, lane);
+            epilogue_slab<kEpi, kW>(p, t_row + cc, m, mvalid, nb, lane, s_scale + cc, s_shift + cc);
         }
         tc_fence_before();
         // Publication of the BatchNorm coefficients for the backward pass + moving-statistics update: one CTA,
@@ -742,22 +750,86 @@ struct WgradArgs {
     int stages;
 };
 
+// One thread's share of the wgrad A operand: 16-byte chunk j16 (8 of the tile's 128 linearised (tap, cin) columns,
+// fixed for the thread) of positions rb + i * kStep (i < kR) of every 64-position k-block. A cursor per row —
+// (ho, wo), position index and the element offset of the input pixel this thread's tap reads — advances by 64
+// positions per k-block with two carries: no divisions and no coordinate rebuild in the main loop.
+template <int kR, int kStep>
+struct WgradRows {
+    int r_ho[kR], r_wo[kR], r_off[kR], r_m[kR];
+    int s_ho, s_wo, step_off, wrapw_off, wraph_off, ch, cw, st;
+    bool cvalid;
+
+    __device__ __forceinline__ void init(const WgradArgs& p, int kb_begin, int rb, int tap, int c, bool cv) {
+        const int hw = p.Ho * p.Wo;
+        const int kh = fdiv(tap, p.d_kw);
+        const int kw = tap - kh * p.KW;
+        const int s_b = 64 / hw;
+        s_ho = (64 - s_b * hw) / p.Wo;
+        s_wo = 64 - s_b * hw - s_ho * p.Wo;
+        st = p.stride;
+        step_off = ((s_b * p.H + s_ho * st) * p.W + s_wo * st) * p.x_pitch;
+        wrapw_off = (st * p.W - p.Wo * st) * p.x_pitch;
+        wraph_off = (p.H * p.W - p.Ho * st * p.W) * p.x_pitch;
+        ch = kh - p.pad_t;
+        cw = kw - p.pad_l;
+        cvalid = cv;
+#pragma unroll
+        for (int i = 0; i < kR; ++i) {
+            const int m = kb_begin * 64 + i * kStep + rb;
+            const int b = fdiv(m, p.d_hw);
+            const int rem = m - b * hw;
+            r_ho[i] = fdiv(rem, p.d_wo);
+            r_wo[i] = rem - r_ho[i] * p.Wo;
+            r_m[i] = m;
+            r_off[i] = ((b * p.H + r_ho[i] * st + ch) * p.W + r_wo[i] * st + cw) * p.x_pitch + p.x_coff + c;
+        }
+    }
+    // validity mask of the next k-block's rows (bit i) and their element offsets; advances the cursor
+    __device__ __forceinline__ uint32_t next(const WgradArgs& p, int (&off)[kR]) {
+        uint32_t okmask = 0;
+#pragma unroll
+        for (int i = 0; i < kR; ++i) {
+            const unsigned hi = static_cast<unsigned>(r_ho[i] * st + ch);
+            const unsigned wi = static_cast<unsigned>(r_wo[i] * st + cw);
+            const bool ok = cvalid && r_m[i] < p.M && hi < static_cast<unsigned>(p.H) && wi < static_cast<unsigned>(p.W);
+            if (ok) okmask |= 1u << i;
+            off[i] = r_off[i];
+            r_m[i] += 64;
+            r_wo[i] += s_wo;
+            r_ho[i] += s_ho;
+            r_off[i] += step_off;
+            if (r_wo[i] >= p.Wo) { r_wo[i] -= p.Wo; ++r_ho[i]; r_off[i] += wrapw_off; }
+            if (r_ho[i] >= p.Ho) { r_ho[i] -= p.Ho; r_off[i] += wraph_off; }
+        }
+        return okmask;
+    }
+};
+
+// Thread layout (see conv_gemm_kernel): warps 0-7 workers (prologue transform + epilogue), warps 8-11 loaders
+// (asynchronous copies only), warp 12 TMA (dy tiles), warp 13 MMA.
+constexpr int kWgWork = 256, kWgLoad = 128, kWgThreads = kWgWork + kWgLoad + 64;
+constexpr int kWgTmaWarp = (kWgWork + kWgLoad) / 32, kWgMmaWarp = kWgTmaWarp + 1;
+
 template <int kBN>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kWgThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ WgradArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     constexpr int kBTile = ((kBN + 63) / 64) * 8192;
+    constexpr int kTmaWarp = kWgTmaWarp, kMmaWarp = kWgMmaWarp;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
     const int nstages = p.stages;
     uint8_t* a_tiles = smem;  // [64 pos][128 k'] as two 8 KiB chunks
     uint8_t* b_tiles = smem + nstages * kATileBytes;
     const bool has_pro = p.pro_scale != nullptr;
-    uint8_t* raw_tiles = b_tiles + nstages * kBTile;   // staging ring, present only with a prologue
+    uint8_t* raw_tiles = b_tiles + nstages * kBTile;   // raw staging ring, present only with a prologue
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(raw_tiles + (has_pro ? kRaw * kRawBytes : 0));
     uint64_t* empty_bar = full_bar + kMaxStages;
     uint64_t* acc_bar = empty_bar + kMaxStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_bar + 1);
+    uint64_t* raw_full = acc_bar + 2;
+    uint64_t* raw_empty = raw_full + kRaw;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -773,10 +845,16 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nstages; ++s) {
-            mbar_init(&full_bar[s], has_pro ? kFullArrivalsPro : kFullArrivalsCp);
+            mbar_init(&full_bar[s], has_pro ? kWgWork / 32 + 1 : kWgLoad + 1);
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(acc_bar, 1);
+        if (has_pro) {
+            for (int s = 0; s < kRaw; ++s) {
+                mbar_init(&raw_full[s], kWgLoad);
+                mbar_init(&raw_empty[s], kWgWork / 32);
+            }
+        }
         mbar_fence_init();
     }
     if (warp == kTmaWarp && lane == 0) tma_prefetch_desc(&tmap_dy);
@@ -791,135 +869,99 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         return;
     }
 
-    if (warp < 8) {
-        // ---- A producers: 16 threads cover one position row (128 k' = 256 B) ----
-        const int j16 = threadIdx.x & 15;
+    if (warp < kWgTmaWarp) {
+        // ---- A side: 16 threads cover one position row (128 k' = 256 B); workers own rows rb + 16 i, loaders rb + 8 i
+        const bool is_loader = warp >= kWgWork / 32;
+        const int t = is_loader ? threadIdx.x - kWgWork : threadIdx.x;
+        const int j16 = t & 15;
         const int half = j16 >> 3;  // which 64-wide chunk
         const int j = j16 & 7;
-        const int rbase = threadIdx.x >> 4;  // 0..15
+        const int rbase = t >> 4;   // workers 0..15, loaders 0..7
         const int kidx = k0 + j16 * 8;
         const bool cvalid = kidx < ktot;
         const int tap = cvalid ? fdiv(kidx, p.d_cin) : 0;
         const int c = cvalid ? kidx - tap * p.Cin : 0;
-        const int kh = fdiv(tap, p.d_kw);
-        const int kw = tap - kh * p.KW;
-        float4 s0 = make_float4(1.f, 1.f, 1.f, 1.f), s1 = s0;
-        float4 h0 = make_float4(0.f, 0.f, 0.f, 0.f), h1 = h0;
-        if (has_pro && cvalid) {
-            s0 = make_float4(p.pro_scale[c], p.pro_scale[c + 1], p.pro_scale[c + 2], p.pro_scale[c + 3]);
-            s1 = make_float4(p.pro_scale[c + 4], p.pro_scale[c + 5], p.pro_scale[c + 6], p.pro_scale[c + 7]);
-            h0 = make_float4(p.pro_shift[c], p.pro_shift[c + 1], p.pro_shift[c + 2], p.pro_shift[c + 3]);
-            h1 = make_float4(p.pro_shift[c + 4], p.pro_shift[c + 5], p.pro_shift[c + 6], p.pro_shift[c + 7]);
-        }
-        // Position cursor per row: (ho, wo) of the output position, the element offset of the input
-        // pixel this thread's tap reads for it, and the position index. One k-block = 64 positions, so the
-        // cursor advances by a fixed (images, rows, columns) step with two carries — no divisions and no
-        // coordinate rebuild per k-block.
-        const int hw = p.Ho * p.Wo;
-        const int s_b = 64 / hw, s_ho = (64 - s_b * hw) / p.Wo, s_wo = 64 - s_b * hw - s_ho * p.Wo;
-        const int step_off = ((s_b * p.H + s_ho * p.stride) * p.W + s_wo * p.stride) * p.x_pitch;
-        const int wrapw_off = (p.stride * p.W - p.Wo * p.stride) * p.x_pitch;
-        const int wraph_off = (p.H * p.W - p.Ho * p.stride * p.W) * p.x_pitch;
-        const int ch = kh - p.pad_t, cw = kw - p.pad_l;
-        int r_ho[4], r_wo[4], r_off[4], r_m[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int m = kb_begin * 64 + i * 16 + rbase;
-            const int b = fdiv(m, p.d_hw);
-            const int rem = m - b * hw;
-            r_ho[i] = fdiv(rem, p.d_wo);
-            r_wo[i] = rem - r_ho[i] * p.Wo;
-            r_m[i] = m;
-            r_off[i] = ((b * p.H + r_ho[i] * p.stride + ch) * p.W + r_wo[i] * p.stride + cw) * p.x_pitch + p.x_coff + c;
-        }
-        const int st = p.stride;
-        // asynchronous copies of this thread's 4 chunks of the next k-block to dst0 + i * dstride
-        auto issue = [&](uint32_t dst0, uint32_t dstride) -> uint32_t {
-            uint32_t okmask = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const unsigned hi = static_cast<unsigned>(r_ho[i] * st + ch);
-                const unsigned wi = static_cast<unsigned>(r_wo[i] * st + cw);
-                const bool ok = cvalid && r_m[i] < p.M && hi < static_cast<unsigned>(p.H) && wi < static_cast<unsigned>(p.W);
-                if (ok) okmask |= 1u << i;
-                cp_async16(dst0 + i * dstride, ok ? static_cast<const void*>(p.x + r_off[i]) : static_cast<const void*>(p.x),
-                           ok ? 16u : 0u);
-                // advance this row's cursor by 64 positions
-                r_m[i] += 64;
-                r_wo[i] += s_wo;
-                r_ho[i] += s_ho;
-                r_off[i] += step_off;
-                if (r_wo[i] >= p.Wo) { r_wo[i] -= p.Wo; ++r_ho[i]; r_off[i] += wrapw_off; }
-                if (r_ho[i] >= p.Ho) { r_ho[i] -= p.Ho; r_off[i] += wraph_off; }
-            }
-            return okmask;
-        };
-        int stage = 0;
-        uint32_t phase = 0;
-        const uint32_t a_base = smem_u32(a_tiles) + half * 8192 + sw128_offset(rbase, j);   // row i adds i * 2048
+        const uint32_t tile_off = half * 8192 + sw128_offset(rbase, j);
         const uint32_t full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
-        if (!has_pro) {
-            // copy path (see conv_gemm_kernel): chunks land directly in the operand tile
-            for (int kb = kb_begin; kb < kb_end; ++kb) {
-                if (kb - kb_begin >= nstages) mbar_wait_s(empty0 + stage * 8, phase ^ 1);
-                issue(a_base + stage * kATileBytes, 2048);
-                cp_async_mbar_arrive(full0 + stage * 8);
-                if (++stage == nstages) {
-                    stage = 0;
+        const uint32_t rfull0 = smem_u32(raw_full), rempty0 = smem_u32(raw_empty);
+        if (is_loader) {
+            // ===================== loaders: asynchronous copies only =====================
+            WgradRows<8, 8> rows;
+            rows.init(p, kb_begin, rbase, tap, c, cvalid);
+            const uint32_t dst_base = smem_u32(has_pro ? raw_tiles : a_tiles) + tile_off;   // row i adds i * 1024
+            const uint32_t slot_bytes = has_pro ? kRawBytes : kATileBytes;
+            const int ring = has_pro ? kRaw : nstages;
+            const uint32_t ready0 = has_pro ? rfull0 : full0, free0 = has_pro ? rempty0 : empty0;
+            int slot = 0;
+            uint32_t phase = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                if (kb >= ring) mbar_wait_s(free0 + slot * 8, phase ^ 1);
+                int off[8];
+                const uint32_t ok = rows.next(p, off);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const bool v = (ok >> i) & 1u;
+                    cp_async16(dst_base + slot * slot_bytes + i * 1024, p.x + (v ? off[i] : 0), v ? 16u : 0u);
+                }
+                cp_async_mbar_arrive(ready0 + slot * 8);
+                if (++slot == ring) {
+                    slot = 0;
                     phase ^= 1;
                 }
             }
         } else {
-            // transform path: private staging ring, kRaw k-blocks ahead
-            const uint32_t raw_base = smem_u32(raw_tiles) + threadIdx.x * 16;   // chunk i at + i * 4096
-            const int pro_act = p.pro_act;
-            uint32_t okh[kRaw];
+            if (has_pro) {
+                // ===================== workers: BatchNorm/activation transform raw ring -> operand tile ==========
+                float4 s0 = make_float4(1.f, 1.f, 1.f, 1.f), s1 = s0;
+                float4 h0 = make_float4(0.f, 0.f, 0.f, 0.f), h1 = h0;
+                if (cvalid) {
+                    s0 = make_float4(p.pro_scale[c], p.pro_scale[c + 1], p.pro_scale[c + 2], p.pro_scale[c + 3]);
+                    s1 = make_float4(p.pro_scale[c + 4], p.pro_scale[c + 5], p.pro_scale[c + 6], p.pro_scale[c + 7]);
+                    h0 = make_float4(p.pro_shift[c], p.pro_shift[c + 1], p.pro_shift[c + 2], p.pro_shift[c + 3]);
+                    h1 = make_float4(p.pro_shift[c + 4], p.pro_shift[c + 5], p.pro_shift[c + 6], p.pro_shift[c + 7]);
+                }
+                WgradRows<4, 16> rows;   // validity masks only
+                rows.init(p, kb_begin, rbase, tap, c, cvalid);
+                const uint32_t a_base = smem_u32(a_tiles) + tile_off;       // row i adds i * 2048
+                const uint32_t raw_base = smem_u32(raw_tiles) + tile_off;
+                const int pro_act = p.pro_act;
+                int stage = 0, slot = 0;
+                uint32_t phase = 0, rphase = 0;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    int off[4];
+                    const uint32_t ok = rows.next(p, off);
+                    mbar_wait_s(rfull0 + slot * 8, rphase);
+                    uint4 v[4];
 #pragma unroll
-            for (int d = 0; d < kRaw; ++d) {
-                okh[d] = 0;
-                if (kb_begin + d < kb_end) okh[d] = issue(raw_base + d * kRawBytes, 4096);
-                cp_async_commit();
-            }
-            for (int kb0 = kb_begin; kb0 < kb_end; kb0 += kRaw) {
+                    for (int i = 0; i < 4; ++i) v[i] = ld_shared_v4(raw_base + slot * kRawBytes + i * 2048);
+                    if (ok != 0) {
+                        if (pro_act == 1) {
 #pragma unroll
-                for (int d = 0; d < kRaw; ++d) {
-                    const int kb = kb0 + d;
-                    if (kb < kb_end) {  // warp-uniform
-                        cp_async_wait<kRaw - 1>();
-                        uint4 v[4];
+                            for (int i = 0; i < 4; ++i)
+                                if (ok & (1u << i)) transform8_act<1>(v[i], s0, s1, h0, h1);
+                        } else if (pro_act == 2) {
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) v[i] = ld_shared_v4(raw_base + d * kRawBytes + i * 4096);
-                        if (okh[d] != 0) {
-                            if (pro_act == 1) {
+                            for (int i = 0; i < 4; ++i)
+                                if (ok & (1u << i)) transform8_act<2>(v[i], s0, s1, h0, h1);
+                        } else {
 #pragma unroll
-                                for (int i = 0; i < 4; ++i)
-                                    if (okh[d] & (1u << i)) transform8_act<1>(v[i], s0, s1, h0, h1);
-                            } else if (pro_act == 2) {
-#pragma unroll
-                                for (int i = 0; i < 4; ++i)
-                                    if (okh[d] & (1u << i)) transform8_act<2>(v[i], s0, s1, h0, h1);
-                            } else {
-#pragma unroll
-                                for (int i = 0; i < 4; ++i)
-                                    if (okh[d] & (1u << i)) transform8_act<0>(v[i], s0, s1, h0, h1);
-                            }
+                            for (int i = 0; i < 4; ++i)
+                                if (ok & (1u << i)) transform8_act<0>(v[i], s0, s1, h0, h1);
                         }
-                        if (kb - kb_begin >= nstages) mbar_wait_s(empty0 + stage * 8, phase ^ 1);
-                        const uint32_t a_dst = a_base + stage * kATileBytes;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) st_shared_v4(a_dst + i * 2048, v[i]);
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive_s(full0 + stage * 8);
-                        if (++stage == nstages) {
-                            stage = 0;
-                            phase ^= 1;
-                        }
-                        if (kb + kRaw < kb_end) okh[d] = issue(raw_base + d * kRawBytes, 4096);
-                        cp_async_commit();
                     }
+                    if (kb >= nstages) mbar_wait_s(empty0 + stage * 8, phase ^ 1);
+                    const uint32_t a_dst = a_base + stage * kATileBytes;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) st_shared_v4(a_dst + i * 2048, v[i]);
+                    __syncwarp();
+                    if (lane == 0) {
+                        mbar_arrive_s(full0 + stage * 8);
+                        mbar_arrive_s(rempty0 + slot * 8);
+                    }
+                    if (++stage == nstages) { stage = 0; phase ^= 1; }
+                    if (++slot == kRaw) { slot = 0; rphase ^= 1; }
                 }
             }
-        }
         // ---- epilogue: red.add the fp32 tile into dW ----
         mbar_wait(acc_bar, 0);
         tc_fence_after();
@@ -943,6 +985,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
             }
         }
         tc_fence_before();
+        }   // workers
     } else if (warp == kTmaWarp) {
         if (lane == 0) {
             int stage = 0;
@@ -1032,7 +1075,7 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     using L = FwdSmem<kBN, kBMN>;
     const int taps = a.KH * a.KW;
     const int num_kb = kBMN ? taps * ceil_div(a.Cin, kBK) : ceil_div(taps * a.Cin, kBK);
-    const int extra = kBarBytes + 2 * (int)sizeof(float) * (a.Cin + 4) + 64;
+    const int extra = kBarBytes + 2 * (int)sizeof(float) * ((a.Cin > 128 ? a.Cin : 128) + 4) + 64;
     const bool has_pro = !kBMN && (a.pro_scale != nullptr || a.bn_sum != nullptr);
     a.stages = pick_stages(num_kb, has_pro, L::kStageBytes, 1024 + (has_pro ? kRaw * kRawBytes : 0) + extra,
                            kBMN ? 1LL * ceil_div(a.M, kBM) * ceil_div(a.Cout, kBN) : 0);
@@ -1061,7 +1104,7 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
 template <int kBN>
 static int launch_wgrad(const CUtensorMap& tm, WgradArgs& a, cudaStream_t st) {
     constexpr int kBTile = ((kBN + 63) / 64) * 8192;
-    const int extra = (2 * kMaxStages + 1) * 8 + 16 + 64;
+    const int extra = kBarBytes + 64;
     a.stages = pick_stages(a.kb_per_split, a.pro_scale != nullptr, kATileBytes + kBTile,
                            1024 + (a.pro_scale != nullptr ? kRaw * kRawBytes : 0) + extra);
     const size_t smem = 1024 + a.stages * (kATileBytes + kBTile) + (a.pro_scale != nullptr ? kRaw * kRawBytes : 0) + extra;
@@ -1078,7 +1121,7 @@ static int launch_wgrad(const CUtensorMap& tm, WgradArgs& a, cudaStream_t st) {
         attr_set = true;
     }
     dim3 grid(ceil_div(a.KH * a.KW * a.Cin, 128), ceil_div(a.Cout, kBN), a.splits);
-    kern<<<grid, kThreads, smem, st>>>(tm, a);
+    kern<<<grid, kWgThreads, smem, st>>>(tm, a);
     IDCB_LAUNCH_CHECK();
     return 0;
 }

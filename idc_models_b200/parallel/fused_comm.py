@@ -45,6 +45,12 @@ class FusedComm:
         store.grad = self.grad.tensor[:n]
         store.shadow = self.shadow.tensor[:n]
         store.touch(external=True)
+        # BatchNorm moving statistics (averaged over replicas on read): same treatment, padded to 4 floats
+        self.n_stats = int(store.stats.numel()) if getattr(store, "n_stats", 0) else 0
+        if self.n_stats:
+            self.stats = self.alloc.alloc(-(-self.n_stats // 4) * 4, torch.float32)
+            self.stats.tensor[:self.n_stats].copy_(store.stats)
+            store.stats = self.stats.tensor[:self.n_stats]
         self.scal = self.alloc.alloc(4, torch.float32)
         self.scal_out = torch.zeros(4, dtype=torch.float32, device=world.device)
         torch.cuda.synchronize()
@@ -86,6 +92,17 @@ class FusedComm:
             _lib.count_launch()
             scalars = None      # reduce the metric slots once, with the first range
         return self.scal_out if want_scalars else None
+
+    def stat_mean(self) -> None:
+        """store.stats <- mean over ranks (csrc/comm.cu:stat_mean_kernel); every rank ends with the same values"""
+        if not self.n_stats:
+            return
+        lib = _lib.cuda_lib()
+        cw = self.alloc.comm_world()
+        n4 = -(-self.n_stats // 4) * 4
+        _lib.check(lib.idcb_stat_mean(C.byref(cw), self.stats.ptrs(), self.stats.mc() if self.stats.mc_ptr else vp(0),
+                                      C.c_longlong(n4), _lib.stream()))
+        _lib.count_launch()
 
     def allreduce_range(self, optimizer, b: int, e: int, grad_scale: float = 1.0) -> None:
         """One launch over the flat range [b, e) with the optimizer's CURRENT scalars; no step bookkeeping

@@ -135,6 +135,9 @@ class Strategy:
     # ---- BN moving statistics: MEAN over replicas when read (C4) -------------------------------
     def aggregate_moving_stats(self, store) -> None:
         if self.world.is_distributed and store.n_stats:
+            if self.comm == "fused" and self._fused is not None and self._fused.store is store:
+                self._fused.stat_mean()
+                return
             self.world.all_reduce_sum(store.stats)
             store.stats.div_(self.world.size)
 
@@ -151,6 +154,7 @@ class MirroredStrategy(Strategy):
 
 class CentralStorageStrategy(Strategy):
     name = "central_storage"
+    overlap = False      # one owner updates everything after the backward pass; nothing is launched from inside it
 
     def __init__(self, compute_devices=None, parameter_device=None, world: World | None = None,
                  comm: str = "auto", owner: int = 0):

@@ -265,6 +265,10 @@ int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad, void* cons
  *   global[offset:offset+n] += server_lr * sum_k n_k (w_k - global) / sum_k n_k        on every rank
  * idcb_fedavg_finite_flags zeroes the weight of a local client whose range holds a non-finite value
  * (TFF drops such a client's update). */
+/* BatchNorm moving statistics, MEAN over replicas on read (tf.distribute ON_READ variables under
+ * MirroredStrategy, dist_model_tf_mobile.py:115-129): stats[p][0..n) of every rank is
+ * replaced by the element-wise mean over ranks. n % 4 == 0. */
+int idcb_stat_mean(const idcb_comm_world* w, void* const* stats, void* mc_stats, long long n, void* stream);
 /* Cap on the CTAs used by the communication kernels (0 = one per SM, the default). Used for gradient buckets
  * that are reduced while the backward pass is still running (SURVEY 8.1 "tile by tile as buckets become ready"). */
 int idcb_comm_set_max_ctas(int max_ctas);

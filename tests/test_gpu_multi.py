@@ -20,12 +20,13 @@ import sys, json, torch
 sys.path.insert(0, %r)
 from idc_models_b200.models.applications import build_transfer_model
 from idc_models_b200.optim.optimizers import SGD
-from idc_models_b200.parallel.strategy import MirroredStrategy
+from idc_models_b200.parallel.strategy import CentralStorageStrategy, MirroredStrategy
 from idc_models_b200.parallel.world import World
 world = World.from_env()
 res = {}
-for comm in ("nccl", "fused", "fused_overlap", "fused_overlap_graph"):
-    strategy = MirroredStrategy(world=world, comm=comm.split("_")[0])
+for comm in ("nccl", "fused", "fused_overlap", "fused_overlap_graph", "nccl_central", "fused_central"):
+    cls = CentralStorageStrategy if comm.endswith("central") else MirroredStrategy
+    strategy = cls(world=world, comm=comm.split("_")[0])
     strategy.overlap = "overlap" in comm
     strategy.overlap_min_bucket = 4096
     with strategy.scope():
@@ -42,6 +43,15 @@ for comm in ("nccl", "fused", "fused_overlap", "fused_overlap_graph"):
         m.train_on_batch(x, y)
     torch.cuda.synchronize()
     mc = bool(strategy._fused.uses_multicast) if comm.startswith("fused") else None
+    if comm == "fused":
+        # BN moving statistics differ per replica (own batches); on read they become the mean over replicas
+        mine = m.store.stats.detach().cpu().clone()
+        allst = world.all_gather_object(mine)
+        want = torch.stack(allst).double().mean(0).float()
+        strategy.aggregate_moving_stats(m.store)
+        torch.cuda.synchronize()
+        res["stat_mean_err"] = (m.store.stats.cpu() - want).abs().max().item()
+        res["stat_spread"] = (torch.stack(allst).max(0).values - torch.stack(allst).min(0).values).max().item()
     res[comm] = (m.store.master.double().sum().item(), m.store.master.double().abs().sum().item(), mc)
 outs = world.all_gather_object(res)
 if world.rank == 0:
@@ -74,7 +84,8 @@ def test_fused_allreduce_matches_nccl_path_across_processes():
         assert abs(o["fused"][0] - o["nccl"][0]) < 1e-4 * max(1.0, abs(o["nccl"][1]))
         # buckets launched from inside the backward pass (eagerly and from a replayed CUDA graph); the fp32
         # atomics of the weight-gradient kernels make runs differ in the last bits, hence the same tolerance
-        for k in ("fused_overlap", "fused_overlap_graph"):
+        assert o["stat_mean_err"] < 1e-6 and o["stat_spread"] > 1e-6, (o["stat_mean_err"], o["stat_spread"])
+        for k in ("fused_overlap", "fused_overlap_graph", "nccl_central", "fused_central"):
             assert o[k][:2] == outs[0][k][:2], "replicas are not bit-identical"
             assert abs(o[k][0] - o["nccl"][0]) < 1e-4 * max(1.0, abs(o["nccl"][1])), (k, o[k], o["nccl"])
     print("multicast (NVLS) used by the fused path:", outs[0]["fused"][2])
