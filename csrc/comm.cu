@@ -90,38 +90,68 @@ struct Peers {
     int use_barrier;            // 0 when one process emulates the ranks sequentially (tests)
 };
 
-// All CTAs of the local grid arrive; CTA 0 then handshakes with every peer; everyone is released.
-// `phase` distinguishes the barriers inside one launch (the pad epoch advances by `nphases` per launch).
-__device__ void grid_and_world_barrier(const Peers& pr, uint32_t epoch) {
+__device__ __forceinline__ void st_relaxed_sys_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_release_gpu_u32(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// All CTAs of the local grid arrive; the last one to arrive handshakes with every peer; everyone is released.
+// `epoch` distinguishes the barriers inside one launch (the pad epoch advances by 2 per launch).
+// Cost model (measured: the first version, with a system-scope release per flag store, took ~11 us per barrier
+// on 2 GPUs): system-scope fences are the expensive part, so there is exactly ONE per CTA (making its own data
+// writes visible everywhere before it is counted) and one in the handshaking thread; the flags themselves are
+// relaxed stores issued by the lanes of one warp in parallel (lane p talks to rank p), and the local release of
+// the other CTAs is GPU scope.
+// `publish`: this kernel has written data that peers will read after the barrier (peer / multicast stores): every
+// CTA then makes its writes visible system-wide before it is counted. An opening barrier that only waits for the
+// peers' PREVIOUS kernels (whose writes the kernel boundary already completed) passes publish = false.
+__device__ void grid_and_world_barrier(const Peers& pr, uint32_t epoch, bool publish = true) {
     if (!pr.use_barrier) return;
     __syncthreads();
     uint32_t* mypad = pr.pad[pr.rank];
+    __shared__ int s_last;
     if (threadIdx.x == 0) {
-        __threadfence_system();
+        if (publish) __threadfence_system();
         const uint32_t arrived = atomicAdd(mypad + 16, 1u) + 1u;
-        if (arrived == gridDim.x) {
-            // last local CTA: tell every peer, wait for every peer
+        s_last = arrived == gridDim.x;
+        if (s_last) {
             atomicExch(mypad + 16, 0u);
-            for (int p = 0; p < pr.world; ++p) st_release_sys_u32(pr.pad[p] + pr.rank, epoch);
-            for (int p = 0; p < pr.world; ++p) {
+            __threadfence();   // the other CTAs' (already published) writes, seen through the counter, precede the flags
+        }
+    }
+    __syncthreads();
+    if (s_last) {
+        if (threadIdx.x < 32) {
+            const int p = threadIdx.x;
+            if (p < pr.world) {
+                st_relaxed_sys_u32(pr.pad[p] + pr.rank, epoch);
                 long long t0 = clock64();
                 while (static_cast<int32_t>(ld_acquire_sys_u32(mypad + p) - epoch) < 0) {
                     if (clock64() - t0 > 20000000000LL) __trap();  // ~10 s: a peer never arrived
                 }
             }
-            st_release_sys_u32(mypad + 17, epoch);
-        } else {
-            long long t0 = clock64();
-            while (static_cast<int32_t>(ld_acquire_sys_u32(mypad + 17) - epoch) < 0) {
-                if (clock64() - t0 > 20000000000LL) __trap();
-            }
+            __syncwarp();
+            if (p == 0) st_release_gpu_u32(mypad + 17, epoch);
+        }
+    } else if (threadIdx.x == 0) {
+        long long t0 = clock64();
+        while (static_cast<int32_t>(ld_acquire_gpu_u32(mypad + 17) - epoch) < 0) {
+            if (clock64() - t0 > 20000000000LL) __trap();
         }
     }
     __syncthreads();
 }
 
 __device__ __forceinline__ uint32_t load_epoch(const Peers& pr) {
-    return pr.use_barrier ? ld_acquire_sys_u32(pr.pad[pr.rank] + 8) : 0u;
+    // written by the previous launch on this GPU (kernel boundary orders it): a plain volatile load is enough
+    return pr.use_barrier ? *reinterpret_cast<volatile const uint32_t*>(pr.pad[pr.rank] + 8) : 0u;
 }
 // the LAST CTA to finish bumps the stored epoch (all CTAs have read it long before: they passed barriers)
 __device__ __forceinline__ void store_epoch(const Peers& pr, uint32_t next, uint32_t* done_counter) {
@@ -131,7 +161,7 @@ __device__ __forceinline__ void store_epoch(const Peers& pr, uint32_t next, uint
         const uint32_t d = atomicAdd(done_counter, 1u) + 1u;
         if (d == gridDim.x) {
             atomicExch(done_counter, 0u);
-            st_release_sys_u32(pr.pad[pr.rank] + 8, next);
+            *reinterpret_cast<volatile uint32_t*>(pr.pad[pr.rank] + 8) = next;   // read by the next launch only
         }
     }
 }
@@ -189,7 +219,7 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(Allreduce
     const Peers& pr = a.pr;
     const uint32_t e0 = load_epoch(pr);
     // every rank's backward has finished once its kernel has started (stream order) -> safe to read
-    grid_and_world_barrier(pr, e0 + 1);
+    grid_and_world_barrier(pr, e0 + 1, /*publish=*/false);
     long long lo, hi;
     shard_bounds(a.n >> 2, pr.world, pr.rank, lo, hi);
     if (a.owner >= 0) {
@@ -285,7 +315,7 @@ struct StatMeanArgs {
 __global__ void __launch_bounds__(kCommThreads) stat_mean_kernel(StatMeanArgs a) {
     const Peers& pr = a.pr;
     const uint32_t e0 = load_epoch(pr);
-    grid_and_world_barrier(pr, e0 + 1);
+    grid_and_world_barrier(pr, e0 + 1, /*publish=*/false);
     long long lo, hi;
     shard_bounds(a.n >> 2, pr.world, pr.rank, lo, hi);
     const float inv = 1.f / static_cast<float>(pr.world);
@@ -345,7 +375,7 @@ __global__ void fedavg_finite_kernel(const float* clients, long long stride, lon
 __global__ void __launch_bounds__(kCommThreads) fedavg_reduce_kernel(FedAvgArgs a) {
     const Peers& pr = a.pr;
     const uint32_t e0 = load_epoch(pr);
-    grid_and_world_barrier(pr, e0 + 1);
+    grid_and_world_barrier(pr, e0 + 1, /*publish=*/false);
     // total weight (tiny: world * k_local scalars, read by every thread once)
     float wsum = 0.f;
     for (int p = 0; p < pr.world; ++p)
@@ -439,7 +469,7 @@ __global__ void __launch_bounds__(kCommThreads) secagg_kernel(SecAggArgs a) {
         }
         *reinterpret_cast<uint4*>(a.ybuf[pr.rank] + (i << 2)) = acc;
     }
-    grid_and_world_barrier(pr, e0 + 1);
+    grid_and_world_barrier(pr, e0 + 1);   // publishes the partial sums written above
     // ---- phase B: sharded integer sum, dequantise, mean, broadcast ------------------------------------
     long long lo, hi;
     shard_bounds(n4, pr.world, pr.rank, lo, hi);

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Fused all-reduce + optimizer kernel vs NCCL all-reduce + optimizer launch, on the gradient sizes of the
-three models. Launch with torchrun on N >= 2 GPUs. Device-timed, max over ranks; reports the
+three models. Launch with torchrun on N >= 2 GPUs. Device-timed (graph replay), max over ranks; reports the
 achieved fraction of the NVLink roofline S / link_bw (link_bw = 770 GB/s measured peer copy, 900 nominal)."""
 import json
 import sys
@@ -27,7 +27,38 @@ class Store:
 world = World.from_env()
 dev = world.device
 res = []
-for name, n in (("densenet121 (fp32 grads)", 6954881), ("vgg16 (fp32 grads)", 14715201), ("mobilenet_v2", 2225153)):
+REPS = 10
+
+
+def graph_time(fn) -> float:
+    """device microseconds per call: REPS calls captured in a CUDA graph and replayed between two events (host launch
+    cost, ~25 us per eager call through Python, would otherwise sit inside the timed region); max over ranks"""
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize(); world.barrier()
+    st_ = torch.cuda.Stream()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(st_):
+        with torch.cuda.graph(g, stream=st_):
+            for _ in range(REPS):
+                fn()
+    torch.cuda.synchronize(); world.barrier()
+    g.replay(); torch.cuda.synchronize(); world.barrier()
+    times = []
+    for _ in range(5):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        world.barrier(); torch.cuda.synchronize()
+        s.record(); g.replay(); e.record()
+        torch.cuda.synchronize()
+        times.append(s.elapsed_time(e) * 1e3 / REPS)
+    t = torch.tensor([sorted(times)[len(times) // 2]], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+import os
+CASES = (("densenet121 (fp32 grads)", 6954881), ("vgg16 (fp32 grads)", 14715201), ("mobilenet_v2", 2225153), ("tiny: fixed cost (launch + 2 barriers)", 4096))
+if os.environ.get("IDCB_AR_CASES"):
+    CASES = tuple(c for c in CASES if any(k in c[0] for k in os.environ["IDCB_AR_CASES"].split(",")))
+for name, n in CASES:
     n = -(-n // 256) * 256
     for use_mc in (True, False):
         st = Store(n, dev)
@@ -35,29 +66,16 @@ for name, n in (("densenet121 (fp32 grads)", 6954881), ("vgg16 (fp32 grads)", 14
         if use_mc and not fc.uses_multicast:
             continue
         opt = RMSprop(1e-4).bind(st, [(0, n)])
-        for _ in range(5):
-            fc.allreduce_apply(opt, 1.0)
-        torch.cuda.synchronize(); world.barrier()
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(20)]
-        for s, e in ev:
-            s.record(); fc.allreduce_apply(opt, 1.0); e.record()
-        torch.cuda.synchronize()
-        t = torch.tensor([sorted(s.elapsed_time(e) for s, e in ev)[len(ev) // 2]], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        res.append((name, "fused+mc" if use_mc else "fused p2p", n, float(t.item()) * 1e3))
+        us = graph_time(lambda: fc.allreduce_apply(opt, 1.0))
+        res.append((name, "fused+mc" if use_mc else "fused p2p", n, us))
     # NCCL baseline: all_reduce + optimizer kernel
     st = Store(n, dev)
     opt = RMSprop(1e-4).bind(st, [(0, n)])
-    for _ in range(5):
-        dist.all_reduce(st.grad); opt.apply(1.0)
-    torch.cuda.synchronize(); world.barrier()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(20)]
-    for s, e in ev:
-        s.record(); dist.all_reduce(st.grad); opt.apply(1.0); e.record()
-    torch.cuda.synchronize()
-    t = torch.tensor([sorted(s.elapsed_time(e) for s, e in ev)[len(ev) // 2]], device=dev, dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    res.append((name, "nccl allreduce + optimizer", n, float(t.item()) * 1e3))
+    def nccl_step():
+        dist.all_reduce(st.grad)
+        opt.apply(1.0)
+    us = graph_time(nccl_step)
+    res.append((name, "nccl allreduce + optimizer", n, us))
 if world.rank == 0:
     N = world.size
     for name, kind, n, us in res:
