@@ -108,8 +108,25 @@ def weighted_delta_mean(w0: torch.Tensor, clients: torch.Tensor, weights: torch.
     return out
 
 
+def _local_clients(federated_data: list, world, placement: str) -> list:
+    """The client datasets this rank trains. ``round_robin``: client i -> rank i % N. ``balanced``: longest-
+    processing-time-first on the clients' batch counts (fed/scheduler.py, C++), for clients of unequal size; every
+    rank must then hold every client's dataset object (its length is the cost)."""
+    if not world.is_distributed:
+        return list(federated_data)
+    if placement == "balanced":
+        from .scheduler import clients_of_rank
+        costs = [len(ds) if hasattr(ds, "__len__") else 1 for ds in federated_data]
+        return [federated_data[i] for i in clients_of_rank(costs, world.size, world.rank)]
+    return federated_data[world.rank::world.size]
+
+
 class FederatedAveragingProcess:
-    def __init__(self, model_fn, client_optimizer_fn, server_optimizer_fn=None, strategy=None, comm: str = "fused"):
+    def __init__(self, model_fn, client_optimizer_fn, server_optimizer_fn=None, strategy=None, comm: str = "fused",
+                 placement: str = "round_robin"):
+        if placement not in ("round_robin", "balanced"):
+            raise ValueError("placement must be 'round_robin' or 'balanced'")
+        self.placement = placement
         if comm not in ("fused", "nccl"):
             raise ValueError("comm must be 'fused' (one kernel over peer memory) or 'nccl' (library all-reduce baseline)")
         self.comm = comm
@@ -158,7 +175,7 @@ class FederatedAveragingProcess:
         net = wr.model
         world = net.strategy.world
         n = net.store.master.numel()
-        mine = federated_data[world.rank::world.size] if world.is_distributed else list(federated_data)
+        mine = _local_clients(federated_data, world, self.placement)
         k_counts = world.all_gather_object(len(mine))
         k_local = max(k_counts)
         clients, weights, gbuf, gshadow = self._client_block(net, k_local)
@@ -242,11 +259,12 @@ class FederatedAveragingProcess:
         return new
 
 
-def build_federated_averaging_process(model_fn, client_optimizer_fn, server_optimizer_fn=None, comm: str = "fused"):
-    return FederatedAveragingProcess(model_fn, client_optimizer_fn, server_optimizer_fn, comm=comm)
+def build_federated_averaging_process(model_fn, client_optimizer_fn, server_optimizer_fn=None, comm: str = "fused",
+                                      placement: str = "round_robin"):
+    return FederatedAveragingProcess(model_fn, client_optimizer_fn, server_optimizer_fn, comm=comm, placement=placement)
 
 
-def build_federated_evaluation(model_fn):
+def build_federated_evaluation(model_fn, placement: str = "round_robin"):
     """-> evaluation(server_model, federated_data) -> (binary_accuracy, loss), example-weighted over the
     clients' full datasets (fed_model.py:210,224,228)."""
     holder = {}
@@ -263,7 +281,7 @@ def build_federated_evaluation(model_fn):
         net.store.refresh_shadow()
         if net.optimizer is None:
             net.compile(optimizer=SGD(0.0), loss=wr.loss, metrics=wr.metrics)
-        mine = federated_data[world.rank::world.size] if world.is_distributed else list(federated_data)
+        mine = _local_clients(federated_data, world, placement)
         msum = torch.zeros(3, dtype=torch.float64)
         for ds in mine:
             for x, y in ds:

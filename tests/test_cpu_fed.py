@@ -139,3 +139,15 @@ def test_secure_clients_paillier_path_equals_mask_path():
     for got in results.values():
         for g, w in zip(got, want):
             assert np.allclose(g, w, atol=2e-5)
+
+
+def test_client_scheduler_balances_and_is_deterministic():
+    from idc_models_b200.fed.scheduler import assign_clients, clients_of_rank
+    assert assign_clients([100] * 8, 4) == [0, 1, 2, 3, 0, 1, 2, 3]          # equal sizes: round-robin
+    costs = [900, 100, 100, 100, 400, 400, 50, 50]
+    plan = assign_clients(costs, 2)
+    loads = [sum(c for c, r in zip(costs, plan) if r == k) for k in range(2)]
+    assert sorted(loads) == [1050, 1050] or max(loads) <= 4 / 3 * (sum(costs) / 2)
+    assert plan == assign_clients(costs, 2)
+    assert sorted(clients_of_rank(costs, 2, 0) + clients_of_rank(costs, 2, 1)) == list(range(8))
+    assert assign_clients([5, 3], 1) == [0, 0]
