@@ -109,6 +109,16 @@ __device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* p) {
 // writes visible everywhere before it is counted) and one in the handshaking thread; the flags themselves are
 // relaxed stores issued by the lanes of one warp in parallel (lane p talks to rank p), and the local release of
 // the other CTAs is GPU scope.
+// A peer never arrived: say who is missing (per-rank flag state) before trapping, so that a protocol bug or a
+// crashed rank shows up as a diagnosable launch failure instead of a silent hang.
+__device__ __noinline__ void barrier_timeout(uint32_t* mypad, int rank, int world, uint32_t epoch, int waiting_for) {
+    printf("idcb comm barrier timeout: rank %d of %d waited ~10 s for rank %d at epoch %u; flags seen:", rank, world,
+           waiting_for, epoch);
+    for (int p = 0; p < world; ++p) printf(" [%d]=%u", p, ld_acquire_sys_u32(mypad + p));
+    printf(" (local arrivals %u, released %u)\n", mypad[16], mypad[17]);
+    __trap();
+}
+
 // `publish`: this kernel has written data that peers will read after the barrier (peer / multicast stores): every
 // CTA then makes its writes visible system-wide before it is counted. An opening barrier that only waits for the
 // peers' PREVIOUS kernels (whose writes the kernel boundary already completed) passes publish = false.
@@ -134,7 +144,7 @@ __device__ void grid_and_world_barrier(const Peers& pr, uint32_t epoch, bool pub
                 st_relaxed_sys_u32(pr.pad[p] + pr.rank, epoch);
                 long long t0 = clock64();
                 while (static_cast<int32_t>(ld_acquire_sys_u32(mypad + p) - epoch) < 0) {
-                    if (clock64() - t0 > 20000000000LL) __trap();  // ~10 s: a peer never arrived
+                    if (clock64() - t0 > 20000000000LL) barrier_timeout(mypad, pr.rank, pr.world, epoch, p);  // ~10 s
                 }
             }
             __syncwarp();

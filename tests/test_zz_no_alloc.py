@@ -10,6 +10,7 @@ already run. It passes alone in a fresh process and after the rest of the suite 
 storage keeps state between calls by design, so the test makes no assumption about its initial contents).
 """
 import ctypes as C
+import gc
 
 import pytest
 import torch
@@ -49,13 +50,19 @@ def test_noalloc_entry_point_matches_the_buffered_one_on_two_calls_in_a_row():
         clients = torch.randn(k, stride, device="cuda") * 2
         want = _reference(L, lib, clients, k, stride, off, n, 16, seed)
         out = torch.zeros(stride, dtype=torch.float32, device="cuda")
+        # objects of earlier tests may still be waiting for the garbage collector; let it run now so that a
+        # collection in the middle of the measured window cannot change the allocator's count
+        gc.collect()
+        torch.cuda.synchronize()
         before = torch.cuda.memory_allocated()
+        free_before = torch.cuda.mem_get_info()[0]
         rc = lib.idcb_secagg_mean_noalloc(C.c_void_p(clients.data_ptr()), C.c_void_p(out.data_ptr()), C.c_int(k),
                                           C.c_longlong(stride), C.c_longlong(off), C.c_longlong(n), C.c_int(16),
                                           C.c_ulonglong(seed), L.stream())
         assert rc == 0, lib.idcb_last_error().decode()
         torch.cuda.synchronize()
         assert torch.cuda.memory_allocated() == before
+        assert torch.cuda.mem_get_info()[0] >= free_before          # nor did the driver hand out device memory
         # same kernel, same arithmetic: bit-identical; and it is the mean, to the quantisation step
         assert torch.equal(out, want), f"call {call}: differs from the buffered entry point"
         assert (out[off:off + n] - clients[:, off:off + n].mean(0)).abs().max().item() < 2e-5
