@@ -242,63 +242,79 @@ __global__ void __launch_bounds__(kCommThreads) allreduce_optim_kernel(Allreduce
         a.scal_out[threadIdx.x] = t;
     }
     const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
-    // kU independent 16-byte reductions in flight per thread: the NVLink round trip (~2-4 us through
-    // the switch) is hidden by memory-level parallelism, not by occupancy
-    constexpr int kU = 8;
+    // Software pipeline over chunks of kU 16-byte reductions per thread: the reductions of chunk c+1 are issued
+    // BEFORE chunk c is updated and broadcast, so the two NVLink directions work at the same time (reduce =
+    // this GPU pulling, broadcast = this GPU pushing) and 2*kU reductions per thread hide the ~2-4 us round trip
+    // through the switch. (A single pass with everything in flight leaves the push phase waiting for the pull.)
+    constexpr int kU = 2;
     const long long tstride = (long long)gridDim.x * blockDim.x;
-    for (long long i0 = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < hi; i0 += tstride * kU) {
-      float4 gg[kU];
+    const long long cstride = tstride * kU;
+    auto pull = [&](long long i0, float4 (&gg)[kU]) {
 #pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        const long long i = i0 + u * tstride;
-        gg[u] = zero;
-        if (i >= hi) continue;
-        const long long e = i << 2;
-        if (a.mc_grad != nullptr) {
-            gg[u] = mc_ld_reduce_f4(a.mc_grad + e);
-        } else {
-            for (int q = 0; q < pr.world; ++q) {
-                const int p = (pr.rank + q) % pr.world;   // stagger peers so ranks do not gang up on one
-                const float4 v = ld_sys_f4(a.grad[p] + e);
-                gg[u].x += v.x; gg[u].y += v.y; gg[u].z += v.z; gg[u].w += v.w;
+        for (int u = 0; u < kU; ++u) {
+            const long long i = i0 + u * tstride;
+            gg[u] = zero;
+            if (i >= hi) continue;
+            const long long e = i << 2;
+            if (a.mc_grad != nullptr) {
+                gg[u] = mc_ld_reduce_f4(a.mc_grad + e);
+            } else {
+                for (int q = 0; q < pr.world; ++q) {
+                    const int p = (pr.rank + q) % pr.world;   // stagger peers so ranks do not gang up on one
+                    const float4 v = ld_sys_f4(a.grad[p] + e);
+                    gg[u].x += v.x; gg[u].y += v.y; gg[u].z += v.z; gg[u].w += v.w;
+                }
             }
         }
-      }
+    };
+    auto update_and_push = [&](long long i0, const float4 (&gg)[kU]) {
 #pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        const long long i = i0 + u * tstride;
-        if (i >= hi) continue;
-        const long long e = i << 2;
-        float4 g = gg[u];
-        // The consumed bucket must be zero again before the next backward accumulates into it. With live
-        // barriers every rank clears its OWN bucket after the closing barrier (HBM speed, nothing on NVLink);
-        // broadcasting zeros from here would add (N-1)/N of the bucket to every GPU's inbound traffic.
-        // Only the single-process emulation (no barriers, ranks run one after another) clears per shard.
-        if (!pr.use_barrier) {
-            for (int q = 0; q < pr.world; ++q) st_sys_f4(a.grad[(pr.rank + q) % pr.world] + e, zero);
-        }
-        g.x *= a.grad_scale; g.y *= a.grad_scale; g.z *= a.grad_scale; g.w *= a.grad_scale;
-        float4 w = *reinterpret_cast<const float4*>(a.master[pr.rank] + e);
-        float4 s1 = a.s1 ? *reinterpret_cast<const float4*>(a.s1 + e) : zero;
-        float4 s2 = a.s2 ? *reinterpret_cast<const float4*>(a.s2 + e) : zero;
-        w.x = opt_step(a.kind, w.x, g.x, s1.x, s2.x, a.lr, a.p1, a.p2, a.eps);
-        w.y = opt_step(a.kind, w.y, g.y, s1.y, s2.y, a.lr, a.p1, a.p2, a.eps);
-        w.z = opt_step(a.kind, w.z, g.z, s1.z, s2.z, a.lr, a.p1, a.p2, a.eps);
-        w.w = opt_step(a.kind, w.w, g.w, s1.w, s2.w, a.lr, a.p1, a.p2, a.eps);
-        if (a.s1) *reinterpret_cast<float4*>(a.s1 + e) = s1;
-        if (a.s2) *reinterpret_cast<float4*>(a.s2 + e) = s2;
-        const uint2 wb = make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
-        if (a.mc_master != nullptr) {
-            mc_st_f4(a.mc_master + e, w);
-            if (a.mc_shadow) mc_st_u2(a.mc_shadow + e, wb);
-        } else {
-            for (int q = 0; q < pr.world; ++q) {
-                const int p = (pr.rank + q) % pr.world;
-                st_sys_f4(a.master[p] + e, w);
-                if (a.shadow[p]) st_sys_u2(a.shadow[p] + e, wb);
+        for (int u = 0; u < kU; ++u) {
+            const long long i = i0 + u * tstride;
+            if (i >= hi) continue;
+            const long long e = i << 2;
+            float4 g = gg[u];
+            // The consumed bucket must be zero again before the next backward accumulates into it. With live
+            // barriers every rank clears its OWN bucket after the closing barrier (HBM speed, nothing on NVLink);
+            // broadcasting zeros from here would add (N-1)/N of the bucket to every GPU's inbound traffic.
+            // Only the single-process emulation (no barriers, ranks run one after another) clears per shard.
+            if (!pr.use_barrier) {
+                for (int q = 0; q < pr.world; ++q) st_sys_f4(a.grad[(pr.rank + q) % pr.world] + e, zero);
+            }
+            g.x *= a.grad_scale; g.y *= a.grad_scale; g.z *= a.grad_scale; g.w *= a.grad_scale;
+            float4 w = *reinterpret_cast<const float4*>(a.master[pr.rank] + e);
+            float4 s1 = a.s1 ? *reinterpret_cast<const float4*>(a.s1 + e) : zero;
+            float4 s2 = a.s2 ? *reinterpret_cast<const float4*>(a.s2 + e) : zero;
+            w.x = opt_step(a.kind, w.x, g.x, s1.x, s2.x, a.lr, a.p1, a.p2, a.eps);
+            w.y = opt_step(a.kind, w.y, g.y, s1.y, s2.y, a.lr, a.p1, a.p2, a.eps);
+            w.z = opt_step(a.kind, w.z, g.z, s1.z, s2.z, a.lr, a.p1, a.p2, a.eps);
+            w.w = opt_step(a.kind, w.w, g.w, s1.w, s2.w, a.lr, a.p1, a.p2, a.eps);
+            if (a.s1) *reinterpret_cast<float4*>(a.s1 + e) = s1;
+            if (a.s2) *reinterpret_cast<float4*>(a.s2 + e) = s2;
+            const uint2 wb = make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
+            if (a.mc_master != nullptr) {
+                mc_st_f4(a.mc_master + e, w);
+                if (a.mc_shadow) mc_st_u2(a.mc_shadow + e, wb);
+            } else {
+                for (int q = 0; q < pr.world; ++q) {
+                    const int p = (pr.rank + q) % pr.world;
+                    st_sys_f4(a.master[p] + e, w);
+                    if (a.shadow[p]) st_sys_u2(a.shadow[p] + e, wb);
+                }
             }
         }
-      }
+    };
+    {
+        float4 cur[kU], nxt[kU];
+        long long i0 = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x;
+        if (i0 < hi) pull(i0, cur);
+        for (; i0 < hi; i0 += cstride) {
+            const bool more = i0 + cstride < hi;
+            if (more) pull(i0 + cstride, nxt);
+            update_and_push(i0, cur);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) cur[u] = nxt[u];
+        }
     }
     // every rank must have received all shards (and had its bucket re-zeroed) before anyone goes on
     grid_and_world_barrier(pr, e0 + 2);
