@@ -44,7 +44,7 @@ namespace idcb {
 constexpr int kBM = 128;      // UMMA M (rows of the accumulator = TMEM lanes)
 constexpr int kBK = 64;       // K elements per pipeline stage (one 128-byte swizzle row)
 constexpr int kMaxStages = 8;
-constexpr int kRaw = 4;                          // k-blocks of raw activations in flight per CTA (transform path)
+constexpr int kRaw = 6;                          // k-blocks of raw activations in flight per CTA (transform path)
 constexpr int kBarBytes = 256;                    // barrier block: full/empty/acc/raw_full/raw_empty + TMEM slot
 constexpr int kRawBytes = kBM * 128;             // one k-block of raw 16-byte chunks, [chunk row i][thread]
 constexpr int kATileBytes = kBM * 128;  // 16 KiB
