@@ -3,8 +3,8 @@
 //   dgrad : dpre = dw^T(dy) * act'(scale*x+shift)       + BN-backward sums
 //   wgrad : dw += sum_pos act(scale*x+shift) * dy
 // Bandwidth-bound (~6 % of MobileNetV2 MACs), so these are direct kernels, one
-// thread per 8 channels, 16-byte accesses, fused BN prologue/epilogue bookkeeping instead of separate
-// BN kernels. Reference: DepthwiseConv2D layers inside tf.keras.applications.MobileNetV2
+// thread per 8 channels, 16-byte accesses laid out so that a warp touches whole 128-byte lines (DwLane),
+// fused BN prologue/epilogue bookkeeping instead of separate BN kernels. Reference: DepthwiseConv2D layers inside tf.keras.applications.MobileNetV2
 // (/root/reference/dist_model_tf_mobile.py:119), executed by TF's depthwise CUDA kernels.
 #include "common.cuh"
 #include "../include/idcb200.h"
@@ -41,22 +41,41 @@ __device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
     *reinterpret_cast<uint4*>(p) = q;
 }
 
-// block-level reduction of 8 per-thread values into global atomics (one channel octet per block row)
-__device__ __forceinline__ void block_reduce8_atomic(const float (&v)[8], float* dst, float (*sh)[9]) {
+// Thread layout shared by the three kernels: consecutive threads own consecutive channel octets of one
+// position (so a warp reads whole 128-byte lines of the NHWC tensor), then the next position:
+//   oct = tid % nOct, pl = tid / nOct, ppb = 256 / nOct positions per block pass; threads with pl >= ppb idle.
+// A thread's octet never changes, so its 3x3 weights and BN coefficients live in registers.
+struct DwLane {
+    int nOct, ppb, oct, pl, c;
+    bool active;
+    __device__ __forceinline__ DwLane(int C) {
+        nOct = C >> 3;
+        ppb = blockDim.x / nOct;
+        oct = threadIdx.x % nOct;
+        pl = threadIdx.x / nOct;
+        c = oct * 8;
+        active = pl < ppb;
+    }
+};
+
+// block-level reduction of 8 per-thread values per channel octet into global atomics: dst[oct * 8 + e]
+__device__ __forceinline__ void block_reduce8_atomic(const float (&v)[8], float* dst, float (*sh)[9], const DwLane& L) {
     __syncthreads();
 #pragma unroll
-    for (int e = 0; e < 8; ++e) sh[threadIdx.x][e] = v[e];
+    for (int e = 0; e < 8; ++e) sh[threadIdx.x][e] = L.active ? v[e] : 0.f;
     __syncthreads();
-    if (threadIdx.x < 8) {
+    for (int i = threadIdx.x; i < L.nOct * 8; i += blockDim.x) {
+        const int o = i >> 3, e = i & 7;
         float t = 0.f;
-        for (int r = 0; r < (int)blockDim.x; ++r) t += sh[r][threadIdx.x];
-        atomicAdd(dst + threadIdx.x, t);
+        for (int r = 0; r < L.ppb; ++r) t += sh[r * L.nOct + o][e];
+        atomicAdd(dst + i, t);
     }
 }
 
 __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
     __shared__ float sh[256][9];
-    const int c = blockIdx.y * 8;
+    const DwLane L(p.C);
+    const int c = L.c;
     float sc[8], sf[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
@@ -64,13 +83,14 @@ __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
         sf[e] = p.scale ? p.shift[c + e] : 0.f;
     }
     float wk[9][8];
-    for (int t = 0; t < p.k * p.k; ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
+#pragma unroll
+    for (int t = 0; t < 9; ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
     float sa[8], sb[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) sa[e] = sb[e] = 0.f;
     const long long npos = 1LL * p.B * p.Ho * p.Wo;
-    for (long long pos = blockIdx.x * (long long)blockDim.x + threadIdx.x; pos < npos;
-         pos += (long long)gridDim.x * blockDim.x) {
+    for (long long pos = blockIdx.x * (long long)L.ppb + L.pl; L.active && pos < npos;
+         pos += (long long)gridDim.x * L.ppb) {
         const int wo = static_cast<int>(pos % p.Wo);
         const long long t2 = pos / p.Wo;
         const int ho = static_cast<int>(t2 % p.Ho);
@@ -78,10 +98,12 @@ __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
         float acc[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-        for (int kh = 0; kh < p.k; ++kh) {
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
             const int hi = ho * p.stride - p.pad_t + kh;
             if (hi < 0 || hi >= p.H) continue;
-            for (int kw = 0; kw < p.k; ++kw) {
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
                 const int wi = wo * p.stride - p.pad_l + kw;
                 if (wi < 0 || wi >= p.W) continue;
                 float xv[8];
@@ -90,7 +112,7 @@ __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
                 for (int e = 0; e < 8; ++e) {
                     float a = xv[e];
                     if (p.scale) a = __bfloat162float(__float2bfloat16_rn(apply_act(fmaf(a, sc[e], sf[e]), p.act)));
-                    acc[e] = fmaf(a, wk[kh * p.k + kw][e], acc[e]);
+                    acc[e] = fmaf(a, wk[kh * 3 + kw][e], acc[e]);
                 }
             }
         }
@@ -102,13 +124,14 @@ __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
         }
         store8(p.y + pos * p.y_pitch + p.y_coff + c, acc);
     }
-    if (p.stat_a) block_reduce8_atomic(sa, p.stat_a + c, sh);
-    if (p.stat_b) block_reduce8_atomic(sb, p.stat_b + c, sh);
+    if (p.stat_a) block_reduce8_atomic(sa, p.stat_a, sh, L);
+    if (p.stat_b) block_reduce8_atomic(sb, p.stat_b, sh, L);
 }
 
 __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
     __shared__ float sh[256][9];
-    const int c = blockIdx.y * 8;
+    const DwLane L(p.C);
+    const int c = L.c;
     float sc[8], sf[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
@@ -116,13 +139,14 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
         sf[e] = p.scale ? p.shift[c + e] : 0.f;
     }
     float wk[9][8];
-    for (int t = 0; t < p.k * p.k; ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
+#pragma unroll
+    for (int t = 0; t < 9; ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
     float sa[8], sb[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) sa[e] = sb[e] = 0.f;
     const long long npos = 1LL * p.B * p.H * p.W;
-    for (long long pos = blockIdx.x * (long long)blockDim.x + threadIdx.x; pos < npos;
-         pos += (long long)gridDim.x * blockDim.x) {
+    for (long long pos = blockIdx.x * (long long)L.ppb + L.pl; L.active && pos < npos;
+         pos += (long long)gridDim.x * L.ppb) {
         const int wi = static_cast<int>(pos % p.W);
         const long long t2 = pos / p.W;
         const int hi = static_cast<int>(t2 % p.H);
@@ -130,12 +154,14 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
         float g[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) g[e] = 0.f;
-        for (int kh = 0; kh < p.k; ++kh) {
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
             const int hn = hi + p.pad_t - kh;
             if (hn < 0 || hn % p.stride) continue;
             const int ho = hn / p.stride;
             if (ho >= p.Ho) continue;
-            for (int kw = 0; kw < p.k; ++kw) {
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
                 const int wn = wi + p.pad_l - kw;
                 if (wn < 0 || wn % p.stride) continue;
                 const int wo = wn / p.stride;
@@ -143,7 +169,7 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
                 float dv[8];
                 load8(p.dy + (static_cast<size_t>(b * p.Ho + ho) * p.Wo + wo) * p.dy_pitch + p.dy_coff + c, dv);
 #pragma unroll
-                for (int e = 0; e < 8; ++e) g[e] = fmaf(dv[e], wk[kh * p.k + kw][e], g[e]);
+                for (int e = 0; e < 8; ++e) g[e] = fmaf(dv[e], wk[kh * 3 + kw][e], g[e]);
             }
         }
         float xv[8];
@@ -157,13 +183,14 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
         }
         store8(p.dx + pos * p.dx_pitch + p.dx_coff + c, g);
     }
-    if (p.stat_a) block_reduce8_atomic(sa, p.stat_a + c, sh);
-    if (p.stat_b) block_reduce8_atomic(sb, p.stat_b + c, sh);
+    if (p.stat_a) block_reduce8_atomic(sa, p.stat_a, sh, L);
+    if (p.stat_b) block_reduce8_atomic(sb, p.stat_b, sh, L);
 }
 
 __global__ void __launch_bounds__(256) dw_wgrad_kernel(DwArgs p) {
     __shared__ float sh[256][9];
-    const int c = blockIdx.y * 8;
+    const DwLane L(p.C);
+    const int c = L.c;
     float sc[8], sf[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
@@ -176,8 +203,8 @@ __global__ void __launch_bounds__(256) dw_wgrad_kernel(DwArgs p) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[t][e] = 0.f;
     const long long npos = 1LL * p.B * p.Ho * p.Wo;
-    for (long long pos = blockIdx.x * (long long)blockDim.x + threadIdx.x; pos < npos;
-         pos += (long long)gridDim.x * blockDim.x) {
+    for (long long pos = blockIdx.x * (long long)L.ppb + L.pl; L.active && pos < npos;
+         pos += (long long)gridDim.x * L.ppb) {
         const int wo = static_cast<int>(pos % p.Wo);
         const long long t2 = pos / p.Wo;
         const int ho = static_cast<int>(t2 % p.Ho);
@@ -204,12 +231,12 @@ __global__ void __launch_bounds__(256) dw_wgrad_kernel(DwArgs p) {
         }
     }
 #pragma unroll
-    for (int t = 0; t < 9; ++t) block_reduce8_atomic(acc[t], p.dw + static_cast<size_t>(t) * p.C + c, sh);
+    for (int t = 0; t < 9; ++t) block_reduce8_atomic(acc[t], p.dw + static_cast<size_t>(t) * p.C, sh, L);
 }
 
 static int fill(DwArgs& p, const idcb_conv_desc* d) {
     IDCB_REQUIRE(d != nullptr, "depthwise: null descriptor");
-    IDCB_REQUIRE(d->cin == d->cout && d->cin % 8 == 0, "depthwise: C must be a multiple of 8");
+    IDCB_REQUIRE(d->cin == d->cout && d->cin % 8 == 0 && d->cin <= 2048, "depthwise: C must be a multiple of 8, at most 2048");
     IDCB_REQUIRE(d->kh == 3 && d->kw == 3, "depthwise: only 3x3 is implemented");
     IDCB_REQUIRE(d->x_pitch % 8 == 0 && d->x_coff % 8 == 0 && d->y_pitch % 8 == 0 && d->y_coff % 8 == 0,
                  "depthwise: alignment");
@@ -218,12 +245,15 @@ static int fill(DwArgs& p, const idcb_conv_desc* d) {
     return 0;
 }
 
-static dim3 dw_grid(long long npos, int C) {
-    int gx = static_cast<int>(ceil_div_ll(npos, 256));
-    const int cap = ceil_div(8 * num_sms(), C / 8);
+static dim3 dw_grid(long long npos, int C, int pos_per_thread = 1) {
+    const int ppb = 256 / (C / 8);                          // positions per block pass (see DwLane)
+    long long gx = ceil_div_ll(npos, 1LL * ppb * pos_per_thread);
+    // every block ends with per-channel atomics (statistics / weight gradient): the number of blocks, not the
+    // data volume, sets the contention on those few hundred addresses
+    const long long cap = (pos_per_thread > 1 ? 1LL : 2LL) * num_sms();
     if (gx > cap) gx = cap;
     if (gx < 1) gx = 1;
-    return dim3(gx, C / 8);
+    return dim3(static_cast<unsigned>(gx), 1);
 }
 
 }  // namespace idcb
@@ -274,11 +304,7 @@ extern "C" int idcb_dwconv_wgrad(const idcb_conv_desc* d, const void* x, const v
     p.scale = scale; p.shift = shift; p.act = act;
     const long long npos = 1LL * p.B * p.Ho * p.Wo;
     if (npos == 0) return 0;
-    int gx = static_cast<int>(ceil_div_ll(npos, 256 * 8));
-    const int cap = ceil_div(4 * num_sms(), p.C / 8);
-    if (gx > cap) gx = cap;
-    if (gx < 1) gx = 1;
-    dw_wgrad_kernel<<<dim3(gx, p.C / 8), 256, 0, (cudaStream_t)stream>>>(p);
+    dw_wgrad_kernel<<<dw_grid(npos, p.C, 8), 256, 0, (cudaStream_t)stream>>>(p);
     IDCB_LAUNCH_CHECK();
     return 0;
 }
