@@ -126,6 +126,23 @@ class FusedComm:
         _lib.count_launch()
 
 
+def plan_buckets(ready_offsets, lo: int, hi: int, min_bucket: int) -> list:
+    """Bucket plan for the trainable range [lo, hi): ``ready_offsets`` are announced top-down by the backward
+    pass; announcements are merged until a bucket holds at least ``min_bucket`` elements (each bucket costs a
+    launch and two cross-GPU barriers). Returns ``[(announce_offset, begin, end)]`` in launch order; the last
+    entry is whatever is left when the backward pass is done. Pure function of static data: every rank computes
+    the same plan."""
+    plan = []
+    top = hi
+    for o in ready_offsets:
+        o = max(lo, min(int(o) & ~3, top))
+        if top - o >= min_bucket and o > lo:
+            plan.append((o, o, top))
+            top = o
+    plan.append((lo, lo, top))
+    return plan
+
+
 class OverlapSchedule:
     """Bucketed launch of the fused all-reduce+optimizer kernel WHILE the backward pass runs (SURVEY 8.1,
     7.2 step 5). The executor announces "every gradient at flat offset >= o is final" as its backward walks
@@ -147,15 +164,7 @@ class OverlapSchedule:
         if len(optimizer.ranges) != 1:
             raise ValueError("overlap needs one contiguous trainable range")
         self.lo, self.hi = optimizer.ranges[0]
-        # plan: merge announcements until a bucket holds at least min_bucket elements
-        self.plan = []           # [(announce_offset, b, e)] in launch order
-        top = self.hi
-        for o in executor.grad_ready_offsets():
-            o = max(self.lo, min(int(o) & ~3, top))
-            if top - o >= min_bucket and o > self.lo:
-                self.plan.append((o, o, top))
-                top = o
-        self.plan.append((self.lo, self.lo, top))      # whatever is left goes when the backward is done
+        self.plan = plan_buckets(executor.grad_ready_offsets(), self.lo, self.hi, min_bucket)
         import os
         self.overlap_ctas = int(os.environ.get("IDCB_OVERLAP_CTAS", "48"))
         self.side = torch.cuda.Stream(device=fused.world.device, priority=-1)

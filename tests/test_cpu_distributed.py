@@ -68,3 +68,40 @@ def test_two_cpu_replicas_stay_identical_and_match_single_replica(kind):
     assert two[0][0] == two[1][0], "replica weight checksums differ"
     assert abs(two[0][1] - one[0][1]) < 5e-4, f"2-replica loss {two[0][1]} vs single-replica {one[0][1]}"
     assert abs(two[0][0] - one[0][0]) < 1e-3 * max(1.0, abs(one[0][0]))
+
+
+def test_overlap_bucket_plan_is_static_and_covers_the_range():
+    """gradient buckets launched from inside the backward pass (parallel/fused_comm.py): contiguous, top-down,
+    merged up to the minimum size, identical for every rank"""
+    from idc_models_b200.parallel.fused_comm import plan_buckets
+    offs = [900, 700, 650, 300, 100]                      # announced as the backward walks down
+    plan = plan_buckets(offs, 0, 1000, min_bucket=200)
+    assert plan == [(700, 700, 1000), (300, 300, 700), (100, 100, 300), (0, 0, 100)]
+    # covers [lo, hi) exactly once, in descending order
+    assert plan[0][2] == 1000 and plan[-1][1] == 0
+    assert all(a[1] == b[2] for a, b in zip(plan, plan[1:]))
+    # a trainable range that starts above 0 (frozen lower layers) and unaligned announcements
+    plan = plan_buckets([801, 503, 90], 400, 1000, min_bucket=100)
+    assert plan == [(800, 800, 1000), (500, 500, 800), (400, 400, 500)]
+    assert plan_buckets([], 0, 64, 16) == [(0, 0, 64)]
+    # executors expose the offsets statically
+    from idc_models_b200.models.applications import build_transfer_model
+    m = build_transfer_model("densenet_tiny", (50, 50, 3), 1, device="cpu", seed=0, executor="reference")
+    assert not hasattr(m.executor, "grad_ready_offsets") or isinstance(m.executor.grad_ready_offsets(), list)
+
+
+def test_jsonl_logger_and_device_timer(tmp_path):
+    import json
+    from idc_models_b200.utils.trace import DeviceTimer, JsonlLogger, nvtx_range
+    path = tmp_path / "log" / "run.jsonl"
+    log = JsonlLogger(str(path))
+    with nvtx_range("unit"):
+        with DeviceTimer() as t:
+            sum(range(1000))
+    log.log("epoch", epoch=0, loss=0.5)
+    log.log("epoch", epoch=1, loss=0.25, ms=t.ms)
+    recs = [json.loads(l) for l in path.read_text().splitlines()]
+    assert [r["epoch"] for r in recs] == [0, 1] and recs[1]["loss"] == 0.25 and recs[1]["ms"] >= 0
+    JsonlLogger(None).log("epoch", epoch=2)               # disabled logger: no file, no error
+    JsonlLogger(str(path), rank=1).log("epoch", epoch=3)  # only rank 0 writes
+    assert len(path.read_text().splitlines()) == 2
