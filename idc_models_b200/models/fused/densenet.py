@@ -251,7 +251,39 @@ class DenseNetExecutor(FusedExecutor):
         self._block_offsets = offs            # index = dense block number (0-based)
         return list(reversed(offs))
 
+    # ---- weight-gradient kernels run beside the data-gradient chain -----------------------------------
+    # A layer's wgrad and its dgrad both start from the same dy and neither feeds the other; the layers are
+    # small (a dgrad or wgrad of blocks 2-4 occupies a fraction of the SMs for a few microseconds), so the wgrad
+    # is launched on a side stream and the critical path keeps only the dgrad chain. The fork/join edges are
+    # ordinary stream waits, so they are captured into the step's CUDA graph as parallel branches.
+    # Joins: before a buffer a pending wgrad reads (the block's dy3 / dy1 scratch) is overwritten — i.e. at the
+    # start of the next layer — and before the block's gradients are announced as final.
+    wgrad_side_stream = True
+
+    def _wgrad(self, *args, **kw) -> None:
+        if not self.wgrad_side_stream:
+            OC.conv_wgrad_raw(*args, **kw)
+            return
+        if getattr(self, "_wg_stream", None) is None:
+            self._wg_stream = torch.cuda.Stream(device=self.net.device)
+        main = torch.cuda.current_stream()
+        self._wg_stream.wait_stream(main)
+        with torch.cuda.stream(self._wg_stream):
+            OC.conv_wgrad_raw(*args, **kw)
+        self._wg_pending = True
+
+    def _wgrad_join(self) -> None:
+        if getattr(self, "_wg_pending", False):
+            torch.cuda.current_stream().wait_stream(self._wg_stream)
+            self._wg_pending = False
+
     def _backward(self, p) -> None:
+        try:
+            self._backward_impl(p)
+        finally:
+            self._wgrad_join()      # whichever way the truncated backward ended, the side stream rejoins
+
+    def _backward_impl(self, p) -> None:
         if not hasattr(self, "_block_offsets"):
             self.grad_ready_offsets()
         ft = self.first_trainable
@@ -273,7 +305,7 @@ class DenseNetExecutor(FusedExecutor):
                     self._finalize_slice(nxt, 0, nxt.c0, blk.dpool)
                     K.pool_bwd(blk.t, nxt.buf, blk.dpool, blk.dt, nxt.c0, 2, 2, 0, False)
                     if blk.i_tconv in tr:
-                        OC.conv_wgrad_raw(blk.gt, blk.buf, blk.dt, self.gw(blk.tconv), pro_scale=blk.bn_t.scale,
+                        self._wgrad(blk.gt, blk.buf, blk.dt, self.gw(blk.tconv), pro_scale=blk.bn_t.scale,
                                           pro_shift=blk.bn_t.shift, pro_act=ACT_RELU)
                     if ft <= blk.i_tbn:
                         OC.conv_dgrad_raw(blk.gt, blk.dt, self.w16(blk.tconv), None, dx_pitch=blk.ctot, mode=2,
@@ -285,10 +317,11 @@ class DenseNetExecutor(FusedExecutor):
             for dl in reversed(blk.layers):
                 if not dl.bwd:
                     break
+                self._wgrad_join()          # the previous layer's wgrads still read dy3 / dy1
                 self._finalize_slice(blk, dl.cin, GROWTH, blk.dy3)
                 w2 = dl.name + "_2_conv/kernel"
                 if dl.i_c2 in tr:
-                    OC.conv_wgrad_raw(dl.g2, dl.y1, blk.dy3, self.gw(w2), pro_scale=dl.bn1.scale,
+                    self._wgrad(dl.g2, dl.y1, blk.dy3, self.gw(w2), pro_scale=dl.bn1.scale,
                                       pro_shift=dl.bn1.shift, pro_act=ACT_RELU)
                 if ft > dl.i_bn1:
                     continue
@@ -308,7 +341,7 @@ class DenseNetExecutor(FusedExecutor):
                 w1 = dl.name + "_1_conv/kernel"
                 bn0 = dl.bn0
                 if dl.i_c1 in tr:
-                    OC.conv_wgrad_raw(dl.g1, blk.buf, blk.dy1, self.gw(w1), pro_scale=bn0.scale,
+                    self._wgrad(dl.g1, blk.buf, blk.dy1, self.gw(w1), pro_scale=bn0.scale,
                                       pro_shift=bn0.shift, pro_act=ACT_RELU)
                 if ft > dl.i_bn0:
                     continue
@@ -316,6 +349,7 @@ class DenseNetExecutor(FusedExecutor):
                                   bwd_scale=bn0.scale, bwd_shift=bn0.shift, bwd_act=ACT_RELU, gacc=blk.G,
                                   stat_a=bn0.sa, stat_b=bn0.sb)
                 self._consumer_bn_backward(blk, bn0)
+            self._wgrad_join()
             self.grads_ready(self._block_offsets[bi])
         # ---- stem ---------------------------------------------------------------------------------------
         if not p.stem_bwd:
