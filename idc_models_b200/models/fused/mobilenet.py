@@ -220,7 +220,30 @@ class MobileNetV2Executor(FusedExecutor):
         K.bn_bwd_apply(0 if bn.trainable else 1, g, x, out, channels, count, sa=bn.sa, sb=bn.sb,
                        mean=bn.mean, rstd=bn.rstd, scale=bn.scale, dgamma=bn.dgamma, dbeta=bn.dbeta)
 
+    # Weight-gradient kernels (1x1 and depthwise) run on a side stream beside the data-gradient chain: every
+    # buffer they read is per-block and written once per step, so the only join is at the end of the backward.
+    wgrad_side_stream = True
+
+    def _side(self, fn, *args, **kw) -> None:
+        if not self.wgrad_side_stream:
+            fn(*args, **kw)
+            return
+        if getattr(self, "_wg_stream", None) is None:
+            self._wg_stream = torch.cuda.Stream(device=self.net.device)
+        self._wg_stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self._wg_stream):
+            fn(*args, **kw)
+        self._wg_pending = True
+
     def _backward(self, p) -> None:
+        try:
+            self._backward_impl(p)
+        finally:
+            if getattr(self, "_wg_pending", False):
+                torch.cuda.current_stream().wait_stream(self._wg_stream)
+                self._wg_pending = False
+
+    def _backward_impl(self, p) -> None:
         ft, tr = self.first_trainable, self.trainable
         # ---- Conv_1 -------------------------------------------------------------------------------------
         last = p.blocks[-1]
@@ -230,7 +253,7 @@ class MobileNetV2Executor(FusedExecutor):
             return
         self._bn_apply(p.dpre_c, p.c_raw, p.dc_raw, 1280)
         if p.i_c in tr:
-            OC.conv_wgrad_raw(p.gc, last.out, p.dc_raw, self.gw("Conv_1/kernel"))
+            self._side(OC.conv_wgrad_raw, p.gc, last.out, p.dc_raw, self.gw("Conv_1/kernel"))
         if not last.bwd:
             return
         OC.conv_dgrad_raw(p.gc, p.dc_raw, self.w16("Conv_1/kernel"), last.dout, mode=0)
@@ -253,7 +276,7 @@ class MobileNetV2Executor(FusedExecutor):
                 return
             self._bn_apply(b.dout, b.p_raw, b.dp_raw, b.cout)
             if b.i_p in tr:
-                OC.conv_wgrad_raw(b.gp, b.d_raw, b.dp_raw, self.gw(b.prefix + "project/kernel"),
+                self._side(OC.conv_wgrad_raw, b.gp, b.d_raw, b.dp_raw, self.gw(b.prefix + "project/kernel"),
                                   pro_scale=b.bn_d.scale, pro_shift=b.bn_d.shift, pro_act=ACT_RELU6)
             stop = ft > b.i_dbn
             if not stop:
@@ -267,7 +290,7 @@ class MobileNetV2Executor(FusedExecutor):
                 self._bn_apply(b.dpre_d, b.d_raw, b.dd_raw, b.cexp)
                 dw_in, dw_bn = (b.e_raw, b.bn_e) if b.has_expand else (p.s_raw, p.bn_stem)
                 if b.i_d in tr:
-                    K.dwconv_wgrad(b.gd, dw_in, b.dd_raw, self.gw(b.prefix + "depthwise/depthwise_kernel"),
+                    self._side(K.dwconv_wgrad, b.gd, dw_in, b.dd_raw, self.gw(b.prefix + "depthwise/depthwise_kernel"),
                                    scale=dw_bn.scale, shift=dw_bn.shift, act=ACT_RELU6)
                 below = ft <= (b.i_ebn if b.has_expand else p.i_stem_bn)
                 if below:
@@ -281,7 +304,7 @@ class MobileNetV2Executor(FusedExecutor):
                         if need:
                             self._bn_apply(b.dpre_e, b.e_raw, b.de_raw, b.cexp)
                             if b.i_e in tr:
-                                OC.conv_wgrad_raw(b.ge, xin, b.de_raw, self.gw(b.prefix + "expand/kernel"))
+                                self._side(OC.conv_wgrad_raw, b.ge, xin, b.de_raw, self.gw(b.prefix + "expand/kernel"))
                             if prev is not None and prev.bwd:
                                 OC.conv_dgrad_raw(b.ge, b.de_raw, self.w16(b.prefix + "expand/kernel"),
                                                   prev.dout, mode=0, aux=b.dout if b.add else None)
@@ -292,7 +315,7 @@ class MobileNetV2Executor(FusedExecutor):
                         self._bn_bwd(p.bn_stem, self._cnt(p.s_raw), p.c_stem, need)
                         if need:
                             self._bn_apply(p.dpre_stem, p.s_raw, p.ds_raw, 32)
-                            OC.conv_wgrad_raw(p.g_stem, p.x16, p.ds_raw, self.gw("Conv1/kernel"))
+                            self._side(OC.conv_wgrad_raw, p.g_stem, p.x16, p.ds_raw, self.gw("Conv1/kernel"))
                         return
             # the main branch stopped inside this block; only a residual can carry gradient on
             if b.add and prev is not None and prev.bwd:
