@@ -68,6 +68,24 @@ class ChainExecutor(FusedExecutor):
                 st["dy"] = torch.zeros_like(st["y"])
         return p
 
+    wgrad_side_stream = True
+
+    def _side(self, fn, *args, **kw) -> None:
+        if not self.wgrad_side_stream:
+            fn(*args, **kw)
+            return
+        if getattr(self, "_wg_stream", None) is None:
+            self._wg_stream = torch.cuda.Stream(device=self.net.device)
+        self._wg_stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self._wg_stream):
+            fn(*args, **kw)
+        self._wg_pending = True
+
+    def _side_join(self) -> None:
+        if getattr(self, "_wg_pending", False):
+            torch.cuda.current_stream().wait_stream(self._wg_stream)
+            self._wg_pending = False
+
     def grad_ready_offsets(self) -> list:
         st = self.net.store
         offs = [st.slots[l.spec.params[0].name].offset for l in self.net.layers
@@ -127,7 +145,8 @@ class ChainExecutor(FusedExecutor):
                 g = st["geom"]
                 wname = layer.spec.params[0].name
                 if layer.index in self.trainable:
-                    OC.conv_wgrad_raw(g, st["x"], st["dy"], self.gw(wname))
+                    # beside the data-gradient kernel of the same layer (both only read x / dy; see DenseNet executor)
+                    self._side(OC.conv_wgrad_raw, g, st["x"], st["dy"], self.gw(wname))
                 if prev_needs:
                     pl = prev["layer"]
                     if prev["kind"] == "conv":
@@ -138,4 +157,7 @@ class ChainExecutor(FusedExecutor):
                     else:
                         OC.conv_dgrad_raw(g, st["dy"], self.w16(wname), prev["dy"], mode=0)
                 # this layer's weight gradient and (written by its consumer earlier) bias gradient are final
+                if self.grad_hook is not None:
+                    self._side_join()
                 self.grads_ready(self.net.store.slots[wname].offset)
+        self._side_join()
