@@ -210,8 +210,9 @@ class FusedSecureFederation:
         self.params.tensor[:k * n].view(k, n).copy_(self.out.tensor[None, :n].expand(k, n))
 
     # ---- evaluation (client 0's view, secure_fed_model.py:235) --------------------------------------------
-    def evaluate(self, x: torch.Tensor, y: torch.Tensor, steps: int | None = 20):
-        """loss, accuracy of local slot 0's model over ``steps`` batches of (x, y)."""
+    def evaluate(self, x: torch.Tensor, y: torch.Tensor, steps: int | None = 20, with_auc: bool = False):
+        """loss, accuracy (and, with ``with_auc``, the reference's per-batch sklearn AUROC averaged over batches,
+        secure_fed_model.py:81-82) of local slot 0's model over ``steps`` batches of (x, y)."""
         dev = self.world.device
         x = x.to(dev, torch.float32)
         y = y.to(dev, torch.float32).reshape(-1)
@@ -219,6 +220,7 @@ class FusedSecureFederation:
         tot = torch.zeros(4, dtype=torch.float64)
         saved_k = self.k_local
         nb = 0
+        aucs = []
         try:
             self.k_local = 1
             for s in range(0, x.shape[0], B):
@@ -229,9 +231,16 @@ class FusedSecureFederation:
                 self._launch(xb, yb, xb.shape[0], False)
                 tot += self.acc[0].double().cpu()
                 nb += 1
+                if with_auc:
+                    yt = yb.cpu().numpy()
+                    if 0 < yt.sum() < len(yt):       # sklearn raises on a single-class batch; Keras would skip it too
+                        from sklearn.metrics import roc_auc_score
+                        aucs.append(float(roc_auc_score(yt, self._logits[:xb.shape[0]].cpu().numpy())))
         finally:
             self.k_local = saved_k
         cnt = max(float(tot[2]), 1.0)
+        if with_auc:
+            return float(tot[0]) / cnt, float(tot[1]) / cnt, (sum(aucs) / len(aucs) if aucs else 0.0)
         return float(tot[0]) / cnt, float(tot[1]) / cnt
 
     def round_trip(self, epochs: int = 5):

@@ -349,6 +349,9 @@ def main_secure(argv: list) -> dict:
                     help="mask: pairwise Philox masks in a fixed-point ring (default); paillier: the reference's "
                          "element-wise Paillier ciphertexts (parity path, slow)")
     ap.add_argument("--paillier-bits", type=int, default=2048)
+    ap.add_argument("--fused-clients", action="store_true",
+                    help="map the clients onto the GPUs (torchrun: clients % GPUs == 0): all resident clients train in one "
+                         "launch per step and the masked sum is one kernel across GPUs (fed/secure_fused.py)")
     args = ap.parse_args(argv)
     np.random.seed(0)
     device = _device(args)
@@ -378,6 +381,9 @@ def main_secure(argv: list) -> dict:
                        batch_size=BATCH_SIZE, train_size=CLIENT_TRAIN_SIZE, test_size=CLIENT_TEST_SIZE,
                        session_seed=args.seed, protect=args.protect, keypair=keypair) for i in client_ids]
 
+    if args.fused_clients:
+        return _main_secure_fused(args, client_data, labeled_ds, NUM_CLIENTS, CLIENT_TRAIN_SIZE, TRAIN_SIZE, TEST_SIZE,
+                                  BATCH_SIZE, lr, device)
     clients = create_clients(client_data, np.arange(NUM_CLIENTS), args.percent)
     server = Server(NUM_CLIENTS)
     results = []
@@ -394,3 +400,43 @@ def main_secure(argv: list) -> dict:
             print(loss, acc, auc)
             results.append((loss, acc, auc))
     return {"clients": clients, "server": server, "results": results}
+
+
+def _materialise(ds):
+    xs, ys = [], []
+    for x, y in ds:
+        xs.append(np.asarray(x, dtype=np.float32))
+        ys.append(float(np.asarray(y).reshape(-1)[0]))
+    return torch.from_numpy(np.stack(xs)), torch.tensor(ys, dtype=torch.float32)
+
+
+def _main_secure_fused(args, client_data, labeled_ds, n_clients, client_train_size, train_size, test_size, batch_size,
+                       lr, device) -> dict:
+    """secure_fed_model.py's round loop (212-236) with the clients resident on the GPUs: same shards
+    (``shard(NUM_CLIENTS, i)`` then take), same epochs per round, same printed ``loss acc auc`` line of client 0."""
+    from .fed.secure_fused import FusedSecureFederation
+    if not str(device).startswith("cuda"):
+        raise SystemExit("--fused-clients needs CUDA devices")
+    world = World.from_env(device)
+    template = create_small_cnn(world.device, args.seed, lr)
+    fed = FusedSecureFederation(world, n_clients, args.percent, template=template, lr=lr, batch_size=batch_size,
+                                seed=args.seed, comm="fused")
+    for j, cid in enumerate(fed.client_ids()):
+        x, y = _materialise(client_data.shard(n_clients, int(cid)).take(client_train_size))
+        fed.set_client_data(j, x, y)
+    xt, yt = _materialise(labeled_ds.skip(train_size).take(min(test_size, 20 * batch_size)))
+    results = []
+    with Timer("Secure fed model"):
+        for _ in range(args.NUM_ROUNDS):
+            with Timer("Training for " + str(fed.k_local) + " resident clients"):
+                fed.client_fit(args.epochs)
+                torch.cuda.synchronize()
+            with Timer("Masked aggregation"):
+                fed.aggregate()
+                fed.client_update()
+                torch.cuda.synchronize()
+            loss, acc, auc = fed.evaluate(xt, yt, steps=20, with_auc=True)
+            if world.rank == 0:
+                print(loss, acc, auc)
+            results.append((loss, acc, auc))
+    return {"federation": fed, "results": results}
