@@ -216,6 +216,10 @@ def main_fed(argv: list) -> dict:
     ap.add_argument("--client-size", type=int, default=None)
     ap.add_argument("--pretrain-epochs", type=int, default=10)
     ap.add_argument("--fine-tune-at", type=int, default=15)
+    ap.add_argument("--placement", default="round_robin", choices=["round_robin", "balanced"],
+                    help="client -> GPU placement under torchrun (balanced: LPT on client sizes, fed/scheduler.py)")
+    ap.add_argument("--fed-comm", default="fused", choices=["fused", "nccl"],
+                    help="aggregation path on GPUs: one fused kernel over NVLink peer memory, or the library baseline")
     args = ap.parse_args(argv)
     np.random.seed(0)
     path_data = args.path
@@ -294,8 +298,9 @@ def main_fed(argv: list) -> dict:
                                              metrics=[BinaryAccuracy()])
 
     fed_avg = tff_learning.build_federated_averaging_process(
-        model_fn, client_optimizer_fn=lambda: RMSprop(lr=base_learning_rate / 10))
-    evaluation = tff_learning.build_federated_evaluation(model_fn)
+        model_fn, client_optimizer_fn=lambda: RMSprop(lr=base_learning_rate / 10), comm=args.fed_comm,
+        placement=args.placement)
+    evaluation = tff_learning.build_federated_evaluation(model_fn, placement=args.placement)
 
     print("Starting federated training")
     rounds = []
