@@ -105,3 +105,61 @@ def test_jsonl_logger_and_device_timer(tmp_path):
     JsonlLogger(None).log("epoch", epoch=2)               # disabled logger: no file, no error
     JsonlLogger(str(path), rank=1).log("epoch", epoch=3)  # only rank 0 writes
     assert len(path.read_text().splitlines()) == 2
+
+
+FED_WORKER = r'''
+import sys, json, torch
+sys.path.insert(0, %r)
+from idc_models_b200.fed import fedavg as F
+from idc_models_b200.models.applications import build_transfer_model
+from idc_models_b200.optim.optimizers import SGD
+from idc_models_b200.parallel.strategy import FederatedStrategy
+from idc_models_b200.parallel.world import World
+placement = sys.argv[1]
+world = World.from_env("cpu")
+strategy = FederatedStrategy(world)
+def model_fn():
+    with strategy.scope():
+        m = build_transfer_model("mobilenet_v2_tiny", device="cpu", seed=0)
+        m.base.trainable = False          # head only: deterministic, cheap
+    return F.from_keras_model(m, loss="bce", metrics=["accuracy"])
+g = torch.Generator().manual_seed(0)
+def client(n_batches):
+    return [(torch.rand(8, 50, 50, 3, generator=g), (torch.rand(8, generator=g) > 0.5).float()) for _ in range(n_batches)]
+data = [client(4), client(1), client(1)]          # unequal clients: balanced puts the big one alone on a rank
+fed = F.build_federated_averaging_process(model_fn, client_optimizer_fn=lambda: SGD(learning_rate=0.1), placement=placement)
+state = fed.initialize()
+state, metrics = fed.next(state, data)
+ev = F.build_federated_evaluation(model_fn, placement=placement)(state.model, data)
+mine = F._local_clients(data, world, placement)
+outs = world.all_gather_object((float(state.master.double().sum()), metrics[1], ev[1], [len(d) for d in mine]))
+if world.rank == 0:
+    print("RESULT " + json.dumps(outs))
+world.shutdown()
+''' % str(ROOT)
+
+
+def _run_fed(placement, nproc):
+    import json
+    script = ROOT / "build" / "_fed_cpu_worker.py"
+    script.parent.mkdir(exist_ok=True)
+    script.write_text(FED_WORKER)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), str(script), placement]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, OMP_NUM_THREADS="2"))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    return json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][7:])
+
+
+def test_fedavg_client_placement_does_not_change_the_result():
+    """3 unequal clients on 2 gloo ranks: round-robin and balanced (LPT) placement aggregate to the same server model
+    and the same example-weighted metrics as the single-process run; balanced gives the big client a rank of its own."""
+    one = _run_fed("round_robin", 1)[0]
+    rr = _run_fed("round_robin", 2)
+    bal = _run_fed("balanced", 2)
+    assert sorted(map(tuple, (o[3] for o in bal))) == [(1, 1), (4,)]
+    assert sorted(map(tuple, (o[3] for o in rr))) == [(1,), (4, 1)]
+    for outs in (rr, bal):
+        for o in outs:
+            assert abs(o[0] - one[0]) < 1e-4 * max(1.0, abs(one[0]))
+            assert abs(o[1] - one[1]) < 1e-5 and abs(o[2] - one[2]) < 1e-5
