@@ -138,3 +138,118 @@ def load_into(net, path: str, by_name: bool = True, strict: bool = True) -> list
     if strict and missing:
         raise KeyError(f"{path}: missing weights {missing[:5]}{'...' if len(missing) > 5 else ''}")
     return missing
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Full-model file (``model.save("m.h5")``): /model_weights/... + model_config / training_config attributes +
+# /optimizer_weights. ``load_into`` already accepts such a file (weights are matched by the
+# tail of their path); ``load_optimizer_state`` restores the optimizer slots.
+# ---------------------------------------------------------------------------------------------------------
+def _optimizer_entries(net) -> tuple:
+    """(names, {name: array}) in Keras' naming: ``<Opt>/iter:0``, hyper-parameters, then one slot per trainable
+    variable (``<Opt>/<var>/rms:0`` for RMSprop, ``/momentum:0`` for SGD, ``/m:0`` and ``/v:0`` for Adam)."""
+    import numpy as np
+    opt = net.optimizer
+    if opt is None:
+        return [], {}
+    cls = {"rmsprop": "RMSprop", "sgd": "SGD", "adam": "Adam"}[opt.kind]
+    names, data = [], {}
+
+    def put(n, a):
+        names.append(n)
+        data[n] = np.asarray(a, dtype=np.float32)
+
+    put(f"{cls}/iter:0", [float(opt.iterations)])
+    put(f"{cls}/learning_rate:0", [float(opt.learning_rate)])
+    slots = {"rmsprop": [("rms", "s1")], "sgd": [("momentum", "s1")], "adam": [("m", "s1"), ("v", "s2")]}[opt.kind]
+    st = net.store
+    ranges = opt.ranges
+    for wn in st.order:
+        sl = st.slots[wn]
+        if not sl.trainable_kind or not any(b <= sl.offset < e for b, e in ranges):
+            continue
+        for suffix, attr in slots:
+            buf = getattr(opt, attr)
+            if buf is None:
+                continue
+            put(f"{cls}/{wn}/{suffix}:0", net._to_keras(sl.kind, st._logical(buf, sl)))
+    return names, data
+
+
+def save_model(net, path: str) -> None:
+    """Keras full-model HDF5 layout: the weights-only tree under ``/model_weights``, JSON ``model_config`` and
+    ``training_config`` root attributes, optimizer state under ``/optimizer_weights``."""
+    import json
+    if net.strategy.world.rank != 0:
+        return
+    named = net.named_weights()
+    nb = len(net.base.layers)
+    nested = nb != len(net.layers)
+    layer_names = _keras_layer_names(net)
+    groups: dict = {n: [] for n in layer_names}
+    for l in net.layers:
+        if l.spec.kind == "input":
+            continue
+        top = net.base.name if (nested and l.index < nb) else l.name
+        for p in l.spec.params:
+            groups[top].append(p.name + ":0")
+    datasets = {}
+    for top, names in groups.items():
+        for wn in names:
+            datasets[f"model_weights/{top}/{wn}"] = named[wn[:-2]]
+    config = {"class_name": "Sequential",
+              "config": {"name": net.name, "layers": [{"class_name": l.spec.kind, "config": {"name": l.name, "trainable": bool(l.trainable)}}
+                                                       for l in net.layers]},
+              "input_shape": list(net.input_shape), "base": net.base.name}
+    opt = net.optimizer
+    training = {"loss": getattr(net.loss, "kind", None), "metrics": [getattr(m, "name", str(m)) for m in (net.metrics or [])],
+                "optimizer_config": ({"class_name": opt.kind, "config": {"learning_rate": float(opt.learning_rate)}} if opt else None)}
+    attrs = [("", "backend", ["tensorflow"], True), ("", "keras_version", ["2.2.4-tf"], True),
+             ("", "model_config", [json.dumps(config)], True), ("", "training_config", [json.dumps(training)], True),
+             ("model_weights", "backend", ["tensorflow"], True), ("model_weights", "keras_version", ["2.2.4-tf"], True)]
+
+    def add(group, name, values):
+        size = max([len(v) for v in values] + [1]) * max(len(values), 1)
+        if size <= 60000:
+            attrs.append((group, name, values, False))
+            return
+        per = max(1, 60000 // max(len(v) for v in values))
+        for i in range(0, len(values), per):
+            attrs.append((group, f"{name}{i // per}", values[i:i + per], False))
+    add("model_weights", "layer_names", layer_names)
+    for top, names in groups.items():
+        add(f"model_weights/{top}", "weight_names", names)
+    onames, odata = _optimizer_entries(net)
+    if onames:
+        for n in onames:
+            datasets[f"optimizer_weights/{n}"] = odata[n]
+        add("optimizer_weights", "weight_names", onames)
+    write_h5(path, datasets, attrs)
+
+
+def load_optimizer_state(net, path: str) -> int:
+    """Restore the optimizer slots written by :func:`save_model` into the compiled model's optimizer (same optimizer
+    class). Returns the number of slot tensors restored."""
+    data, _ = read_h5(path)
+    opt = net.optimizer
+    if opt is None:
+        raise RuntimeError("compile the model before loading optimizer state")
+    cls = {"rmsprop": "RMSprop", "sgd": "SGD", "adam": "Adam"}[opt.kind]
+    slots = {"rmsprop": [("rms", "s1")], "sgd": [("momentum", "s1")], "adam": [("m", "s1"), ("v", "s2")]}[opt.kind]
+    st = net.store
+    n = 0
+    it = data.get(f"optimizer_weights/{cls}/iter:0")
+    if it is not None:
+        opt.iterations = int(round(float(it.reshape(-1)[0])))
+    for wn in st.order:
+        sl = st.slots[wn]
+        if not sl.trainable_kind:
+            continue
+        for suffix, attr in slots:
+            a = data.get(f"optimizer_weights/{cls}/{wn}/{suffix}:0")
+            buf = getattr(opt, attr)
+            if a is None or buf is None:
+                continue
+            st._logical(buf, sl).copy_(net._from_keras(sl.kind, a).to(buf.device))
+            n += 1
+    return n

@@ -206,6 +206,17 @@ class Network:
         from ..io import checkpoint
         checkpoint.load_weights(self, path)
 
+    def save(self, path: str) -> None:
+        """``model.save("m.h5")``: Keras full-model HDF5 (weights under /model_weights, model / training config,
+        optimizer state). Any other extension writes the flat weights-only checkpoint."""
+        self.strategy.aggregate_moving_stats(self.store)
+        if path.endswith((".h5", ".hdf5")):
+            from ..io import keras_h5
+            keras_h5.save_model(self, path)
+        else:
+            from ..io import checkpoint
+            checkpoint.save_weights(self, path)
+
     # ---- executor -------------------------------------------------------------------------------
     @property
     def executor(self):

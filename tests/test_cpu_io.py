@@ -95,3 +95,42 @@ def test_not_an_hdf5_file_is_a_clear_error(tmp_path):
     p.write_bytes(b"hello world" * 100)
     with pytest.raises(IOError, match="not an HDF5 file"):
         keras_h5.read_h5(str(p))
+
+
+def test_full_model_h5_with_optimizer_state_roundtrip(tmp_path):
+    """``model.save('m.h5')``: weights under /model_weights, JSON configs, optimizer slots under /optimizer_weights;
+    a fresh model loads the weights from it and its optimizer resumes from the saved state."""
+    import json
+    import torch
+    from idc_models_b200.io import keras_h5
+    from idc_models_b200.models.applications import build_transfer_model
+    from idc_models_b200.optim.optimizers import RMSprop
+
+    def make(seed):
+        m = build_transfer_model("mobilenet_v2_tiny", (50, 50, 3), 1, device="cpu", seed=seed)
+        m.base.trainable = True
+        m.compile(optimizer=RMSprop(lr=1e-3), loss="bce", metrics=["accuracy"])
+        return m
+    g = torch.Generator().manual_seed(0)
+    x, y = torch.rand(8, 50, 50, 3, generator=g), (torch.rand(8, generator=g) > 0.5).float()
+    a = make(0)
+    for _ in range(2):
+        a.train_on_batch(x, y)
+    path = str(tmp_path / "model.h5")
+    a.save(path)
+    data, attrs = keras_h5.read_h5(path)
+    assert any(k.startswith("model_weights/") and k.endswith("/kernel:0") for k in data)
+    assert "optimizer_weights/RMSprop/iter:0" in data and float(data["optimizer_weights/RMSprop/iter:0"][0]) == 2.0
+    assert any(k.startswith("optimizer_weights/RMSprop/") and k.endswith("/rms:0") for k in data)
+    cfg = [v for (grp, name), v in attrs.items() if name == "model_config"] if isinstance(attrs, dict) else None
+    if cfg:
+        assert json.loads(cfg[0][0] if isinstance(cfg[0], (list, tuple)) else cfg[0])["class_name"] == "Sequential"
+    b = make(1)
+    b.load_weights(path)
+    assert keras_h5.load_optimizer_state(b, path) > 0
+    assert torch.equal(a.store.master, b.store.master) and torch.equal(a.store.stats, b.store.stats)
+    assert b.optimizer.iterations == 2 and torch.allclose(a.optimizer.s1, b.optimizer.s1)
+    # both continue identically
+    a.train_on_batch(x, y)
+    b.train_on_batch(x, y)
+    assert torch.allclose(a.store.master, b.store.master, atol=1e-7)
