@@ -88,3 +88,15 @@ def test_get_set_weights_keras_layouts_roundtrip():
     assert all((a == b).all() for a, b in zip(w, m2.get_weights()))
     # channel-padded stem storage keeps its pad lanes at zero
     assert m2.store.storage_view("block1_conv1/kernel", "master")[..., 3:].abs().max() == 0
+
+
+def test_densenet201_cifar_fine_tune_set_matches_survey():
+    """dist_model_tf_dense.py: DenseNet201, 32x32x3, 10 classes, fine_tune_at = 150 -> 479 trainable tensors,
+    16,611,530 floats in the packed gradient all-reduce."""
+    m = build_transfer_model("densenet201", (32, 32, 3), 10, device="cpu")
+    m.base.trainable = True
+    for l in m.base.layers[:150]:
+        l.trainable = False
+    tw = m.trainable_weights
+    assert len(tw) == 479
+    assert sum(t.numel() for t in tw) == 16611530
