@@ -113,6 +113,12 @@ int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const void* w, void
 int idcb_conv_wgrad(const idcb_conv_desc* d, const void* x, const void* dy, float* dw,
                     const float* pro_scale, const float* pro_shift, int pro_act, void* stream);
 
+/* Profiling aid: when dev_ptr is non-null, CTA (0,0) of every following conv launch writes clock64() stamps of its
+ * phases (entry, setup done, first tile, producers done, first MMA, last MMA, accumulator ready, ...) into the 16
+ * int64 slots it points to (scripts/conv_phases.py). Pass NULL to switch it off. Note that the stamping thread's
+ * own global stores delay its next release-arrive, so stamps perturb what they measure by a few microseconds. */
+int idcb_conv_set_debug(void* dev_ptr);
+
 /* ---- depthwise 3x3 convolution (direct, bandwidth-bound) ------------------------------------ */
 /* TF depthwise kernels behind DepthwiseConv2D in MobileNetV2 (dist_model_tf_mobile.py:119;
  * SURVEY 2.E K7). Weights bf16 [3][3][C]; the descriptor has cin == cout == C.
