@@ -50,3 +50,22 @@ def test_secure_fed_model_script(tmp_path):
     assert out.count("Decryption for client 0 took") == 2
     assert len(re.findall(r"^[\d.]+ [\d.]+ [\d.]+$", out, flags=re.M)) == 2
     assert "Secure fed model took" in out
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference` prints one JSON line {"impl": "reference", "unavailable": ...} and exits 0 (the
+    reference needs TensorFlow 2.1 / TFF / phe, none installable offline); the product arm refuses to run without CUDA."""
+    import json
+    import subprocess
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    r = subprocess.run([sys.executable, str(root / "bench.py"), "--impl", "reference", "--gpus", "1", "--steps", "2",
+                        "--warmup", "3"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and isinstance(line["unavailable"], str) and line["unavailable"]
+    import torch
+    if not torch.cuda.is_available():
+        r = subprocess.run([sys.executable, str(root / "bench.py")], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 2 and "CUDA" in r.stderr
