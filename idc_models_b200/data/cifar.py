@@ -1,0 +1,73 @@
+"""On-disk CIFAR-10 reader: the data source of the dense script, which the reference gets from
+``tfds.load(name='cifar10', as_supervised=True)`` (/root/reference/dist_model_tf_dense.py:120-121).
+
+There is no network here, so nothing is downloaded; a copy the user has placed under ``<path>/data`` is
+read in either of the two layouts the dataset is distributed in:
+
+* ``cifar-10-batches-bin``: ``data_batch_{1..5}.bin`` + ``test_batch.bin``, records of 1 label byte followed by
+  3072 pixel bytes stored plane by plane (R, G, B; each 32 rows of 32);
+* ``cifar-10-batches-py``: ``data_batch_{1..5}`` + ``test_batch``, pickled dicts with ``data`` (N x 3072 uint8,
+  same plane order) and ``labels``.
+
+Images come back as uint8 NHWC arrays (what tfds yields), labels as int64.
+"""
+from __future__ import annotations
+
+import os
+import pickle
+
+import numpy as np
+
+_BIN, _PY = "cifar-10-batches-bin", "cifar-10-batches-py"
+_RECORD = 1 + 3 * 32 * 32
+
+
+def find_cifar10(path: str) -> str | None:
+    """Directory of an on-disk CIFAR-10 copy under ``path`` (or ``path/data``), or None."""
+    for root in (os.path.join(path, "data"), path):
+        for name in (_BIN, _PY):
+            for d in (os.path.join(root, name), os.path.join(root, "cifar10", name)):
+                if os.path.isdir(d):
+                    return d
+    return None
+
+
+def _planes_to_nhwc(flat: np.ndarray) -> np.ndarray:
+    return np.ascontiguousarray(flat.reshape(-1, 3, 32, 32).transpose(0, 2, 3, 1))
+
+
+def _read_bin(files):
+    xs, ys = [], []
+    for f in files:
+        raw = np.fromfile(f, dtype=np.uint8)
+        if raw.size == 0 or raw.size % _RECORD:
+            raise ValueError(f"{f}: size {raw.size} is not a whole number of {_RECORD}-byte CIFAR-10 records")
+        rec = raw.reshape(-1, _RECORD)
+        ys.append(rec[:, 0].astype(np.int64))
+        xs.append(_planes_to_nhwc(rec[:, 1:]))
+    return np.concatenate(xs), np.concatenate(ys)
+
+
+def _read_py(files):
+    xs, ys = [], []
+    for f in files:
+        with open(f, "rb") as fh:
+            d = pickle.load(fh, encoding="bytes")
+        data = d[b"data"] if b"data" in d else d["data"]
+        labels = d.get(b"labels", d.get("labels"))
+        xs.append(_planes_to_nhwc(np.asarray(data, dtype=np.uint8)))
+        ys.append(np.asarray(labels, dtype=np.int64))
+    return np.concatenate(xs), np.concatenate(ys)
+
+
+def load_cifar10(directory: str):
+    """((x_train, y_train), (x_test, y_test)) from a ``cifar-10-batches-{bin,py}`` directory."""
+    is_bin = os.path.basename(os.path.normpath(directory)) == _BIN or os.path.exists(os.path.join(directory, "test_batch.bin"))
+    ext = ".bin" if is_bin else ""
+    train = [os.path.join(directory, f"data_batch_{i}{ext}") for i in range(1, 6)]
+    train = [f for f in train if os.path.exists(f)]
+    test = os.path.join(directory, f"test_batch{ext}")
+    if not train or not os.path.exists(test):
+        raise FileNotFoundError(f"{directory}: expected data_batch_1..5{ext} and test_batch{ext}")
+    read = _read_bin if is_bin else _read_py
+    return read(train), read([test])

@@ -216,26 +216,49 @@ class Dataset:
             q: queue.Queue = queue.Queue(maxsize=depth)
             stop = object()
             err: list = []
+            cancelled = threading.Event()
+
+            def put(e) -> bool:
+                # a consumer that stopped early (evaluate(steps=20), next(iter(ds))) must not leave this
+                # thread blocked on a full queue for ever, with the upstream generators suspended
+                while not cancelled.is_set():
+                    try:
+                        q.put(e, timeout=0.05)
+                        return True
+                    except queue.Full:
+                        continue
+                return False
 
             def work():
+                it_src = iter(src)
                 try:
-                    for e in src:
-                        q.put(e)
+                    for e in it_src:
+                        if not put(e):
+                            break
                 except BaseException as ex:  # noqa: BLE001
                     err.append(ex)
                 finally:
-                    q.put(stop)
+                    close = getattr(it_src, "close", None)
+                    if close is not None:
+                        try:
+                            close()         # unwinds upstream generators (map's thread pool shuts down)
+                        except Exception:   # noqa: BLE001
+                            pass
+                    put(stop)
             th = threading.Thread(target=work, daemon=True)
             th.start()
 
             def it():
-                while True:
-                    e = q.get()
-                    if e is stop:
-                        if err:
-                            raise err[0]
-                        return
-                    yield e
+                try:
+                    while True:
+                        e = q.get()
+                        if e is stop:
+                            if err:
+                                raise err[0]
+                            return
+                        yield e
+                finally:
+                    cancelled.set()         # GeneratorExit / exhaustion / error: release the producer
             return it()
         return Dataset(gen, self._len)
 

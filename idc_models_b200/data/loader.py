@@ -114,29 +114,37 @@ class NativeLoader:
         # device consumer: H2D of batch k+1 is in flight on the copy stream while batch k is being used
         dev, cs = self.device, self._copy_stream
         pending = None            # (x_dev, y_dev, event, slot)
-        for s, c in self._host_batches():
-            with torch.cuda.stream(cs):
-                xd = self.slot_x[s][:c].to(dev, non_blocking=True)
-                yd = self.slot_y[s][:c].to(dev, non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record(cs)
+        try:
+            for s, c in self._host_batches():
+                with torch.cuda.stream(cs):
+                    xd = self.slot_x[s][:c].to(dev, non_blocking=True)
+                    yd = self.slot_y[s][:c].to(dev, non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(cs)
+                prev, pending = pending, (xd, yd, ev, s)
+                if prev is not None:
+                    px, py, pev, ps = prev
+                    pev.synchronize()                          # its copy has left the pinned slot
+                    lib.idcbh_loader_release(h, ps)
+                    torch.cuda.current_stream(dev).wait_event(pev)
+                    px.record_stream(torch.cuda.current_stream(dev))
+                    py.record_stream(torch.cuda.current_stream(dev))
+                    yield px, py
             if pending is not None:
                 px, py, pev, ps = pending
-                pev.synchronize()                          # its copy has left the pinned slot
+                pending = None
+                pev.synchronize()
                 lib.idcbh_loader_release(h, ps)
                 torch.cuda.current_stream(dev).wait_event(pev)
                 px.record_stream(torch.cuda.current_stream(dev))
                 py.record_stream(torch.cuda.current_stream(dev))
                 yield px, py
-            pending = (xd, yd, ev, s)
-        if pending is not None:
-            px, py, pev, ps = pending
-            pev.synchronize()
-            lib.idcbh_loader_release(h, ps)
-            torch.cuda.current_stream(dev).wait_event(pev)
-            px.record_stream(torch.cuda.current_stream(dev))
-            py.record_stream(torch.cuda.current_stream(dev))
-            yield px, py
+        finally:
+            # the consumer stopped early (steps_per_epoch, evaluate(steps=...)): the slot whose copy was
+            # already issued must go back to the ring or the producer threads stall on the next epoch
+            if pending is not None and getattr(self, "_h", None):
+                pending[2].synchronize()
+                lib.idcbh_loader_release(h, pending[3])
 
     def close(self) -> None:
         if getattr(self, "_h", None):

@@ -127,13 +127,25 @@ def save_weights(net, path: str) -> None:
 def load_into(net, path: str, by_name: bool = True, strict: bool = True) -> list:
     """Load every weight whose Keras name appears in the file; returns the names that were missing."""
     data, _ = read_h5(path)
-    by_suffix = {}
-    for p, a in data.items():
-        if p.endswith(":0"):
-            parts = p[:-2].split("/")
-            for i in range(len(parts)):
-                by_suffix.setdefault("/".join(parts[i:]), a)
-    found = {n: by_suffix[n] for n in net.weight_names() if n in by_suffix}
+    # A Keras file stores weight <w> of top-level layer <top> at /<top>/<w>:0 (under /model_weights for a
+    # model.save file). The same short name can also end a longer path ("bn/gamma" ends ".../conv1/bn/gamma"),
+    # so the match with the fewest leading groups wins and a tie is an error rather than a guess that depends
+    # on the order the file lists its groups in.
+    paths = {p[:-2].strip("/"): a for p, a in data.items() if p.endswith(":0")}
+    by_tail: dict[str, list] = {}
+    for p in paths:
+        by_tail.setdefault(p.rsplit("/", 1)[-1], []).append(p)
+    found = {}
+    for n in net.weight_names():
+        cands = [p for p in by_tail.get(n.rsplit("/", 1)[-1], ()) if p == n or p.endswith("/" + n)]
+        if not cands:
+            continue
+        depth = lambda p: p.count("/") - n.count("/")      # noqa: E731 - number of leading groups
+        best = min(depth(p) for p in cands)
+        top = [p for p in cands if depth(p) == best]
+        if len(top) > 1:
+            raise KeyError(f"{path}: weight name {n!r} is ambiguous: {top[:3]}")
+        found[n] = paths[top[0]]
     missing = net.set_named_weights(found, strict=False)
     if strict and missing:
         raise KeyError(f"{path}: missing weights {missing[:5]}{'...' if len(missing) > 5 else ''}")

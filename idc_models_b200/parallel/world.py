@@ -95,5 +95,11 @@ class World:
 
     def shutdown(self) -> None:
         if dist.is_initialized():
+            # a rank that tears the transport down while a peer is still inside its last collective makes
+            # that peer abort (gloo: SIGABRT); leave together
+            try:
+                self.barrier()
+            except Exception:  # noqa: BLE001 - a peer that already died must not turn shutdown into a hang report
+                pass
             dist.destroy_process_group()
         World._default = None

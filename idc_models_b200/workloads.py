@@ -77,6 +77,15 @@ def _common_flags(ap: argparse.ArgumentParser) -> None:
     ap.add_argument("--steps-per-epoch", type=int, default=None, help="cap the steps of every epoch (smoke runs)")
     ap.add_argument("--graphs", action="store_true", help="replay the fused step as a CUDA graph")
     ap.add_argument("--log-jsonl", default=None, help="append one JSON record per epoch / round to this file")
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"],
+                    help="compute dtype: bf16 = the fused tcgen05 pipeline on CUDA (bf16-emulating reference executor on "
+                         "CPU); fp32 = the fp32 reference executor on either device")
+    ap.add_argument("--gpus", type=int, default=None,
+                    help="expected number of replicas/processes (one per GPU, launched by torchrun); checked, not spawned")
+    ap.add_argument("--shuffle-buffer", type=int, default=1000, help="tf.data shuffle buffer (BUFFER_SIZE / shuffle(1000))")
+    ap.add_argument("--train-split", type=float, default=0.8, help="fraction of the listing used for training")
+    ap.add_argument("--val-split", type=float, default=None,
+                    help="validation fraction (default: 0.1 for the transfer scripts, 0.2 for the federated ones)")
     ap.add_argument("--native-loader", action="store_true",
                     help="serve the cached training set from the C++ loader (threads + pinned ring + async H2D)")
 
@@ -85,6 +94,18 @@ def _device(args) -> str:
     if args.device:
         return args.device
     return "cuda" if torch.cuda.is_available() else "cpu"
+
+
+def _executor_kind(args, device: str) -> str:
+    if args.dtype == "fp32":
+        return "reference"
+    return "auto"        # CUDA: fused bf16 kernels; CPU: the PyTorch reference executor
+
+
+def _check_gpus(args, world) -> None:
+    if args.gpus is not None and args.gpus != world.size:
+        raise SystemExit(f"--gpus {args.gpus}: {world.size} process(es) are running; launch one per GPU with "
+                         f"`python -m torch.distributed.run --nproc-per-node {args.gpus} --master-addr 127.0.0.1 <script> ...`")
 
 
 def _make_strategy(kind: str, device: str, comm: str):
@@ -96,14 +117,40 @@ def _make_strategy(kind: str, device: str, comm: str):
 
 def _idc_dataset(path: str, pattern: str, size: int, img_shape, synthetic_only: bool, seed: int, label_as_int=False,
                  order="shuffled"):
+    """The labelled patch dataset behind every script. ``order="shuffled"`` is the IID listing
+    (``list_files(<pattern>, shuffle=True)``); ``order="class_sorted"`` is fed_model.py's non-IID listing
+    (/root/reference/fed_model.py:161-164): the class ``1/`` files, shuffled among themselves, followed by
+    the class ``0/`` files, so consecutive ``skip/take`` client shards are single-class."""
     files = [] if synthetic_only else glob.glob(os.path.join(path, pattern))
     if files:
-        list_ds = Dataset.list_files(os.path.join(path, pattern), shuffle=True, seed=seed)
-        # shuffled once, then frozen: the reference re-shuffles every epoch, which leaks train into validation
-        frozen = list(list_ds)
+        if order == "class_sorted":
+            root = os.path.join(path, pattern)
+            assert root.endswith("/*/*"), "the class-sorted listing expects a <class>/<file> layout"
+            root = root[:-len("/*/*")]
+            ones = list(Dataset.list_files(os.path.join(root, "1", "*"), shuffle=True, seed=seed))
+            zeros = list(Dataset.list_files(os.path.join(root, "0", "*"), shuffle=True, seed=seed + 1))
+            frozen = ones + zeros
+        else:
+            list_ds = Dataset.list_files(os.path.join(path, pattern), shuffle=True, seed=seed)
+            # shuffled once, then frozen: the reference re-shuffles every epoch, which leaks train into validation
+            frozen = list(list_ds)
         ds = Dataset.from_generator(lambda: frozen, len(frozen))
         return ds.map(make_process_path(img_shape[:2], label_as_int), num_parallel_calls=-1), len(frozen)
     return synthetic.synthetic_idc(size, img_shape, seed, order, label_as_int), size
+
+
+def _cifar10_datasets(path: str, n_train: int, synthetic_only: bool, seed: int):
+    """``tfds.load('cifar10')`` of /root/reference/dist_model_tf_dense.py:120-121: an on-disk copy under
+    ``<path>/data`` (binary or python version, data/cifar.py) when there is one, else the synthetic stand-in."""
+    from .data import cifar
+    if not synthetic_only:
+        found = cifar.find_cifar10(path)
+        if found is not None:
+            (xtr, ytr), (xte, yte) = cifar.load_cifar10(found)
+            print(f"CIFAR-10 from {found}: {len(xtr)} train / {len(xte)} test images")
+            return (Dataset.from_tensor_slices((xtr, ytr)), Dataset.from_tensor_slices((xte, yte)), len(xtr))
+    n_test = max(n_train // 5, 1)
+    return synthetic.synthetic_cifar10(n_train, seed), synthetic.synthetic_cifar10(n_test, seed + 1), n_train
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -131,6 +178,7 @@ def main_transfer(cfg: TransferConfig, argv: list) -> dict:
         img_shape, units = (50, 50, 3), 1
     device = _device(args)
     strategy = _make_strategy("central" if args.central_storage else "mirrored", device, args.comm)
+    _check_gpus(args, strategy.world)
     num_devices = strategy.num_replicas_in_sync
     batch = args.batch_size or cfg.batch_size
     BATCH_SIZE = batch * num_devices if cfg.batch_per_replica else batch
@@ -140,28 +188,28 @@ def main_transfer(cfg: TransferConfig, argv: list) -> dict:
 
     if dataset_kind == "cifar10":
         # tfds.load('cifar10') stand-in; train and "validation"(=test split) each .repeat(2)
-        n_test = max(DATASET_SIZE // 5, 1)
-        train = synthetic.synthetic_cifar10(DATASET_SIZE, args.seed).map(synthetic.scale)
-        test = synthetic.synthetic_cifar10(n_test, args.seed + 1).map(synthetic.scale)
-        train_batches = train.cache().shuffle(1000, seed=args.seed).batch(BATCH_SIZE).repeat(2)
-        validation_batches = test.cache().shuffle(1000, seed=args.seed).batch(BATCH_SIZE).repeat(2)
+        train, test, DATASET_SIZE = _cifar10_datasets(path, DATASET_SIZE, args.synthetic, args.seed)
+        train, test = train.map(synthetic.scale), test.map(synthetic.scale)
+        train_batches = train.cache().shuffle(args.shuffle_buffer, seed=args.seed).batch(BATCH_SIZE).repeat(2)
+        validation_batches = test.cache().shuffle(args.shuffle_buffer, seed=args.seed).batch(BATCH_SIZE).repeat(2)
     else:
         labeled_ds, DATASET_SIZE = _idc_dataset(path, cfg.dataset_glob or MOBILE.dataset_glob, DATASET_SIZE, img_shape,
                                                 args.synthetic, args.seed)
-        TRAIN_SIZE = int(0.8 * DATASET_SIZE)
-        VALIDATION_SIZE = int(0.1 * DATASET_SIZE)
+        TRAIN_SIZE = int(args.train_split * DATASET_SIZE)
+        VALIDATION_SIZE = int((0.1 if args.val_split is None else args.val_split) * DATASET_SIZE)
         TEST_SIZE = DATASET_SIZE - TRAIN_SIZE - VALIDATION_SIZE
         train_ds = labeled_ds.take(TRAIN_SIZE)
         validation_ds = labeled_ds.skip(TRAIN_SIZE).take(VALIDATION_SIZE)
         test_ds = labeled_ds.skip(TRAIN_SIZE + VALIDATION_SIZE).take(TEST_SIZE)
         if args.native_loader:
             from .data.loader import NativeLoader
-            train_batches = NativeLoader.from_dataset(train_ds, BATCH_SIZE, 1000, seed=args.seed,
+            train_batches = NativeLoader.from_dataset(train_ds, BATCH_SIZE, args.shuffle_buffer, seed=args.seed,
                                                       device=device if device.startswith("cuda") else None)
         else:
-            train_batches = prepare_for_training(train_ds, BATCH_SIZE, seed=args.seed)
-        validation_batches = prepare_for_training(validation_ds, BATCH_SIZE, seed=args.seed)
-        test_batches = prepare_for_training(test_ds, BATCH_SIZE, seed=args.seed)  # built, never used (as upstream)
+            train_batches = prepare_for_training(train_ds, BATCH_SIZE, seed=args.seed, shuffle_buffer_size=args.shuffle_buffer)
+        validation_batches = prepare_for_training(validation_ds, BATCH_SIZE, seed=args.seed, shuffle_buffer_size=args.shuffle_buffer)
+        test_batches = prepare_for_training(test_ds, BATCH_SIZE, seed=args.seed,
+                                            shuffle_buffer_size=args.shuffle_buffer)  # built, never used (as upstream)
         del test_batches
 
     base_learning_rate = args.lr or cfg.base_learning_rate
@@ -171,7 +219,8 @@ def main_transfer(cfg: TransferConfig, argv: list) -> dict:
         base_model.trainable = False
         global_average_layer = apps.GlobalAveragePooling2D()
         prediction_layer = apps.Dense(units)
-        model = apps.Sequential([base_model, global_average_layer, prediction_layer], device=device, seed=args.seed)
+        model = apps.Sequential([base_model, global_average_layer, prediction_layer], device=device, seed=args.seed,
+                                executor=_executor_kind(args, device))
         model.compile(optimizer=RMSprop(lr=base_learning_rate), loss=loss(), metrics=["accuracy"])
     if args.graphs and device.startswith("cuda"):
         model.executor.use_graphs = True
@@ -218,6 +267,7 @@ def main_fed(argv: list) -> dict:
     ap.add_argument("--fine-tune-at", type=int, default=15)
     ap.add_argument("--placement", default="round_robin", choices=["round_robin", "balanced"],
                     help="client -> GPU placement under torchrun (balanced: LPT on client sizes, fed/scheduler.py)")
+    ap.add_argument("--validation-steps", type=int, default=20, help="batches of the pre-training evaluate() call")
     ap.add_argument("--fed-comm", default="fused", choices=["fused", "nccl"],
                     help="aggregation path on GPUs: one fused kernel over NVLink peer memory, or the library baseline")
     args = ap.parse_args(argv)
@@ -232,8 +282,8 @@ def main_fed(argv: list) -> dict:
     NUM_TEST_CLIENTS = NUM_CLIENTS - NUM_TRAIN_CLIENTS
     DATASET_SIZE = args.dataset_size or 30000
     CLIENT_SIZE = args.client_size or int(DATASET_SIZE / NUM_CLIENTS)
-    TRAIN_SIZE = int(0.8 * DATASET_SIZE)
-    VALIDATION_SIZE = int(0.2 * DATASET_SIZE)
+    TRAIN_SIZE = int(args.train_split * DATASET_SIZE)
+    VALIDATION_SIZE = int((0.2 if args.val_split is None else args.val_split) * DATASET_SIZE)
     BATCH_SIZE = args.batch_size or 32
     IMG_SHAPE = (50, 50, 3)
     base_learning_rate = args.lr or 0.001
@@ -242,6 +292,7 @@ def main_fed(argv: list) -> dict:
     labeled_ds, _ = _idc_dataset(path_data, "data/balanced_IDC_30k/*/*", DATASET_SIZE, IMG_SHAPE, args.synthetic,
                                  args.seed, label_as_int=True, order="shuffled" if is_iid else "class_sorted")
     strategy = FederatedStrategy(World.from_env(device))
+    _check_gpus(args, strategy.world)
     ckpt = os.path.join(path_data, "pretrained", "cp.ckpt")
     toTrain = not os.path.exists(ckpt)                       # intent of fed_model.py:175
 
@@ -250,14 +301,15 @@ def main_fed(argv: list) -> dict:
         cp_callback = ModelCheckpoint(filepath=checkpoint_path, save_weights_only=True, verbose=1)
         train_ds = labeled_ds.take(TRAIN_SIZE)
         validation_ds = labeled_ds.skip(TRAIN_SIZE).take(VALIDATION_SIZE)
-        train_batches = prepare_for_training(train_ds, BATCH_SIZE, seed=args.seed)
-        validation_batches = prepare_for_training(validation_ds, BATCH_SIZE, seed=args.seed)
+        train_batches = prepare_for_training(train_ds, BATCH_SIZE, seed=args.seed, shuffle_buffer_size=args.shuffle_buffer)
+        validation_batches = prepare_for_training(validation_ds, BATCH_SIZE, seed=args.seed,
+                                                  shuffle_buffer_size=args.shuffle_buffer)
         with strategy.scope():
             base_model = apps.BaseSpec(arch, IMG_SHAPE, args.weights or None)
             base_model.trainable = False
             pretrained_model = apps.Sequential([base_model, apps.GlobalAveragePooling2D(), apps.Dense(1)],
-                                               device=device, seed=args.seed)
-        validation_steps = 20
+                                               device=device, seed=args.seed, executor=_executor_kind(args, device))
+        validation_steps = args.validation_steps
         if train:
             pretrained_model.compile(optimizer=RMSprop(lr=base_learning_rate), loss=BinaryCrossentropy(from_logits=True),
                                      metrics=[BinaryAccuracy()])
@@ -284,7 +336,8 @@ def main_fed(argv: list) -> dict:
     client_train, client_test = ClientData.train_test_client_split(client_data, NUM_TEST_CLIENTS, seed=0)
 
     def make_federated_data(cd, ids):
-        return [prepare_for_training(cd.create_tf_dataset_for_client(x), BATCH_SIZE, seed=args.seed) for x in ids]
+        return [prepare_for_training(cd.create_tf_dataset_for_client(x), BATCH_SIZE, seed=args.seed,
+                                     shuffle_buffer_size=args.shuffle_buffer) for x in ids]
 
     federated_train_data = make_federated_data(client_train, client_train.client_ids)
     federated_test_data = make_federated_data(client_test, client_test.client_ids)
@@ -366,8 +419,8 @@ def main_secure(argv: list) -> dict:
         from .fed.paillier import generate_paillier_keypair
         keypair = generate_paillier_keypair(args.paillier_bits)      # one pair shared by all clients (upstream :79)
     DATASET_SIZE = args.dataset_size or 30000
-    TRAIN_SIZE = int(0.8 * DATASET_SIZE)
-    TEST_SIZE = int(0.2 * DATASET_SIZE)
+    TRAIN_SIZE = int(args.train_split * DATASET_SIZE)
+    TEST_SIZE = int((0.2 if args.val_split is None else args.val_split) * DATASET_SIZE)
     CLIENT_SIZE = int(TRAIN_SIZE / NUM_CLIENTS)
     CLIENT_TRAIN_SIZE = int(0.8 * CLIENT_SIZE)
     CLIENT_TEST_SIZE = int(0.2 * CLIENT_SIZE)
@@ -377,9 +430,10 @@ def main_secure(argv: list) -> dict:
     labeled_ds, _ = _idc_dataset(args.path, "data/balanced_IDC_30k/*/*", DATASET_SIZE, IMG_SHAPE, args.synthetic, args.seed,
                                  label_as_int=True)
     client_data = labeled_ds.take(TRAIN_SIZE)
-    test_data = prepare_for_training(labeled_ds.skip(TRAIN_SIZE).take(TEST_SIZE), BATCH_SIZE, seed=args.seed)
+    test_data = prepare_for_training(labeled_ds.skip(TRAIN_SIZE).take(TEST_SIZE), BATCH_SIZE, seed=args.seed,
+                                     shuffle_buffer_size=args.shuffle_buffer)
     # CPU: PyTorch reference executor; CUDA: the single-kernel fused pipeline (csrc/small_cnn.cu)
-    model_fn = lambda: create_small_cnn(device, args.seed, lr)  # noqa: E731
+    model_fn = lambda: create_small_cnn(device, args.seed, lr, executor=_executor_kind(args, device))  # noqa: E731
 
     def create_clients(all_data, client_ids, percent):
         return [Client(all_data.shard(NUM_CLIENTS, int(i)), int(i), percent, model_fn=model_fn, n_clients=NUM_CLIENTS,
