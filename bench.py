@@ -217,6 +217,18 @@ def main() -> int:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_s = float(t.item())
 
+    # ---- replica consistency: a 64-bit checksum of the raw bits of the fp32 master weights, every rank's ----
+    st = model.store
+    chk = int(st.master.view(torch.int32).to(torch.int64).sum().item())
+    chk16 = int(st.shadow.view(torch.int16).to(torch.int64).sum().item()) if getattr(st, "shadow", None) is not None else 0
+    sums = world.all_gather_object((chk, chk16))
+    replicas_identical = all(s == sums[0] for s in sums)
+    from idc_models_b200.parallel import fused_comm as _fc
+    graph_allreduce = None
+    if comm == "fused" and n > 1:
+        sched = getattr(strategy, "_overlap", None)
+        graph_allreduce = len(sched.plan) if sched is not None else len(model.optimizer.ranges)
+
     if world.rank == 0:
         ms_per_step = dev_ms / args.steps
         value = gb * args.steps / (dev_ms / 1e3)
@@ -247,6 +259,9 @@ def main() -> int:
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": round(e2e_s * 1e3 / args.steps, 4), "last_loss_sum": last_loss},
             "gpu_launches": launches,
+            "replicas_identical": replicas_identical,
+            "master_checksum": f"{sums[0][0] & 0xFFFFFFFFFFFFFFFF:016x}",
+            "allreduce_optim_launches_per_step": graph_allreduce,
         }
         print(json.dumps(out))
     world.barrier()

@@ -22,6 +22,8 @@
 // /root/reference/dist_model_tf_mobile.py:115-132), TFF's federated_mean + server optimizer
 // (fed_model.py:207-227) and the Paillier aggregate of secure_fed_model.py:160-168
 // (the north star replaces Paillier by pairwise masks).
+#include <mutex>
+
 #include "common.cuh"
 #include "philox.cuh"
 #include "../include/idcb200.h"
@@ -336,6 +338,7 @@ struct StatMeanArgs {
     float* stats[kMaxWorld];
     float* mc;
     long long n;
+    float scale;     // 1/world: mean over replicas (BatchNorm moving statistics); 1: plain sum (metric scalars)
 };
 
 __global__ void __launch_bounds__(kCommThreads) stat_mean_kernel(StatMeanArgs a) {
@@ -344,7 +347,7 @@ __global__ void __launch_bounds__(kCommThreads) stat_mean_kernel(StatMeanArgs a)
     grid_and_world_barrier(pr, e0 + 1, /*publish=*/false);
     long long lo, hi;
     shard_bounds(a.n >> 2, pr.world, pr.rank, lo, hi);
-    const float inv = 1.f / static_cast<float>(pr.world);
+    const float inv = a.scale;
     const long long tstride = (long long)gridDim.x * blockDim.x;
     for (long long i = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < hi; i += tstride) {
         const long long e = i << 2;
@@ -528,6 +531,8 @@ __global__ void __launch_bounds__(kCommThreads) secagg_kernel(SecAggArgs a) {
     store_epoch(pr, e0 + 2, pr.pad[pr.rank] + 18);
 }
 
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
 static int fill_peers(Peers& pr, const idcb_comm_world* w) {
     IDCB_REQUIRE(w != nullptr && w->world >= 1 && w->world <= kMaxWorld && w->rank >= 0 && w->rank < w->world,
                  "comm: bad world description");
@@ -596,21 +601,28 @@ extern "C" int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad,
     return 0;
 }
 
-extern "C" int idcb_stat_mean(const idcb_comm_world* w, void* const* stats, void* mc_stats, long long n,
-                              void* stream) {
+extern "C" int idcb_stat_reduce(const idcb_comm_world* w, void* const* stats, void* mc_stats, long long n,
+                                float scale, void* stream) {
     StatMeanArgs a{};
     if (fill_peers(a.pr, w)) return 1;
-    IDCB_REQUIRE(n % 4 == 0, "stat_mean: length must be a multiple of 4");
+    IDCB_REQUIRE(n % 4 == 0, "stat_reduce: length must be a multiple of 4");
     for (int p = 0; p < w->world; ++p) {
         a.stats[p] = static_cast<float*>(stats[p]);
-        IDCB_REQUIRE(a.stats[p] != nullptr, "stat_mean: null peer pointer for rank %d", p);
+        IDCB_REQUIRE(a.stats[p] != nullptr, "stat_reduce: null peer pointer for rank %d", p);
     }
     a.mc = static_cast<float*>(mc_stats);
     a.n = n;
+    a.scale = scale;
     if (n == 0) return 0;
     stat_mean_kernel<<<comm_grid(n / 4, w->world), kCommThreads, 0, (cudaStream_t)stream>>>(a);
     IDCB_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int idcb_stat_mean(const idcb_comm_world* w, void* const* stats, void* mc_stats, long long n,
+                              void* stream) {
+    IDCB_REQUIRE(w != nullptr && w->world >= 1, "stat_mean: bad world description");
+    return idcb_stat_reduce(w, stats, mc_stats, n, 1.f / static_cast<float>(w->world), stream);
 }
 
 extern "C" int idcb_fedavg_finite_flags(const float* clients, long long stride, long long offset, long long n,
@@ -656,6 +668,8 @@ extern "C" int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* cli
     SecAggArgs a{};
     if (fill_peers(a.pr, w)) return 1;
     IDCB_REQUIRE(n % 4 == 0 && offset % 4 == 0 && stride % 4 == 0, "secagg: sizes must be multiples of 4");
+    IDCB_REQUIRE(n >= 0 && offset >= 0 && offset + n <= stride,
+                 "secagg: range [offset=%lld, +n=%lld) does not fit in a client row of %lld elements", offset, n, stride);
     IDCB_REQUIRE(k_local >= 1 && k_local <= 64, "secagg: 1..64 clients per GPU");
     IDCB_REQUIRE(frac_bits >= 1 && frac_bits <= 30, "secagg: frac_bits must be in 1..30");
     for (int p = 0; p < w->world; ++p) {
@@ -663,6 +677,9 @@ extern "C" int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* cli
         a.ybuf[p] = static_cast<uint32_t*>(ybuf[p]);
         a.out[p] = static_cast<float*>(out[p]);
         IDCB_REQUIRE(a.ybuf[p] && a.out[p], "secagg: null peer pointer for rank %d", p);
+        // the kernel moves 16 bytes at a time
+        IDCB_REQUIRE(aligned16(a.ybuf[p]) && aligned16(a.out[p]) && aligned16(a.clients[p]),
+                     "secagg: pointers of rank %d must be 16-byte aligned", p);
     }
     IDCB_REQUIRE(a.clients[w->rank] != nullptr, "secagg: local clients pointer is null");
     a.mc_ybuf = static_cast<uint32_t*>(mc_ybuf);
@@ -686,15 +703,28 @@ extern "C" int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* cli
 // code that is already inside a region where cudaMalloc would synchronise the device. For them the
 // masked-sum kernel above is offered with its staging memory (the masked partial sums and the barrier
 // flags) placed in file-scope __device__ storage that the module itself owns: 4 MiB of uint32 plus a
-// 128-byte flag pad per GPU that loads the library, held until the process exits.
+// 256-byte flag pad per GPU that loads the library, held until the process exits.
 //
 // The symbol names below are host-side handles, not device addresses; the device address is fetched
-// once per device with cudaGetSymbolAddress (with that device current) and cached, so only the first
-// call on a device pays for the lookup. Nothing here calls cudaMalloc,
-// cudaFree or an allocating library routine. All calls on one GPU share the same staging memory, which
-// keeps whatever the previous call left in it: phase A rewrites every word it later reads, and the
-// flag pad is a monotonically increasing epoch by design, so nothing needs clearing — but two calls
-// whose kernels overlap on the GPU (different streams) would race on it; serialise them.
+// once per device with cudaGetSymbolAddress (with that device current) and cached under a mutex, so only
+// the first call on a device pays for the lookup (make that first call outside any stream capture).
+// The cache is keyed by device ordinal: after cudaDeviceReset the module is reloaded and the cached
+// addresses are stale, so a process that resets a device must not call this entry point on it again.
+// Nothing here calls cudaMalloc, cudaFree or an allocating library routine. All calls on one GPU share
+// the same staging memory, which keeps whatever the previous call left in it: phase A rewrites every
+// word it later reads, and the flag pad is a monotonically increasing epoch by design, so nothing needs
+// clearing — but two calls whose kernels overlap on the GPU (different streams) would race on it;
+// serialise them.
+//
+// What "secure" means with one GPU: pairwise masks are only generated between clients that live on
+// DIFFERENT GPUs (a pair on one GPU cancels inside that GPU's partial sum and is skipped). Here every
+// client is on the same GPU, so no mask is generated at all: the staging buffer holds the plain
+// fixed-point ring sum of the quantised weights and the result is the fixed-point mean. The call is the
+// arithmetic of the masked sum (same quantisation, same rounding), not a privacy mechanism.
+//
+// The kernel has a grid-wide barrier between its two phases, so it is launched cooperatively: a grid
+// that cannot be co-resident (another tenant holds the SMs' shared memory, a smaller MIG slice) is
+// refused with a launch error instead of spinning. A cooperative launch allocates nothing.
 // =====================================================================================================
 constexpr long long kNoAllocMaxElems = 1LL << 20;   // protected range limit: 1,048,576 weights (4 MiB)
 static __device__ __align__(256) uint32_t g_noalloc_ybuf[kNoAllocMaxElems];
@@ -706,6 +736,24 @@ struct NoAllocPtrs {
     uint32_t* pad;
 };
 NoAllocPtrs g_noalloc_ptrs[64] = {};
+std::mutex g_noalloc_mu;
+
+// once per device, with that device current; concurrent first calls are serialised
+int noalloc_lookup(int dev, NoAllocPtrs& out) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    NoAllocPtrs& np = g_noalloc_ptrs[dev];
+    if (np.ybuf == nullptr || np.pad == nullptr) {
+        void* p = nullptr;
+        IDCB_CHECK(cudaGetSymbolAddress(&p, g_noalloc_ybuf));
+        void* q = nullptr;
+        IDCB_CHECK(cudaGetSymbolAddress(&q, g_noalloc_pad));
+        IDCB_REQUIRE(p != nullptr && q != nullptr, "secagg_mean_noalloc: symbol lookup returned a null address");
+        np.pad = static_cast<uint32_t*>(q);
+        np.ybuf = static_cast<uint32_t*>(p);
+    }
+    out = np;
+    return 0;
+}
 }  // namespace
 
 extern "C" long long idcb_secagg_noalloc_max_elems(void) { return kNoAllocMaxElems; }
@@ -718,25 +766,23 @@ extern "C" int idcb_secagg_mean_noalloc(const float* clients, float* out, int k_
     IDCB_REQUIRE(n <= kNoAllocMaxElems,
                  "secagg_mean_noalloc: range of %lld elements exceeds the built-in staging area (%lld); "
                  "use idcb_secagg_masked_sum with caller-provided buffers", n, kNoAllocMaxElems);
+    IDCB_REQUIRE(offset >= 0 && offset + n <= stride,
+                 "secagg_mean_noalloc: range [offset=%lld, +n=%lld) does not fit in a client row of %lld elements",
+                 offset, n, stride);
+    IDCB_REQUIRE(aligned16(clients) && aligned16(out),
+                 "secagg_mean_noalloc: clients and out must be 16-byte aligned (the kernel moves 16 bytes at a time)");
     IDCB_REQUIRE(k_clients >= 1 && k_clients <= 64, "secagg_mean_noalloc: 1..64 clients");
     IDCB_REQUIRE(frac_bits >= 1 && frac_bits <= 30, "secagg_mean_noalloc: frac_bits must be in 1..30");
     int dev = 0;
     IDCB_CHECK(cudaGetDevice(&dev));
     IDCB_REQUIRE(dev >= 0 && dev < 64, "secagg_mean_noalloc: device index %d out of range", dev);
-    NoAllocPtrs& np = g_noalloc_ptrs[dev];
-    if (np.ybuf == nullptr) {   // once per device, with that device current
-        void* p = nullptr;
-        IDCB_CHECK(cudaGetSymbolAddress(&p, g_noalloc_ybuf));
-        void* q = nullptr;
-        IDCB_CHECK(cudaGetSymbolAddress(&q, g_noalloc_pad));
-        np.pad = static_cast<uint32_t*>(q);
-        np.ybuf = static_cast<uint32_t*>(p);
-    }
+    NoAllocPtrs np{};
+    if (noalloc_lookup(dev, np)) return 1;
     if (n == 0) return 0;
     SecAggArgs a{};
     a.pr.world = 1;
     a.pr.rank = 0;
-    a.pr.use_barrier = 1;          // the grid-wide barrier between the masking and the summing phase
+    a.pr.use_barrier = 1;          // the grid-wide barrier between the summing and the averaging phase
     a.pr.pad[0] = np.pad;
     a.clients[0] = clients;
     a.ybuf[0] = np.ybuf;
@@ -747,7 +793,8 @@ extern "C" int idcb_secagg_mean_noalloc(const float* clients, float* out, int k_
     a.session_seed = session_seed;
     long long g = ceil_div_ll(n / 4, kCommThreads);
     if (g > num_sms()) g = num_sms();
-    secagg_kernel<<<(int)g, kCommThreads, 0, (cudaStream_t)stream>>>(a);
-    IDCB_LAUNCH_CHECK();
+    void* kargs[] = {&a};
+    IDCB_CHECK(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(secagg_kernel), dim3((unsigned)g),
+                                           dim3(kCommThreads), kargs, 0, (cudaStream_t)stream));
     return 0;
 }

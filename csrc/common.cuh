@@ -39,6 +39,15 @@ static inline long long ceil_div_ll(long long a, long long b) { return (a + b - 
 
 int num_sms();  // cached SM count of the current device
 
+// Programmatic dependent launch (PDL): every single-GPU kernel of this library starts with
+// griddepcontrol.launch_dependents (the next kernel in the stream may be scheduled and run its own
+// set-up while this one computes) and executes griddepcontrol.wait before its first access to
+// global memory that an earlier kernel may have written or may still read. The wait returns only
+// when the prerequisite grid has completed and flushed, so ordering is exactly that of a plain
+// stream; what is gained is that launch latency, barrier initialisation, TMEM allocation and
+// descriptor prefetch overlap the predecessor's tail. IDCB_PDL=0 falls back to plain launches.
+bool pdl_enabled();
+
 // TMA descriptor encode (cuTensorMapEncodeTiled fetched through cudaGetDriverEntryPoint, so the
 // library does not link against libcuda).
 // 2-D bf16 tensor [rows, cols] with a row pitch in elements; box = [box_rows, box_cols].
@@ -46,9 +55,36 @@ int make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_
                       uint64_t row_pitch_elems, uint32_t box_rows, uint32_t box_cols);
 
 #ifdef __CUDACC__
+// Launch with the programmatic-stream-serialization attribute (captured into CUDA graphs as a
+// programmatic dependency edge). Only for kernels that call pdl_wait() / pdl_enter().
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                     cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Device-side PTX wrappers
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// first statement of a kernel with no set-up worth overlapping
+__device__ __forceinline__ void pdl_enter() {
+    pdl_launch_dependents();
+    pdl_wait();
+}
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }

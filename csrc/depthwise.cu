@@ -73,6 +73,7 @@ __device__ __forceinline__ void block_reduce8_atomic(const float (&v)[8], float*
 }
 
 __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
+    pdl_enter();
     __shared__ float sh[256][9];
     const DwLane L(p.C);
     const int c = L.c;
@@ -129,6 +130,7 @@ __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
 }
 
 __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
+    pdl_enter();
     __shared__ float sh[256][9];
     const DwLane L(p.C);
     const int c = L.c;
@@ -188,6 +190,7 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
 }
 
 __global__ void __launch_bounds__(256) dw_wgrad_kernel(DwArgs p) {
+    pdl_enter();
     __shared__ float sh[256][9];
     const DwLane L(p.C);
     const int c = L.c;
@@ -271,7 +274,7 @@ extern "C" int idcb_dwconv_fprop(const idcb_conv_desc* d, const void* x, const v
     p.scale = scale; p.shift = shift; p.act = act; p.stat_a = stat_sum; p.stat_b = stat_sq;
     const long long npos = 1LL * p.B * p.Ho * p.Wo;
     if (npos == 0) return 0;
-    dw_fprop_kernel<<<dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_CHECK(launch_pdl(dw_fprop_kernel, dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream, p));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -289,7 +292,7 @@ extern "C" int idcb_dwconv_dgrad(const idcb_conv_desc* d, const void* dy, const 
     IDCB_REQUIRE(!(scale || stat_b) || x != nullptr, "dwconv_dgrad: x needed for the fused backward");
     const long long npos = 1LL * p.B * p.H * p.W;
     if (npos == 0) return 0;
-    dw_dgrad_kernel<<<dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_CHECK(launch_pdl(dw_dgrad_kernel, dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream, p));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -304,7 +307,7 @@ extern "C" int idcb_dwconv_wgrad(const idcb_conv_desc* d, const void* x, const v
     p.scale = scale; p.shift = shift; p.act = act;
     const long long npos = 1LL * p.B * p.Ho * p.Wo;
     if (npos == 0) return 0;
-    dw_wgrad_kernel<<<dw_grid(npos, p.C, 8), 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_CHECK(launch_pdl(dw_wgrad_kernel, dw_grid(npos, p.C, 8), 256, 0, (cudaStream_t)stream, p));
     IDCB_LAUNCH_CHECK();
     return 0;
 }

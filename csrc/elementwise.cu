@@ -18,6 +18,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
                                    const float* __restrict__ beta, float eps, float* scale,
                                    float* shift, float* mean_out, float* rstd_out,
                                    float* moving_mean, float* moving_var, float momentum, int C) {
+    pdl_enter();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float m = sum[c] / count;
@@ -39,6 +40,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
 __global__ void bn_fold_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
                                const float* __restrict__ mean, const float* __restrict__ var,
                                float eps, float* scale, float* shift, int C) {
+    pdl_enter();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float s = gamma[c] * rsqrtf(var[c] + eps);
@@ -58,6 +60,7 @@ __global__ void bn_bwd_coeffs_kernel(const float* __restrict__ sa, const float* 
                                      const float* __restrict__ scale, float count, float* dgamma,
                                      float* dbeta, float* A, float* B, float* C0, float* acc_s1,
                                      float* acc_s2, int C) {
+    pdl_enter();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float a = sa[c], b = sb[c], m = mean[c], r = rstd[c], s = scale[c];
@@ -80,6 +83,7 @@ __global__ void bn_shared_coeffs_kernel(const float* __restrict__ s1, const floa
                                         const float* __restrict__ mean,
                                         const float* __restrict__ rstd, float count, float* A,
                                         float* B, float* C0, int C) {
+    pdl_enter();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float r = rstd[c], m = mean[c];
@@ -96,6 +100,7 @@ __global__ void affine_act_kernel(const __nv_bfloat16* __restrict__ x, int x_pit
                                   const float* __restrict__ scale, const float* __restrict__ shift,
                                   int act, const __nv_bfloat16* __restrict__ res, int r_pitch,
                                   int r_coff, long long M, int C) {
+    pdl_enter();
     const int c8 = C >> 3;
     const long long total = M * c8;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -132,6 +137,7 @@ __global__ void affine2_kernel(const void* __restrict__ g, int g_pitch, int g_co
                                __nv_bfloat16* out, int o_pitch, int o_coff,
                                const float* __restrict__ A, const float* __restrict__ B,
                                const float* __restrict__ C0, long long M, int C) {
+    pdl_enter();
     const int c8 = C >> 3;
     const long long total = M * c8;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -178,6 +184,7 @@ __global__ void affine2_kernel(const void* __restrict__ g, int g_pitch, int g_co
 // ---------------------------------------------------------------------------------------------
 __global__ void channel_stats_kernel(const __nv_bfloat16* __restrict__ x, int pitch, int coff,
                                      long long M, int C, float* sum, float* sq) {
+    pdl_enter();
     // block = 256 threads = 8 channel-octets x 32 row lanes
     const int oct = threadIdx.x & 7;
     const int rl = threadIdx.x >> 3;
@@ -218,6 +225,7 @@ __global__ void channel_stats_kernel(const __nv_bfloat16* __restrict__ x, int pi
 __global__ void channel_stats2_kernel(const __nv_bfloat16* __restrict__ g, int g_pitch, int g_coff,
                                       const __nv_bfloat16* __restrict__ x, int x_pitch, int x_coff,
                                       long long M, int C, float* sum_g, float* sum_gx) {
+    pdl_enter();
     const int oct = threadIdx.x & 7;
     const int rl = threadIdx.x >> 3;
     const int c = blockIdx.x * 64 + oct * 8;
@@ -272,6 +280,7 @@ struct PoolArgs {
 };
 
 __global__ void pool_fwd_kernel(PoolArgs p) {
+    pdl_enter();
     const int c8 = p.C >> 3;
     const long long total = 1LL * p.B * p.Ho * p.Wo * c8;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -350,6 +359,7 @@ struct PoolBwdArgs {
 };
 
 __global__ void pool_bwd_kernel(PoolBwdArgs p) {
+    pdl_enter();
     const int c8 = p.C >> 3;
     const long long total = 1LL * p.B * p.H * p.W * c8;
     __shared__ float s_a[256][9];   // padded to dodge bank conflicts on the final reduce
@@ -485,6 +495,7 @@ __global__ void pool_bwd_kernel(PoolBwdArgs p) {
 // fp32 NHWC [.., Cin] -> bf16 NHWC [.., Cpad] with zero fill of the pad channels.
 __global__ void pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* y, long long npos,
                                   int cin, int cpad) {
+    pdl_enter();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < npos * cpad;
          i += (long long)gridDim.x * blockDim.x) {
         const long long pos = i / cpad;
@@ -494,6 +505,7 @@ __global__ void pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* y,
 }
 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* y, long long n) {
+    pdl_enter();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
          i += (long long)gridDim.x * blockDim.x)
         y[i] = __float2bfloat16_rn(x[i]);
@@ -525,13 +537,36 @@ struct BnApplyArgs {
     float* dgamma; float* dbeta;
     int mode;
     long long M; int C;
+    // mode 2 only, optional: the BatchNorm-backward bookkeeping of the LAST consumer of this block buffer that
+    // has not been folded into S1/S2 yet (what bn_bwd_coeffs_kernel would have done in a launch of its own).
+    // The pending BatchNorm read channels [0, p_C) of the buffer; this launch's slice starts at channel p_off of
+    // that range. Every CTA adds the pending share of ITS channels on the fly; CTA (0,0) also writes the
+    // pending layer's dgamma / dbeta and folds the other channels' shares into the S1 / S2 accumulators
+    // (acc_s1 / acc_s2 point at channel 0 of the block). The slice's own accumulator entries are not
+    // updated: they are final with this launch and never read again.
+    const float* p_sa; const float* p_sb; const float* p_mean; const float* p_rstd; const float* p_scale;
+    float* p_dgamma; float* p_dbeta; float* acc_s1; float* acc_s2;
+    int p_off, p_C;
 };
 
 template <bool kGFloat>
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(BnApplyArgs p) {
+    pdl_enter();
     const int oct = threadIdx.x & 7;
     const int rl = threadIdx.x >> 3;
     const int c = blockIdx.y * 64 + oct * 8;
+    if (p.p_sa != nullptr && blockIdx.x == 0 && blockIdx.y == 0) {
+        for (int pc = threadIdx.x; pc < p.p_C; pc += blockDim.x) {
+            const float a = p.p_sa[pc], s = p.p_scale[pc];
+            const float dg = p.p_rstd[pc] * (p.p_sb[pc] - p.p_mean[pc] * a);
+            if (p.p_dgamma) p.p_dgamma[pc] += dg;
+            if (p.p_dbeta) p.p_dbeta[pc] += a;
+            if (pc < p.p_off || pc >= p.p_off + p.C) {
+                p.acc_s1[pc] += s * a;
+                p.acc_s2[pc] += s * dg;
+            }
+        }
+    }
     if (c >= p.C) return;
     float A[8], B[8], C0[8];
     const float invn = 1.f / p.count;
@@ -552,9 +587,16 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(BnApplyArgs p) {
             }
         } else {
             const float r = p.rstd[ch], m = p.mean[ch];
+            float s1 = p.sa[ch], s2 = p.sb[ch];
+            if (p.p_sa != nullptr) {
+                const int pc = p.p_off + ch;
+                const float a = p.p_sa[pc], s = p.p_scale[pc];
+                s1 += s * a;
+                s2 += s * (p.p_rstd[pc] * (p.p_sb[pc] - p.p_mean[pc] * a));
+            }
             A[e] = 1.f;
-            B[e] = -r * p.sb[ch] * invn;
-            C0[e] = -p.sa[ch] * invn + r * m * p.sb[ch] * invn;
+            B[e] = -r * s2 * invn;
+            C0[e] = -s1 * invn + r * m * s2 * invn;
         }
     }
     for (long long m = blockIdx.x * 32 + rl; m < p.M; m += (long long)gridDim.x * 32) {
@@ -601,9 +643,9 @@ extern "C" int idcb_bn_finalize(const float* sum, const float* sq, float count, 
                                 float* mean_out, float* rstd_out, float* moving_mean,
                                 float* moving_var, float momentum, int C, void* stream) {
     IDCB_REQUIRE(C > 0 && count > 0.f, "bn_finalize: bad sizes");
-    bn_finalize_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(
+    IDCB_CHECK(launch_pdl(bn_finalize_kernel, ceil_div(C, 128), 128, 0, (cudaStream_t)stream, 
         sum, sq, count, gamma, beta, eps, scale, shift, mean_out, rstd_out, moving_mean, moving_var,
-        momentum, C);
+        momentum, C));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -611,8 +653,8 @@ extern "C" int idcb_bn_finalize(const float* sum, const float* sq, float count, 
 extern "C" int idcb_bn_fold(const float* gamma, const float* beta, const float* mean,
                             const float* var, float eps, float* scale, float* shift, int C,
                             void* stream) {
-    bn_fold_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(gamma, beta, mean, var, eps,
-                                                                       scale, shift, C);
+    IDCB_CHECK(launch_pdl(bn_fold_kernel, ceil_div(C, 128), 128, 0, (cudaStream_t)stream, gamma, beta, mean, var, eps,
+                                                                       scale, shift, C));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -622,8 +664,8 @@ extern "C" int idcb_bn_bwd_coeffs(const float* sa, const float* sb, const float*
                                   float* dbeta, float* A, float* B, float* C0, float* acc_s1,
                                   float* acc_s2, int C, void* stream) {
     IDCB_REQUIRE((acc_s1 == nullptr) == (acc_s2 == nullptr), "bn_bwd_coeffs: S1/S2 go together");
-    bn_bwd_coeffs_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(
-        sa, sb, mean, rstd, scale, count, dgamma, dbeta, A, B, C0, acc_s1, acc_s2, C);
+    IDCB_CHECK(launch_pdl(bn_bwd_coeffs_kernel, ceil_div(C, 128), 128, 0, (cudaStream_t)stream, 
+        sa, sb, mean, rstd, scale, count, dgamma, dbeta, A, B, C0, acc_s1, acc_s2, C));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -631,8 +673,8 @@ extern "C" int idcb_bn_bwd_coeffs(const float* sa, const float* sb, const float*
 extern "C" int idcb_bn_shared_coeffs(const float* s1, const float* s2, const float* mean,
                                      const float* rstd, float count, float* A, float* B, float* C0,
                                      int C, void* stream) {
-    bn_shared_coeffs_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(s1, s2, mean, rstd,
-                                                                                count, A, B, C0, C);
+    IDCB_CHECK(launch_pdl(bn_shared_coeffs_kernel, ceil_div(C, 128), 128, 0, (cudaStream_t)stream, s1, s2, mean, rstd,
+                                                                                count, A, B, C0, C));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -645,9 +687,9 @@ extern "C" int idcb_affine_act(const void* x, int x_pitch, int x_coff, void* y, 
                      y_coff % 8 == 0 && r_pitch % 8 == 0 && r_coff % 8 == 0,
                  "affine_act: channel counts/pitches must be multiples of 8");
     if (M == 0) return 0;
-    affine_act_kernel<<<ew_grid(M * (C / 8), 256), 256, 0, (cudaStream_t)stream>>>(
+    IDCB_CHECK(launch_pdl(affine_act_kernel, ew_grid(M * (C / 8), 256), 256, 0, (cudaStream_t)stream, 
         (cbf)x, x_pitch, x_coff, (bf)y, y_pitch, y_coff, scale, shift, act, (cbf)res, r_pitch, r_coff,
-        M, C);
+        M, C));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -662,11 +704,11 @@ extern "C" int idcb_affine2(const void* g, int g_is_float, int g_pitch, int g_co
     if (M == 0) return 0;
     const int grid = ew_grid(M * (C / 8), 256);
     if (g_is_float)
-        affine2_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(
-            g, g_pitch, g_coff, (cbf)x, x_pitch, x_coff, (bf)out, o_pitch, o_coff, A, B, C0, M, C);
+        IDCB_CHECK(launch_pdl(affine2_kernel<true>, grid, 256, 0, (cudaStream_t)stream, 
+            g, g_pitch, g_coff, (cbf)x, x_pitch, x_coff, (bf)out, o_pitch, o_coff, A, B, C0, M, C));
     else
-        affine2_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(
-            g, g_pitch, g_coff, (cbf)x, x_pitch, x_coff, (bf)out, o_pitch, o_coff, A, B, C0, M, C);
+        IDCB_CHECK(launch_pdl(affine2_kernel<false>, grid, 256, 0, (cudaStream_t)stream, 
+            g, g_pitch, g_coff, (cbf)x, x_pitch, x_coff, (bf)out, o_pitch, o_coff, A, B, C0, M, C));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -697,9 +739,9 @@ extern "C" int idcb_bn_bwd_apply(int mode, const void* g, int g_is_float, int g_
     if (splits < 1) splits = 1;
     dim3 grid(splits, ygroups);
     if (g_is_float)
-        bn_bwd_apply_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+        IDCB_CHECK(launch_pdl(bn_bwd_apply_kernel<true>, grid, 256, 0, (cudaStream_t)stream, a));
     else
-        bn_bwd_apply_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+        IDCB_CHECK(launch_pdl(bn_bwd_apply_kernel<false>, grid, 256, 0, (cudaStream_t)stream, a));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -713,7 +755,7 @@ extern "C" int idcb_channel_stats(const void* x, int pitch, int coff, long long 
     if (splits > cap) splits = cap;
     if (splits < 1) splits = 1;
     dim3 grid(ceil_div(C, 64), splits);
-    channel_stats_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((cbf)x, pitch, coff, M, C, sum, sq);
+    IDCB_CHECK(launch_pdl(channel_stats_kernel, grid, 256, 0, (cudaStream_t)stream, (cbf)x, pitch, coff, M, C, sum, sq));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -729,8 +771,8 @@ extern "C" int idcb_channel_stats2(const void* g, int g_pitch, int g_coff, const
     if (splits > cap) splits = cap;
     if (splits < 1) splits = 1;
     dim3 grid(ceil_div(C, 64), splits);
-    channel_stats2_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((cbf)g, g_pitch, g_coff, (cbf)x, x_pitch,
-                                                               x_coff, M, C, sum_g, sum_gx);
+    IDCB_CHECK(launch_pdl(channel_stats2_kernel, grid, 256, 0, (cudaStream_t)stream, (cbf)g, g_pitch, g_coff, (cbf)x, x_pitch,
+                                                               x_coff, M, C, sum_g, sum_gx));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -747,7 +789,7 @@ extern "C" int idcb_pool_fwd(const idcb_pool_desc* d, const void* x, void* y, co
     p.scale = scale; p.shift = shift; p.act = act; p.is_max = d->is_max;
     const long long items = 1LL * p.B * p.Ho * p.Wo * (p.C / 8);
     if (items == 0) return 0;
-    pool_fwd_kernel<<<ew_grid(items, 256), 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_CHECK(launch_pdl(pool_fwd_kernel, ew_grid(items, 256), 256, 0, (cudaStream_t)stream, p));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -775,7 +817,7 @@ extern "C" int idcb_pool_bwd(const idcb_pool_desc* d, const void* x, const void*
     if (gx > cap) gx = cap;
     if (gx < 1) gx = 1;
     dim3 grid(gx, p.C / 8);
-    pool_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(p);
+    IDCB_CHECK(launch_pdl(pool_bwd_kernel, grid, 256, 0, (cudaStream_t)stream, p));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -783,15 +825,48 @@ extern "C" int idcb_pool_bwd(const idcb_pool_desc* d, const void* x, const void*
 extern "C" int idcb_pack_input(const float* x, void* y, long long npos, int cin, int cpad,
                                void* stream) {
     if (npos == 0) return 0;
-    pack_input_kernel<<<ew_grid(npos * cpad, 256), 256, 0, (cudaStream_t)stream>>>(x, (bf)y, npos, cin,
-                                                                                  cpad);
+    IDCB_CHECK(launch_pdl(pack_input_kernel, ew_grid(npos * cpad, 256), 256, 0, (cudaStream_t)stream, x, (bf)y, npos, cin,
+                                                                                  cpad));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
 
 extern "C" int idcb_cast_f32_bf16(const float* x, void* y, long long n, void* stream) {
     if (n == 0) return 0;
-    cast_f32_bf16_kernel<<<ew_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(x, (bf)y, n);
+    IDCB_CHECK(launch_pdl(cast_f32_bf16_kernel, ew_grid(n, 256), 256, 0, (cudaStream_t)stream, x, (bf)y, n));
     IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+// DenseNet block-buffer slice: dx = G - S1/N - xhat * S2/N, with the bookkeeping of the block's most recent
+// consumer BatchNorm (dgamma / dbeta / its S1,S2 share) folded into the same launch.
+extern "C" int idcb_bn_bwd_slice(const float* g, int g_pitch, int g_coff, const void* x, int x_pitch, int x_coff,
+                                 void* out, int o_pitch, int o_coff, float* acc_s1, float* acc_s2, int c_lo,
+                                 const float* mean, const float* rstd, float count, long long M, int C,
+                                 const float* p_sa, const float* p_sb, const float* p_mean, const float* p_rstd,
+                                 const float* p_scale, float* p_dgamma, float* p_dbeta, int p_C, void* stream) {
+    IDCB_REQUIRE(C % 8 == 0 && g_pitch % 8 == 0 && g_coff % 8 == 0 && x_pitch % 8 == 0 && x_coff % 8 == 0 &&
+                     o_pitch % 8 == 0 && o_coff % 8 == 0 && c_lo % 8 == 0,
+                 "bn_bwd_slice: channel counts/pitches must be multiples of 8");
+    IDCB_REQUIRE(acc_s1 && acc_s2 && mean && rstd && count > 0.f, "bn_bwd_slice: missing per-channel inputs");
+    IDCB_REQUIRE(p_sa == nullptr || (p_sb && p_mean && p_rstd && p_scale && c_lo >= 0 && c_lo + C <= p_C),
+                 "bn_bwd_slice: the slice [%d, %d) must lie inside the pending BatchNorm's %d channels", c_lo,
+                 c_lo + C, p_C);
+    if (M == 0) return 0;
+    BnApplyArgs a{};
+    a.g = g; a.g_is_float = 1; a.g_pitch = g_pitch; a.g_coff = g_coff;
+    a.x = (cbf)x; a.x_pitch = x_pitch; a.x_coff = x_coff;
+    a.out = (bf)out; a.o_pitch = o_pitch; a.o_coff = o_coff;
+    a.sa = acc_s1 + c_lo; a.sb = acc_s2 + c_lo; a.mean = mean; a.rstd = rstd; a.count = count;
+    a.mode = 2; a.M = M; a.C = C;
+    a.p_sa = p_sa; a.p_sb = p_sb; a.p_mean = p_mean; a.p_rstd = p_rstd; a.p_scale = p_scale;
+    a.p_dgamma = p_dgamma; a.p_dbeta = p_dbeta; a.acc_s1 = acc_s1; a.acc_s2 = acc_s2;
+    a.p_off = c_lo; a.p_C = p_sa ? p_C : 0;
+    const int ygroups = ceil_div(C, 64);
+    int splits = static_cast<int>(ceil_div_ll(M, 32 * 4));
+    const int cap = ceil_div(4 * num_sms(), ygroups);
+    if (splits > cap) splits = cap;
+    if (splits < 1) splits = 1;
+    IDCB_CHECK(launch_pdl(bn_bwd_apply_kernel<true>, dim3(splits, ygroups), 256, 0, (cudaStream_t)stream, a));
     return 0;
 }

@@ -51,6 +51,7 @@ struct HeadArgs {
 };
 
 __global__ void __launch_bounds__(kHeadThreads) head_kernel(HeadArgs p) {
+    pdl_enter();
     extern __shared__ float sm[];
     float* feat = sm;                 // [C]
     float* red = feat + p.C;          // [32]
@@ -166,7 +167,7 @@ extern "C" int idcb_head(const idcb_head_desc* d, const void* x, const float* w,
     p.stat_a = stat_a; p.stat_b = stat_b;
     if (d->batch == 0) return 0;
     const size_t smem = (d->c + 32 + 2 * kMaxClasses) * sizeof(float);
-    head_kernel<<<d->batch, kHeadThreads, smem, (cudaStream_t)stream>>>(p);
+    IDCB_CHECK(launch_pdl(head_kernel, d->batch, kHeadThreads, smem, (cudaStream_t)stream, p));
     IDCB_LAUNCH_CHECK();
     return 0;
 }

@@ -38,6 +38,7 @@ __device__ __forceinline__ float opt_update(int kind, float w, float g, float& s
 }
 
 __global__ void optim_kernel(OptArgs a) {
+    pdl_enter();
     const long long n4 = a.n >> 2;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4;
          i += (long long)gridDim.x * blockDim.x) {
@@ -77,7 +78,7 @@ extern "C" int idcb_optim_step(int kind, float* w, float* g, float* s1, float* s
     OptArgs a{w, g, s1, s2, (__nv_bfloat16*)shadow, n, kind, lr, p1, p2, eps, grad_scale, zero_grad};
     long long blocks = ceil_div_ll(n / 4, 256);
     if (blocks > 8LL * num_sms()) blocks = 8LL * num_sms();
-    optim_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(a);
+    IDCB_CHECK(launch_pdl(optim_kernel, (int)blocks, 256, 0, (cudaStream_t)stream, a));
     IDCB_LAUNCH_CHECK();
     return 0;
 }

@@ -1,6 +1,7 @@
 // Host runtime of the idcb200 CUDA library: error reporting, device queries, TMA descriptor
 // encoding through the driver entry point (no link-time libcuda dependency).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -24,6 +25,8 @@ int check_cuda(cudaError_t e, const char* what) {
     return 2;
 }
 
+void set_pdl(int on);
+
 int num_sms() {
     static int cached[64] = {0};
     int dev = 0;
@@ -36,6 +39,16 @@ int num_sms() {
     }
     return cached[dev];
 }
+
+static int g_pdl = -1;   // -1: not decided yet (IDCB_PDL, default on)
+bool pdl_enabled() {
+    if (g_pdl < 0) {
+        const char* e = getenv("IDCB_PDL");
+        g_pdl = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return g_pdl != 0;
+}
+void set_pdl(int on) { g_pdl = on ? 1 : 0; }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -82,3 +95,9 @@ extern "C" const char* idcb_last_error(void) { return idcb::g_err; }
 extern "C" int idcb_version(void) { return 100; }
 
 extern "C" int idcb_device_sm_count(void) { return idcb::num_sms(); }
+
+extern "C" int idcb_set_pdl(int on) {
+    const int was = idcb::pdl_enabled() ? 1 : 0;
+    idcb::set_pdl(on);
+    return was;
+}

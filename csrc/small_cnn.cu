@@ -46,6 +46,7 @@ __device__ __forceinline__ bool keep(unsigned long long seed, unsigned step, uns
 }
 
 __global__ void __launch_bounds__(128) small_cnn_kernel(SmallCnnArgs a) {
+    pdl_enter();
     __shared__ float sx[kH * kH * kC];
     __shared__ float sW[kMaxBlock];
     __shared__ float conv[kConvOut * kConvOut * kF];   // post-relu conv output
@@ -168,6 +169,7 @@ __global__ void __launch_bounds__(128) small_cnn_kernel(SmallCnnArgs a) {
 // ---------------------------------------------------------------------------------------------
 __global__ void synth_patches_kernel(float* x, float* labels, long long n_img, int hwc, int channels,
                                      unsigned long long seed, unsigned int step) {
+    pdl_enter();
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n_img * hwc;
          i += (long long)gridDim.x * blockDim.x) {
         const long long img = i / hwc;
@@ -203,7 +205,7 @@ extern "C" int idcb_small_cnn_step(const float* x, const float* labels, const fl
     SmallCnnArgs a{x, labels, params, grads, logits, acc, batch, param_stride,
                    offsets6[0], offsets6[1], offsets6[2], offsets6[3], offsets6[4], offsets6[5], conv_cin_stride, span,
                    training, grad_scale, drop1, drop2, seed, step, threshold, acc_on_prob};
-    small_cnn_kernel<<<dim3(batch, n_clients), 128, 0, (cudaStream_t)stream>>>(a);
+    IDCB_CHECK(launch_pdl(small_cnn_kernel, dim3(batch, n_clients), 128, 0, (cudaStream_t)stream, a));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -215,7 +217,7 @@ extern "C" int idcb_synth_patches(float* x, float* labels, long long n_img, int 
     const int hwc = h * w * channels;
     long long g = ceil_div_ll(n_img * hwc, 256);
     if (g > 16LL * num_sms()) g = 16LL * num_sms();
-    synth_patches_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(x, labels, n_img, hwc, channels, seed, step);
+    IDCB_CHECK(launch_pdl(synth_patches_kernel, (int)g, 256, 0, (cudaStream_t)stream, x, labels, n_img, hwc, channels, seed, step));
     IDCB_LAUNCH_CHECK();
     return 0;
 }

@@ -107,6 +107,20 @@ struct ConvArgs {
     float* stat_b;  //                    mode 0: sum(y^2);  mode 2: sum(dpre * x_raw)
     int w_cols_per_tap;  // dgrad: column stride between taps in the 2-D weight view
     long long* dbg;      // optional: per-phase clock64 stamps of CTA (0,0) (profiling aid)
+    // mode 2, optional: the backward of the BatchNorm whose output gradient this kernel produces, finished in
+    // the same launch. tail = 1 (training BN): after every CTA has added its column sums to stat_a / stat_b the
+    // grid meets at a barrier (the accumulators stay in TMEM meanwhile), then each CTA turns its own dpre tile
+    // into dx = s*(dpre - sa/N - xhat*dgamma/N) and the first row of CTAs emits dgamma / dbeta.
+    // tail = 2 (frozen BN): dx = s * dpre, no barrier. Needs the whole grid co-resident (checked on the host).
+    int tail;
+    __nv_bfloat16* tail_out;
+    int tail_pitch, tail_coff;
+    const float* tail_mean;
+    const float* tail_rstd;
+    float tail_count;
+    float* tail_dgamma;
+    float* tail_dbeta;
+    unsigned int* tail_counter;   // zero at launch
 };
 
 #define IDCB_STAMP(i)                                                                     \
@@ -291,6 +305,43 @@ __device__ __forceinline__ void epilogue_slab(const ConvArgs& p, uint32_t taddr,
     }
 }
 
+// Second pass of a mode-2 epilogue with a BatchNorm tail: the same dpre as the first pass (recomputed from the
+// accumulator that is still in TMEM and the raw activation row), turned into dx = A*dpre + B*x + C.
+template <int kW>
+__device__ __forceinline__ void tail_slab(const ConvArgs& p, uint32_t taddr, int m, bool mvalid, int nb,
+                                          const float* es_scale, const float* es_shift, const float* es_b,
+                                          const float* es_c) {
+    float vv[kW];
+    tmem_ld_cols<kW>(taddr, vv);
+    float xr[kW];
+    load_row_bf16<kW>(p.aux + static_cast<size_t>(m) * p.aux_pitch + p.aux_coff + nb, mvalid, nb, p.Cout, xr);
+    const int act = p.bwd_act;
+    uint32_t packed[kW / 2];
+#pragma unroll
+    for (int g4 = 0; g4 < kW / 4; ++g4) {
+        const float4 gs = *reinterpret_cast<const float4*>(es_scale + g4 * 4);
+        const float4 gh = *reinterpret_cast<const float4*>(es_shift + g4 * 4);
+        const float4 cb = *reinterpret_cast<const float4*>(es_b + g4 * 4);
+        const float4 cc = *reinterpret_cast<const float4*>(es_c + g4 * 4);
+        const float d0 = vv[g4 * 4 + 0] * act_mask(fmaf(gs.x, xr[g4 * 4 + 0], gh.x), act);
+        const float d1 = vv[g4 * 4 + 1] * act_mask(fmaf(gs.y, xr[g4 * 4 + 1], gh.y), act);
+        const float d2 = vv[g4 * 4 + 2] * act_mask(fmaf(gs.z, xr[g4 * 4 + 2], gh.z), act);
+        const float d3 = vv[g4 * 4 + 3] * act_mask(fmaf(gs.w, xr[g4 * 4 + 3], gh.w), act);
+        packed[g4 * 2 + 0] = pack_bf16x2(fmaf(gs.x, d0, fmaf(cb.x, xr[g4 * 4 + 0], cc.x)),
+                                         fmaf(gs.y, d1, fmaf(cb.y, xr[g4 * 4 + 1], cc.y)));
+        packed[g4 * 2 + 1] = pack_bf16x2(fmaf(gs.z, d2, fmaf(cb.z, xr[g4 * 4 + 2], cc.z)),
+                                         fmaf(gs.w, d3, fmaf(cb.w, xr[g4 * 4 + 3], cc.w)));
+    }
+    if (mvalid) {
+        __nv_bfloat16* orow = p.tail_out + static_cast<size_t>(m) * p.tail_pitch + p.tail_coff + nb;
+#pragma unroll
+        for (int g = 0; g < kW / 8; ++g)
+            if (nb + g * 8 < p.Cout)
+                *reinterpret_cast<uint4*>(orow + g * 8) =
+                    make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+    }
+}
+
 template <int kBN, bool kBMN>
 struct FwdSmem {
     static constexpr int kBTileBytes = kBMN ? ((kBN + 63) / 64) * 8192 : kBN * 128;
@@ -441,7 +492,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     const int cblocks = (p.Cin + kBK - 1) / kBK;                 // dgrad: k-blocks per tap
     const int ktot = taps * p.Cin;                              // fprop: linearised K extent
     const int num_kb = kBMN ? taps * cblocks : (ktot + kBK - 1) / kBK;
-    if (threadIdx.x == 0) IDCB_STAMP(0);
+    pdl_launch_dependents();
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nstages; ++s) {
@@ -460,6 +511,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     }
     if (warp == kTmaWarp && lane == 0) tma_prefetch_desc(&tmap_w);
     if (warp == kMmaWarp) tmem_alloc<kBN < 32 ? 32 : kBN>(tmem_slot);
+    // everything above touched only this CTA's shared memory, TMEM and the kernel parameters; from here on
+    // the kernel reads what its predecessors wrote
+    pdl_wait();
+    if (threadIdx.x == 0) IDCB_STAMP(0);
     if (p.bn_sum != nullptr) {
         // BatchNorm finalised from the batch sums by every CTA for itself (the publication of the
         // coefficients and the moving-statistics update happen at the very end of the kernel)
@@ -723,6 +778,63 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     if (threadIdx.x == 0) IDCB_STAMP(7);
     __syncthreads();
     if (threadIdx.x == 0) IDCB_STAMP(8);
+    if (kEpi == 2 && p.tail != 0) {
+        float* s_cb = s_scale + 256;
+        float* s_cc = s_scale + 384;
+        if (p.tail == 1) {
+            // grid barrier: this CTA's column sums (atomics issued before the __syncthreads above) are made
+            // visible, it is counted, and it waits for everybody else's
+            if (threadIdx.x == 0) {
+                __threadfence();
+                atomicAdd(p.tail_counter, 1u);
+                const unsigned int total = gridDim.x * gridDim.y;
+                unsigned int seen;
+                long long t0 = clock64();
+                do {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.tail_counter) : "memory");
+                    if (seen < total && clock64() - t0 > 8000000000LL) __trap();   // a grid that is not co-resident
+                } while (seen < total);
+            }
+            __syncthreads();
+        }
+        const float invn = 1.f / p.tail_count;
+        for (int c = threadIdx.x; c < kBN; c += kNT) {
+            const int n = n0 + c;
+            float cb = 0.f, cc = 0.f;
+            if (p.tail == 1 && n < p.Cout) {
+                const float a = __ldcg(p.stat_a + n), b = __ldcg(p.stat_b + n);
+                const float m = p.tail_mean[n], r = p.tail_rstd[n], sc = s_scale[c];
+                const float dg = r * (b - m * a);
+                cb = -sc * r * dg * invn;
+                cc = -sc * a * invn + sc * r * m * dg * invn;
+                if (blockIdx.x == 0) {
+                    if (p.tail_dgamma != nullptr) p.tail_dgamma[n] += dg;
+                    if (p.tail_dbeta != nullptr) p.tail_dbeta[n] += a;
+                }
+            }
+            s_cb[c] = cb;
+            s_cc[c] = cc;
+        }
+        __syncthreads();
+        tc_fence_after();
+        if (warp < kWork / 32) {
+            constexpr int kHalf = kBN / 2;
+            constexpr int kW = (kHalf >= 32 && (kBMN || kBN < 128)) ? 32 : 16;
+            const int quad = warp & 3;
+            const int half = warp >> 2;
+            const int m = m0 + quad * 32 + lane;
+            const bool mvalid = m < p.M;
+            const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+#pragma unroll 1
+            for (int cc = half * kHalf; cc < (half + 1) * kHalf; cc += kW) {
+                const int nb = n0 + cc;
+                if (nb >= p.Cout) break;  // warp-uniform
+                tail_slab<kW>(p, t_row + cc, m, mvalid, nb, s_scale + cc, s_shift + cc, s_cb + cc, s_cc + cc);
+            }
+            tc_fence_before();
+        }
+        __syncthreads();
+    }
     if (warp == kMmaWarp) {
         tc_fence_after();
         tmem_dealloc<kBN < 32 ? 32 : kBN>(tmem_base);
@@ -842,6 +954,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     int kb_end = kb_begin + p.kb_per_split;
     if (kb_end > total_kb) kb_end = total_kb;
     const int num_kb = kb_end > kb_begin ? kb_end - kb_begin : 0;
+    pdl_launch_dependents();
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < nstages; ++s) {
@@ -859,6 +972,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     }
     if (warp == kTmaWarp && lane == 0) tma_prefetch_desc(&tmap_dy);
     if (warp == kMmaWarp) tmem_alloc<kBN < 32 ? 32 : kBN>(tmem_slot);
+    pdl_wait();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -1045,6 +1159,12 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 // ---------------------------------------------------------------------------------------------
 static long long* g_dbg = nullptr;
 
+static int current_device() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    return dev;
+}
+
 // N-tile width: the widest tile that still leaves enough CTAs to spread a small problem over the chip
 // (a 128-row x 128-column tile of a tiny layer would otherwise run its whole MMA chain on one SM).
 static int pick_bn(int M, int N) {
@@ -1075,7 +1195,8 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     using L = FwdSmem<kBN, kBMN>;
     const int taps = a.KH * a.KW;
     const int num_kb = kBMN ? taps * ceil_div(a.Cin, kBK) : ceil_div(taps * a.Cin, kBK);
-    const int extra = kBarBytes + 2 * (int)sizeof(float) * ((a.Cin > 128 ? a.Cin : 128) + 4) + 64;
+    const int extra = kBarBytes + 2 * (int)sizeof(float) * ((a.Cin > 128 ? a.Cin : 128) + 4) + 64 +
+                      (kEpi == 2 ? 1024 : 0);   // mode 2 with a BatchNorm tail: two more 128-float tables
     const bool has_pro = !kBMN && (a.pro_scale != nullptr || a.bn_sum != nullptr);
     a.stages = pick_stages(num_kb, has_pro, L::kStageBytes, 1024 + (has_pro ? kRaw * kRawBytes : 0) + extra,
                            kBMN ? 1LL * ceil_div(a.M, kBM) * ceil_div(a.Cout, kBN) : 0);
@@ -1088,16 +1209,22 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     a.d_kw = make_fdiv(a.KW);
     a.d_cb = make_fdiv(ceil_div(a.Cin, kBK));
     auto kern = conv_gemm_kernel<kBN, kBMN, kEpi>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};      // the attribute belongs to the (function, device) pair
+    const int dev = current_device();
+    if (!attr_set[dev]) {
         IDCB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         227 * 1024));
-        attr_set = true;
+        attr_set[dev] = true;
     }
     dim3 grid(ceil_div(a.M, kBM), ceil_div(a.Cout, kBN), 1);
+    if (kEpi == 2 && a.tail == 1) {
+        int per_sm = 0;
+        IDCB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, GemmCfg<kBMN>::kNT, smem));
+        IDCB_REQUIRE(static_cast<long long>(grid.x) * grid.y <= static_cast<long long>(per_sm) * num_sms(),
+                     "conv_dgrad: a %u x %u grid with a BatchNorm tail cannot be co-resident", grid.x, grid.y);
+    }
     a.dbg = g_dbg;
-    kern<<<grid, GemmCfg<kBMN>::kNT, smem, st>>>(tm, a);
-    IDCB_LAUNCH_CHECK();
+    IDCB_CHECK(launch_pdl(kern, grid, dim3(GemmCfg<kBMN>::kNT), smem, st, tm, a));
     return 0;
 }
 
@@ -1114,15 +1241,15 @@ static int launch_wgrad(const CUtensorMap& tm, WgradArgs& a, cudaStream_t st) {
     a.d_cin = make_fdiv(a.Cin);
     a.d_kw = make_fdiv(a.KW);
     auto kern = conv_wgrad_kernel<kBN>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {};
+    const int dev = current_device();
+    if (!attr_set[dev]) {
         IDCB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         227 * 1024));
-        attr_set = true;
+        attr_set[dev] = true;
     }
     dim3 grid(ceil_div(a.KH * a.KW * a.Cin, 128), ceil_div(a.Cout, kBN), a.splits);
-    kern<<<grid, kWgThreads, smem, st>>>(tm, a);
-    IDCB_LAUNCH_CHECK();
+    IDCB_CHECK(launch_pdl(kern, grid, dim3(kWgThreads), smem, st, tm, a));
     return 0;
 }
 
@@ -1237,26 +1364,51 @@ extern "C" int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const vo
         IDCB_REQUIRE(f->gacc == nullptr || (f->g_pitch % 4 == 0 && f->g_coff % 4 == 0),
                      "conv_dgrad: G pitch/offset must be multiples of 4");
     }
-    IDCB_REQUIRE(a.y != nullptr || a.gacc != nullptr, "conv_dgrad: no output given");
-    CUtensorMap tm;
     const int kbn = pick_bn(a.M, d->cin);
+    bool split_tail = false;
+    if (f && f->tail != nullptr) {
+        const idcb_bn_tail* t = f->tail;
+        IDCB_REQUIRE(mode == 2 && a.stat_a && a.stat_b, "conv_dgrad: a BatchNorm tail needs mode 2 and both column sums");
+        IDCB_REQUIRE(t->out && t->mean && t->rstd && t->count > 0.f && (t->frozen || t->counter),
+                     "conv_dgrad: incomplete BatchNorm tail");
+        IDCB_REQUIRE(t->out_pitch % 8 == 0 && t->out_coff % 8 == 0, "conv_dgrad: tail pitch/offset must be multiples of 8");
+        // mode-2 CTAs take an SM each (launch bounds, ~200 KB of shared memory)
+        const long long tiles = 1LL * ceil_div(a.M, kBM) * ceil_div(d->cin, kbn);
+        if (t->frozen || tiles <= num_sms()) {
+            a.tail = t->frozen ? 2 : 1;
+            a.tail_out = static_cast<__nv_bfloat16*>(t->out);
+            a.tail_pitch = t->out_pitch; a.tail_coff = t->out_coff;
+            a.tail_mean = t->mean; a.tail_rstd = t->rstd; a.tail_count = t->count;
+            a.tail_dgamma = t->dgamma; a.tail_dbeta = t->dbeta; a.tail_counter = t->counter;
+            a.y = nullptr;     // dpre itself is not needed in memory
+        } else {
+            IDCB_REQUIRE(a.y != nullptr, "conv_dgrad: the tail does not fit on the device and no dx buffer was given");
+            split_tail = true;
+        }
+    }
+    IDCB_REQUIRE(a.y != nullptr || a.gacc != nullptr || a.tail != 0, "conv_dgrad: no output given");
+    CUtensorMap tm;
     // weight view [Cout rows][taps*Cin cols]; MN-major boxes are 64 cols x 64 rows
     if (make_tmap_2d_bf16(&tm, w, d->cout, (uint64_t)d->kh * d->kw * d->cin,
                           (uint64_t)d->kh * d->kw * d->cin, 64, 64))
         return 1;
+    int rc;
     if (kbn == 32) {
-        if (mode == 0) return launch_gemm<32, true, 0>(tm, a, st);
-        if (mode == 1) return launch_gemm<32, true, 1>(tm, a, st);
-        return launch_gemm<32, true, 2>(tm, a, st);
+        rc = mode == 0 ? launch_gemm<32, true, 0>(tm, a, st)
+             : mode == 1 ? launch_gemm<32, true, 1>(tm, a, st) : launch_gemm<32, true, 2>(tm, a, st);
+    } else if (kbn == 64) {
+        rc = mode == 0 ? launch_gemm<64, true, 0>(tm, a, st)
+             : mode == 1 ? launch_gemm<64, true, 1>(tm, a, st) : launch_gemm<64, true, 2>(tm, a, st);
+    } else {
+        rc = mode == 0 ? launch_gemm<128, true, 0>(tm, a, st)
+             : mode == 1 ? launch_gemm<128, true, 1>(tm, a, st) : launch_gemm<128, true, 2>(tm, a, st);
     }
-    if (kbn == 64) {
-        if (mode == 0) return launch_gemm<64, true, 0>(tm, a, st);
-        if (mode == 1) return launch_gemm<64, true, 1>(tm, a, st);
-        return launch_gemm<64, true, 2>(tm, a, st);
-    }
-    if (mode == 0) return launch_gemm<128, true, 0>(tm, a, st);
-    if (mode == 1) return launch_gemm<128, true, 1>(tm, a, st);
-    return launch_gemm<128, true, 2>(tm, a, st);
+    if (rc != 0 || !split_tail) return rc;
+    // more tiles than SMs: the BatchNorm backward runs as a launch of its own over the stored dpre
+    const idcb_bn_tail* t = f->tail;
+    return idcb_bn_bwd_apply(0, dx, 0, d->x_pitch, d->x_coff, f->aux, f->aux_pitch, f->aux_coff, t->out, t->out_pitch,
+                             t->out_coff, f->stat_a, f->stat_b, t->mean, t->rstd, f->bwd_scale, t->count, t->dgamma,
+                             t->dbeta, a.M, d->cin, stream);
 }
 
 extern "C" int idcb_conv_wgrad(const idcb_conv_desc* d, const void* x, const void* dy, float* dw,

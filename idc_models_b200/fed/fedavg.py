@@ -121,6 +121,17 @@ def _local_clients(federated_data: list, world, placement: str) -> list:
     return federated_data[world.rank::world.size]
 
 
+def _sum_over_ranks(world, t: torch.Tensor, fused: bool = True) -> torch.Tensor:
+    """Federated metric aggregation: on GPUs the three scalars are summed by the peer-memory
+    kernel (parallel/symm.py:ScalarReducer), elsewhere by the library collective."""
+    if not world.is_distributed:
+        return t
+    if fused and t.is_cuda:
+        from ..parallel.symm import ScalarReducer
+        return ScalarReducer.for_world(world).sum(t)
+    return world.all_reduce_sum(t)
+
+
 class FederatedAveragingProcess:
     def __init__(self, model_fn, client_optimizer_fn, server_optimizer_fn=None, strategy=None, comm: str = "fused",
                  placement: str = "round_robin"):
@@ -200,9 +211,7 @@ class FederatedAveragingProcess:
             weights.tensor[k] = float(n_ex)
         ranges = net.store.ranges(net.trainable_layer_indices())
         new_master = self._aggregate(net, state, clients, weights, gbuf, gshadow, k_local, ranges)
-        if world.is_distributed:
-            world.all_reduce_sum(msum)
-        msum = msum.cpu()
+        msum = _sum_over_ranks(world, msum, fused=self.comm == "fused").cpu()
         cnt = max(float(msum[2]), 1.0)
         metrics = (float(msum[1]) / cnt, float(msum[0]) / cnt)
         return ServerState(new_master, state.stats.clone(), net), metrics
@@ -282,15 +291,12 @@ def build_federated_evaluation(model_fn, placement: str = "round_robin"):
         if net.optimizer is None:
             net.compile(optimizer=SGD(0.0), loss=wr.loss, metrics=wr.metrics)
         mine = _local_clients(federated_data, world, placement)
-        msum = torch.zeros(3, dtype=torch.float64)
+        msum = torch.zeros(3, dtype=torch.float64, device=net.device)   # stays on the device: no sync per batch
         for ds in mine:
             for x, y in ds:
                 stats, _ = net.executor.eval_batch(x, y)
-                msum += stats.detach().to("cpu", torch.float64)
-        if world.is_distributed:
-            t = msum.to(net.device)
-            world.all_reduce_sum(t)
-            msum = t.cpu()
+                msum += stats.detach()[:3].to(torch.float64)
+        msum = _sum_over_ranks(world, msum).cpu()
         cnt = max(float(msum[2]), 1.0)
         return (float(msum[1]) / cnt, float(msum[0]) / cnt)
     return evaluation

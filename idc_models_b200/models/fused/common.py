@@ -80,6 +80,7 @@ class FusedExecutor:
         if hook is None:
             self.run(plan, training, grad_scale)
             return
+        hook.scalars_src = plan.acc          # the step's metric slots ride on the last bucket's barrier
         hook.begin()
         self._hook_live = True
         try:

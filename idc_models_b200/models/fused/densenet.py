@@ -19,6 +19,8 @@ backward for the same layer.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from ...ops import conv as OC
@@ -101,6 +103,7 @@ class DenseNetExecutor(FusedExecutor):
                 dl.y1 = torch.zeros(batch, h, w, 4 * GROWTH, dtype=bf, device=dev)
                 dl.o_sum1, dl.o_sq1 = sc.reserve(4 * GROWTH), sc.reserve(4 * GROWTH)
                 dl.bwd = ft <= dl.i_c2
+                dl.o_ctr = sc.reserve(64) if dl.bwd else None     # grid-barrier word of the dgrad + BN-tail launch
                 dl.bn0 = BNState(self, n + "_0_bn", dl.cin, sc, dl.bwd and ft <= dl.i_bn0)
                 dl.bn1 = BNState(self, n + "_1_bn", 4 * GROWTH, sc, dl.bwd and ft <= dl.i_bn1)
                 blk.layers.append(dl)
@@ -218,10 +221,22 @@ class DenseNetExecutor(FusedExecutor):
 
     # -------------------------------------------------------------------------------------------------
     def _consumer_bn_backward(self, blk, bn: BNState) -> None:
-        """A BN reading the block buffer has produced sa/sb in its consumer's dgrad epilogue: emit its
-        parameter gradients and fold its share of the batch-statistics correction into S1/S2."""
+        """A BN reading the block buffer has produced sa/sb in its consumer's dgrad epilogue. Its parameter
+        gradients and its share of the batch-statistics correction (S1/S2) are NOT given a launch of their own:
+        the next slice finalisation of the same block folds them in (csrc/elementwise.cu:idcb_bn_bwd_slice);
+        whatever is still pending when the block's gradients are announced is flushed by _flush_pending."""
         if not bn.trainable:
             return
+        self._flush_pending()
+        self._pending = (blk, bn)
+
+    _pending = None
+
+    def _flush_pending(self) -> None:
+        if self._pending is None:
+            return
+        blk, bn = self._pending
+        self._pending = None
         sc = blk.scratch
         K.bn_bwd_coeffs(bn.sa, bn.sb, bn.mean, bn.rstd, bn.scale, blk.count, dgamma=bn.dgamma,
                         dbeta=bn.dbeta, acc_s1=sc.view(blk.o_s1, bn.c), acc_s2=sc.view(blk.o_s2, bn.c))
@@ -230,11 +245,17 @@ class DenseNetExecutor(FusedExecutor):
         """out (bf16, c_n channels) = d(loss)/d(buffer[:, c_lo:c_lo+c_n]) including the BN-statistics
         terms of every consumer."""
         sc = blk.scratch
-        s1 = sc.view(blk.o_s1, blk.ctot)[c_lo:c_lo + c_n]
-        s2 = sc.view(blk.o_s2, blk.ctot)[c_lo:c_lo + c_n]
+        pend = None
+        if self._pending is not None:
+            pblk, pbn = self._pending
+            if pblk is blk and c_lo + c_n <= pbn.c:
+                pend = (pbn.sa, pbn.sb, pbn.mean, pbn.rstd, pbn.scale, pbn.dgamma, pbn.dbeta)
+                self._pending = None
+            else:
+                self._flush_pending()
         bn = blk.bn_t
-        K.bn_bwd_apply(2, blk.G, blk.buf, out, c_n, blk.count, sa=s1, sb=s2, mean=bn.mean[c_lo:c_lo + c_n],
-                       rstd=bn.rstd[c_lo:c_lo + c_n], g_coff=c_lo, x_coff=c_lo)
+        K.bn_bwd_slice(blk.G, blk.buf, out, c_lo, c_n, blk.count, sc.view(blk.o_s1, blk.ctot),
+                       sc.view(blk.o_s2, blk.ctot), bn.mean, bn.rstd, pending=pend)
 
     def grad_ready_offsets(self) -> list:
         """after dense block bi's backward, every gradient at or above the block's first parameter is final"""
@@ -259,6 +280,8 @@ class DenseNetExecutor(FusedExecutor):
     # Joins: before a buffer a pending wgrad reads (the block's dy3 / dy1 scratch) is overwritten — i.e. at the
     # start of the next layer — and before the block's gradients are announced as final.
     wgrad_side_stream = True
+    # finish BN1's backward inside the 3x3 dgrad launch (IDCB_BN_TAIL=0: separate bn_bwd_apply launch)
+    bn_tail = os.environ.get("IDCB_BN_TAIL", "1") != "0"
 
     def _wgrad(self, *args, **kw) -> None:
         if not self.wgrad_side_stream:
@@ -278,8 +301,10 @@ class DenseNetExecutor(FusedExecutor):
             self._wg_pending = False
 
     def _backward(self, p) -> None:
+        self._pending = None
         try:
             self._backward_impl(p)
+            self._flush_pending()
         finally:
             self._wgrad_join()      # whichever way the truncated backward ended, the side stream rejoins
 
@@ -326,18 +351,26 @@ class DenseNetExecutor(FusedExecutor):
                 if ft > dl.i_bn1:
                     continue
                 bn1 = dl.bn1
+                # BN1's backward rides in the dgrad launch: column sums, a grid barrier with the tile parked in
+                # TMEM, then dy1 straight from the accumulators (dpre1 never goes to memory). The native side
+                # falls back to dgrad + bn_bwd_apply through dpre1 when the grid has more tiles than SMs (block 1).
+                tail = None
+                if self.bn_tail and ft <= dl.i_c1:
+                    tail = OC.bn_tail(blk.dy1, bn1.mean, bn1.rstd, blk.count, counter=sc.view(dl.o_ctr, 1),
+                                      dgamma=bn1.dgamma, dbeta=bn1.dbeta, frozen=not bn1.trainable)
                 OC.conv_dgrad_raw(dl.g2, blk.dy3, self.w16(w2), blk.dpre1, mode=2, aux=dl.y1,
                                   bwd_scale=bn1.scale, bwd_shift=bn1.shift, bwd_act=ACT_RELU,
-                                  stat_a=bn1.sa, stat_b=bn1.sb)
+                                  stat_a=bn1.sa, stat_b=bn1.sb, tail=tail)
                 if ft > dl.i_c1:
                     # only BN1's own parameters are trainable below this point
                     if bn1.trainable:
                         K.bn_bwd_coeffs(bn1.sa, bn1.sb, bn1.mean, bn1.rstd, bn1.scale, blk.count,
                                         dgamma=bn1.dgamma, dbeta=bn1.dbeta)
                     continue
-                K.bn_bwd_apply(0 if bn1.trainable else 1, blk.dpre1, dl.y1, blk.dy1, 4 * GROWTH, blk.count,
-                               sa=bn1.sa, sb=bn1.sb, mean=bn1.mean, rstd=bn1.rstd, scale=bn1.scale,
-                               dgamma=bn1.dgamma, dbeta=bn1.dbeta)
+                if tail is None:
+                    K.bn_bwd_apply(0 if bn1.trainable else 1, blk.dpre1, dl.y1, blk.dy1, 4 * GROWTH, blk.count,
+                                   sa=bn1.sa, sb=bn1.sb, mean=bn1.mean, rstd=bn1.rstd, scale=bn1.scale,
+                                   dgamma=bn1.dgamma, dbeta=bn1.dbeta)
                 w1 = dl.name + "_1_conv/kernel"
                 bn0 = dl.bn0
                 if dl.i_c1 in tr:
@@ -350,6 +383,7 @@ class DenseNetExecutor(FusedExecutor):
                                   stat_a=bn0.sa, stat_b=bn0.sb)
                 self._consumer_bn_backward(blk, bn0)
             self._wgrad_join()
+            self._flush_pending()       # the block's first BatchNorm: its gradients are part of the announcement
             self.grads_ready(self._block_offsets[bi])
         # ---- stem ---------------------------------------------------------------------------------------
         if not p.stem_bwd:

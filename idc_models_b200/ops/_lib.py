@@ -45,12 +45,19 @@ class BnInline(C.Structure):
     ]
 
 
+class BnTail(C.Structure):
+    _fields_ = [
+        ("out", vp), ("out_pitch", C.c_int), ("out_coff", C.c_int), ("mean", vp), ("rstd", vp),
+        ("count", C.c_float), ("dgamma", vp), ("dbeta", vp), ("counter", vp), ("frozen", C.c_int),
+    ]
+
+
 class ConvBwdFused(C.Structure):
     _fields_ = [
         ("mode", C.c_int), ("aux", vp), ("aux_pitch", C.c_int), ("aux_coff", C.c_int),
         ("bwd_scale", vp), ("bwd_shift", vp), ("bwd_act", C.c_int),
         ("gacc", vp), ("g_pitch", C.c_int), ("g_coff", C.c_int),
-        ("stat_a", vp), ("stat_b", vp),
+        ("stat_a", vp), ("stat_b", vp), ("tail", vp),
     ]
 
 

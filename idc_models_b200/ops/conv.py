@@ -103,8 +103,9 @@ def conv_fprop_raw(g: ConvGeom, x: torch.Tensor, w: torch.Tensor, y: torch.Tenso
 def conv_dgrad_raw(g: ConvGeom, dy: torch.Tensor, w: torch.Tensor, dx: torch.Tensor | None, *,
                    dy_coff: int = 0, dx_coff: int = 0, dx_pitch: int | None = None, mode: int = 0,
                    aux=None, aux_coff: int = 0, bwd_scale=None, bwd_shift=None, bwd_act: int = ACT_NONE,
-                   gacc=None, g_coff: int = 0, stat_a=None, stat_b=None) -> None:
-    """dx = epi(conv^T(dy, w)); see include/idcb200.h for the epilogue modes."""
+                   gacc=None, g_coff: int = 0, stat_a=None, stat_b=None, tail=None) -> None:
+    """dx = epi(conv^T(dy, w)); see include/idcb200.h for the epilogue modes. ``tail`` (bn_tail(...)): finish
+    the BatchNorm backward of the mode-2 epilogue in the same launch."""
     _chk(dy, torch.bfloat16, "dy"); _chk(w, torch.bfloat16, "w"); _chk(dx, torch.bfloat16, "dx")
     _chk(aux, torch.bfloat16, "aux"); _chk(gacc, torch.float32, "gacc")
     b = dy.shape[0]
@@ -114,7 +115,8 @@ def conv_dgrad_raw(g: ConvGeom, dy: torch.Tensor, w: torch.Tensor, dx: torch.Ten
     f = _lib.ConvBwdFused(mode, _lib.ptr(aux), aux.shape[-1] if aux is not None else 0, aux_coff,
                           _lib.ptr(bwd_scale), _lib.ptr(bwd_shift), bwd_act, _lib.ptr(gacc),
                           gacc.shape[-1] if gacc is not None else 0, g_coff, _lib.ptr(stat_a),
-                          _lib.ptr(stat_b))
+                          _lib.ptr(stat_b),
+                          C.cast(C.pointer(tail), C.c_void_p) if tail is not None else C.c_void_p(0))
     lib = _lib.cuda_lib()
     _lib.check(lib.idcb_conv_dgrad(C.byref(d), _lib.ptr(dy), _lib.ptr(w), _lib.ptr(dx), C.byref(f),
                                    _lib.stream()))
@@ -131,6 +133,15 @@ def conv_wgrad_raw(g: ConvGeom, x: torch.Tensor, dy: torch.Tensor, dw: torch.Ten
     _lib.check(lib.idcb_conv_wgrad(C.byref(d), _lib.ptr(x), _lib.ptr(dy), _lib.ptr(dw),
                                    _lib.ptr(pro_scale), _lib.ptr(pro_shift), pro_act, _lib.stream()))
     _lib.count_launch()
+
+
+def bn_tail(out: torch.Tensor, mean, rstd, count, counter=None, dgamma=None, dbeta=None, out_coff: int = 0,
+            frozen: bool = False) -> _lib.BnTail:
+    """BatchNorm backward to be finished inside a mode-2 dgrad launch (include/idcb200.h: idcb_bn_tail).
+    ``counter``: a zeroed 4-byte slot (any dtype) private to this launch."""
+    p = _lib.ptr
+    return _lib.BnTail(p(out), out.shape[-1], out_coff, p(mean), p(rstd), float(count), p(dgamma), p(dbeta),
+                       p(counter), 1 if frozen else 0)
 
 
 def bn_inline(sum_, sq, gamma, beta, count, eps, momentum, scale_out, shift_out, mean_out, rstd_out,

@@ -99,6 +99,17 @@ def bn_bwd_apply(mode, g, x, out, channels, count, *, sa=None, sb=None, mean=Non
           C.c_longlong(_rows(x)), C.c_int(channels))
 
 
+def bn_bwd_slice(g, x, out, c_lo, channels, count, acc_s1, acc_s2, mean, rstd, pending=None):
+    """DenseNet block-buffer slice backward with the pending consumer BatchNorm's bookkeeping folded in.
+    ``pending`` = (sa, sb, mean, rstd, scale, dgamma, dbeta) over channels [0, len(sa)) of the block."""
+    ps = pending or (None,) * 7
+    _call(_lib.cuda_lib().idcb_bn_bwd_slice, _p(g), C.c_int(g.shape[-1]), C.c_int(c_lo), _p(x),
+          C.c_int(x.shape[-1]), C.c_int(c_lo), _p(out), C.c_int(out.shape[-1]), C.c_int(0), _p(acc_s1), _p(acc_s2),
+          C.c_int(c_lo), _off(mean, c_lo), _off(rstd, c_lo), C.c_float(count), C.c_longlong(_rows(x)),
+          C.c_int(channels), _p(ps[0]), _p(ps[1]), _p(ps[2]), _p(ps[3]), _p(ps[4]), _p(ps[5]), _p(ps[6]),
+          C.c_int(ps[0].numel() if ps[0] is not None else 0))
+
+
 def channel_stats(x, channels, sum_, sq, coff=0):
     _call(_lib.cuda_lib().idcb_channel_stats, _p(x), C.c_int(x.shape[-1]), C.c_int(coff),
           C.c_longlong(_rows(x)), C.c_int(channels), _p(sum_), _p(sq))

@@ -25,6 +25,16 @@ from .symm import SymmAllocator, ptr_array
 
 vp = C.c_void_p
 
+# launches of csrc/comm.cu:allreduce_optim_kernel issued (or captured) by this process; bench.py reports the
+# per-step count next to its replica checksum
+ALLREDUCE_LAUNCHES = 0
+
+
+def _count_allreduce() -> None:
+    global ALLREDUCE_LAUNCHES
+    ALLREDUCE_LAUNCHES += 1
+    _lib.count_launch()
+
 
 class FusedComm:
     def __init__(self, world, store, use_multicast: bool = True):
@@ -53,6 +63,7 @@ class FusedComm:
             store.stats = self.stats.tensor[:self.n_stats]
         self.scal = self.alloc.alloc(4, torch.float32)
         self.scal_out = torch.zeros(4, dtype=torch.float32, device=world.device)
+        self.red = self.alloc.alloc(64, torch.float32)       # reduce_scalars staging (up to 64 values)
         torch.cuda.synchronize()
         world.barrier()
 
@@ -66,7 +77,8 @@ class FusedComm:
         tensor) is summed over ranks on the kernel's barrier; the sum is returned."""
         want_scalars = scalars is not None
         if want_scalars:
-            self.scal.tensor[:4].copy_(scalars.reshape(-1)[:4])
+            k = min(4, scalars.numel())
+            self.scal.tensor[:k].copy_(scalars.reshape(-1)[:k])
         optimizer.iterations += 1
         self.store.touch()
         lr = optimizer._step_lr()
@@ -89,9 +101,25 @@ class FusedComm:
                 C.c_float(p2), C.c_float(eps), C.c_float(grad_scale), C.c_int(owner),
                 self.scal.ptrs() if scalars is not None else None,
                 vp(self.scal_out.data_ptr()) if scalars is not None else vp(0), _lib.stream()))
-            _lib.count_launch()
+            _count_allreduce()
             scalars = None      # reduce the metric slots once, with the first range
         return self.scal_out if want_scalars else None
+
+    def reduce_scalars(self, t: torch.Tensor) -> torch.Tensor:
+        """Sum of a handful of device scalars over ranks through the owner-computes kernel: no
+        library collective. Values travel as fp32."""
+        n = t.numel()
+        if n > self.red.tensor.numel():
+            raise ValueError("reduce_scalars: at most 64 values")
+        n4 = -(-n // 4) * 4
+        self.red.tensor[:n4].zero_()
+        self.red.tensor[:n].copy_(t.reshape(-1).to(torch.float32))
+        lib = _lib.cuda_lib()
+        cw = self.alloc.comm_world()
+        _lib.check(lib.idcb_stat_reduce(C.byref(cw), self.red.ptrs(), self.red.mc() if self.red.mc_ptr else vp(0),
+                                        C.c_longlong(n4), C.c_float(1.0), _lib.stream()))
+        _lib.count_launch()
+        return self.red.tensor[:n].to(t.dtype).reshape(t.shape).clone()
 
     def stat_mean(self) -> None:
         """store.stats <- mean over ranks (csrc/comm.cu:stat_mean_kernel); every rank ends with the same values"""
@@ -104,11 +132,18 @@ class FusedComm:
                                       C.c_longlong(n4), _lib.stream()))
         _lib.count_launch()
 
-    def allreduce_range(self, optimizer, b: int, e: int, grad_scale: float = 1.0) -> None:
+    def allreduce_range(self, optimizer, b: int, e: int, grad_scale: float = 1.0, scalars=None) -> None:
         """One launch over the flat range [b, e) with the optimizer's CURRENT scalars; no step bookkeeping
-        (used by :class:`OverlapSchedule`, which may run inside a captured graph)."""
+        (used by :class:`OverlapSchedule`, which may run inside a captured graph). ``scalars``: a device
+        tensor of >= 3 floats (or the string "zero") whose sum over ranks lands in ``self.scal_out``."""
         if e <= b:
             return
+        if scalars is not None:
+            if isinstance(scalars, str):
+                self.scal.tensor[:4].zero_()
+            else:
+                k = min(4, scalars.numel())
+                self.scal.tensor[:k].copy_(scalars.reshape(-1)[:k])
         lr = optimizer._step_lr()
         p1, p2, eps = optimizer._params()
         lib = _lib.cuda_lib()
@@ -122,8 +157,10 @@ class FusedComm:
             vp(s1.data_ptr() + 4 * b if s1 is not None else 0),
             vp(s2.data_ptr() + 4 * b if s2 is not None else 0),
             C.c_longlong(e - b), C.c_int(KIND[optimizer.kind]), C.c_float(lr), C.c_float(p1),
-            C.c_float(p2), C.c_float(eps), C.c_float(grad_scale), C.c_int(-1), None, vp(0), _lib.stream()))
-        _lib.count_launch()
+            C.c_float(p2), C.c_float(eps), C.c_float(grad_scale), C.c_int(-1),
+            self.scal.ptrs() if scalars is not None else None,
+            vp(self.scal_out.data_ptr()) if scalars is not None else vp(0), _lib.stream()))
+        _count_allreduce()
 
 
 def plan_buckets(ready_offsets, lo: int, hi: int, min_bucket: int) -> list:
@@ -171,6 +208,9 @@ class OverlapSchedule:
         self._next = 0
         self._forked = False
         self.consumed = False        # set by the executor once a training step has launched (or replayed) the buckets
+        # the step's (loss sum, correct, count) slots on this rank: summed over ranks by the LAST bucket's kernel
+        # (set by the executor before begin(); None = this rank contributes zeros)
+        self.scalars_src = None
 
     def key(self):
         o = self.optimizer
@@ -187,7 +227,8 @@ class OverlapSchedule:
         # buckets that run next to the backward kernels use few CTAs; the last one has the GPU to itself
         lib.idcb_comm_set_max_ctas(C.c_int(0 if last else self.overlap_ctas))
         with torch.cuda.stream(self.side):
-            self.fused.allreduce_range(self.optimizer, b, e, self.grad_scale)
+            self.fused.allreduce_range(self.optimizer, b, e, self.grad_scale,
+                                       scalars=(self.scalars_src if self.scalars_src is not None else "zero") if last else None)
         lib.idcb_comm_set_max_ctas(C.c_int(0))
         self._forked = True
 
@@ -201,13 +242,14 @@ class OverlapSchedule:
         """launch what is left (at least the bottom bucket) and join the side stream"""
         while self._next < len(self.plan):
             _, b, e = self.plan[self._next]
-            self._launch(b, e, last=True)
+            self._launch(b, e, last=self._next == len(self.plan) - 1)
             self._next += 1
         if self._forked:
             torch.cuda.current_stream().wait_stream(self.side)
 
     def run_all(self) -> None:
         """a rank with an empty local batch: same launches, nothing to overlap with"""
+        self.scalars_src = None
         self.begin()
         self.end()
 
@@ -225,4 +267,4 @@ def allreduce_apply_emulated(emu, rank_bufs, opt_states, n, kind, lr, p1, p2, ep
             vp(s1.data_ptr() if s1 is not None else 0), vp(s2.data_ptr() if s2 is not None else 0),
             C.c_longlong(n), C.c_int(KIND[kind]), C.c_float(lr), C.c_float(p1), C.c_float(p2),
             C.c_float(eps), C.c_float(grad_scale), C.c_int(owner), None, vp(0), _lib.stream()))
-        _lib.count_launch()
+        _count_allreduce()

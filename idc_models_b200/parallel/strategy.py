@@ -70,12 +70,14 @@ class Strategy:
             store.refresh_shadow()
 
     # ---- per-step gradient reduction + update (C1 + K13) --------------------------------------
-    def reduce_and_apply(self, store, optimizer, grad_scale: float = 1.0) -> None:
-        """Sum gradients over replicas and apply the optimizer on every replica."""
+    def reduce_and_apply(self, store, optimizer, grad_scale: float = 1.0, scalars=None):
+        """Sum gradients over replicas and apply the optimizer on every replica. ``scalars`` (the step's
+        device-side loss-sum / correct / count slots) are summed over replicas on the way where the transport
+        can carry them (the fused kernel's barrier); the global sums are returned, else None."""
         w = self.world
         if not w.is_distributed:
             optimizer.apply(grad_scale)
-            return
+            return None
         if self.comm == "fused":
             sched = getattr(self, "_overlap", None)
             if sched is not None and sched.optimizer is optimizer:
@@ -86,12 +88,13 @@ class Strategy:
                 sched.consumed = False
                 optimizer.iterations += 1
                 store.touch()
-                return
-            self._fused_comm(store).allreduce_apply(optimizer, grad_scale)
-            return
+                return sched.fused.scal_out[:3] if scalars is not None else None
+            out = self._fused_comm(store).allreduce_apply(optimizer, grad_scale, scalars=scalars)
+            return out[:3] if out is not None else None
         for b, e in optimizer.ranges:
             w.all_reduce_sum(store.grad[b:e])
         optimizer.apply(grad_scale)
+        return None
 
     def _fused_comm(self, store):
         if self._fused is None or self._fused.store is not store:
@@ -130,6 +133,9 @@ class Strategy:
 
     # ---- scalar metric reduction (C2) -----------------------------------------------------------
     def reduce_scalars(self, t: torch.Tensor) -> torch.Tensor:
+        if (self.comm == "fused" and self._fused is not None and self.world.is_distributed and t.is_cuda
+                and t.numel() <= 64 and t.dtype in (torch.float32, torch.float16, torch.bfloat16)):
+            return self._fused.reduce_scalars(t)
         return self.world.all_reduce_sum(t)
 
     # ---- BN moving statistics: MEAN over replicas when read (C4) -------------------------------
@@ -161,15 +167,15 @@ class CentralStorageStrategy(Strategy):
         super().__init__(world or World.from_env(), comm)
         self.owner = owner
 
-    def reduce_and_apply(self, store, optimizer, grad_scale: float = 1.0) -> None:
+    def reduce_and_apply(self, store, optimizer, grad_scale: float = 1.0, scalars=None):
         w = self.world
         if not w.is_distributed:
             optimizer.apply(grad_scale)
-            return
+            return None
         if self.comm == "fused":
             # same kernel, one owner: reduce-to-owner + update + broadcast over NVLink
-            self._fused_comm(store).allreduce_apply(optimizer, grad_scale, owner=self.owner)
-            return
+            out = self._fused_comm(store).allreduce_apply(optimizer, grad_scale, owner=self.owner, scalars=scalars)
+            return out[:3] if out is not None else None
         # gradients -> owner ; owner applies ; fresh variables -> everyone
         for b, e in optimizer.ranges:
             w.reduce_to(store.grad[b:e], self.owner)
@@ -204,8 +210,9 @@ class FederatedStrategy(Strategy):
     def local_slice(self, n: int) -> slice:
         return slice(0, n)
 
-    def reduce_and_apply(self, store, optimizer, grad_scale: float = 1.0) -> None:
+    def reduce_and_apply(self, store, optimizer, grad_scale: float = 1.0, scalars=None):
         optimizer.apply(grad_scale)
+        return None
 
     def reduce_scalars(self, t):
         return t

@@ -107,6 +107,40 @@ class SymmAllocator:
         return cw
 
 
+class ScalarReducer:
+    """Sum of a few device scalars over the ranks of a world through the owner-computes peer-memory kernel
+    (csrc/comm.cu:stat_mean_kernel with scale 1) instead of a library collective: the metric aggregation of the
+    data-parallel and federated loops. One instance per world (``for_world``)."""
+    _cache: dict = {}
+
+    def __init__(self, world, alloc: "SymmAllocator | None" = None):
+        self.world = world
+        self.alloc = alloc or SymmAllocator(world)
+        self.buf = self.alloc.alloc(64, torch.float32)
+
+    @classmethod
+    def for_world(cls, world) -> "ScalarReducer":
+        r = cls._cache.get(id(world))
+        if r is None or r.world is not world:
+            r = cls(world)
+            cls._cache[id(world)] = r
+        return r
+
+    def sum(self, t: torch.Tensor) -> torch.Tensor:
+        from ..ops import _lib
+        n = t.numel()
+        if n > 64:
+            raise ValueError("ScalarReducer: at most 64 values")
+        n4 = -(-n // 4) * 4
+        self.buf.tensor[:n4].zero_()
+        self.buf.tensor[:n].copy_(t.reshape(-1).to(torch.float32))
+        cw = self.alloc.comm_world()
+        _lib.check(_lib.cuda_lib().idcb_stat_reduce(C.byref(cw), self.buf.ptrs(), self.buf.mc(), C.c_longlong(n4),
+                                                    C.c_float(1.0), _lib.stream()))
+        _lib.count_launch()
+        return self.buf.tensor[:n].to(t.dtype).reshape(t.shape).clone()
+
+
 class EmulatedWorld:
     """N ranks emulated by one process on one device (tests / single-GPU development)."""
 

@@ -110,19 +110,26 @@ class _Accum:
     def __init__(self, net):
         self.net = net
         self.acc = torch.zeros(3, dtype=torch.float32, device=net.device)
+        self.gacc = torch.zeros(3, dtype=torch.float32, device=net.device)   # None once a step came without global sums
         self.extra = [m for m in net.metrics if not _builtin_metric(m)]
         for m in self.extra:
             m.reset()
 
-    def add(self, stats, logits, y):
+    def add(self, stats, logits, y, global_stats=None):
+        """``global_stats``: the same three slots already summed over replicas (they rode on the fused
+        all-reduce kernel's barrier); when every step provides them no collective is needed at the end."""
         self.acc += stats.to(self.acc.dtype)
+        if global_stats is not None and self.gacc is not None:
+            self.gacc += global_stats.to(self.acc.dtype)
+        else:
+            self.gacc = None
         for m in self.extra:
             if logits is not None and logits.shape[0]:
                 m.update(logits.float().cpu(), y.cpu())
 
     def result(self, prefix: str = "") -> dict:
         net = self.net
-        acc = net.strategy.reduce_scalars(self.acc.clone())
+        acc = self.gacc if self.gacc is not None else net.strategy.reduce_scalars(self.acc.clone())
         loss_sum, correct, count = (float(v) for v in acc.tolist())
         out = {prefix + "loss": loss_sum / count if count else 0.0}
         for m in net.metrics:
@@ -168,8 +175,8 @@ def fit(net, data, epochs, initial_epoch, validation_data, callbacks, verbose, s
                 xs, ys = x[sl], y[sl]
                 with nvtx_range("train_step"):
                     stats, logits = net.executor.train_batch(xs, ys, n)
-                    net.strategy.reduce_and_apply(net.store, net.optimizer, 1.0)
-                accum.add(stats, logits, ys)
+                    gstats = net.strategy.reduce_and_apply(net.store, net.optimizer, 1.0, scalars=stats)
+                accum.add(stats, logits, ys, gstats)
                 nb += 1
                 seen += n
                 if steps_per_epoch is not None and nb >= steps_per_epoch:

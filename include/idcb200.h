@@ -27,6 +27,11 @@ extern "C" {
 const char* idcb_last_error(void);
 int idcb_version(void);
 int idcb_device_sm_count(void);
+/* Programmatic dependent launch of the library's single-GPU kernels (default on, or IDCB_PDL=0):
+ * each kernel lets its successor start its set-up early and waits (griddepcontrol.wait) before it
+ * touches data. Returns the previous setting. Replaces nothing in the reference (the TF runtime's
+ * kernel scheduling, /root/reference/dist_model_tf_dense.py:148). */
+int idcb_set_pdl(int on);
 
 /* ---- convolution (tcgen05 implicit GEMM) --------------------------------------------------- */
 /* Geometry of the FORWARD convolution; dgrad/wgrad take the same descriptor. */
@@ -88,6 +93,25 @@ typedef struct idcb_conv_fused {
  *           dx (bf16, optional) = dpre ; gacc (fp32, optional) += bwd_scale * dpre
  *           stat_a[c] += sum_p dpre ; stat_b[c] += sum_p dpre * aux
  *   in modes 0/1 stat_a[c] += sum_p dx (bias gradient of the producer layer).                    */
+/* Mode 2 only, optional: the backward of the training-mode BatchNorm in front of the activation is finished
+ * inside the dgrad launch instead of by idcb_bn_bwd_apply. The kernel adds its column sums to stat_a/stat_b,
+ * the grid meets at a barrier (the fp32 tile stays in TMEM), and every CTA writes
+ *   out = scale*(dpre - stat_a/N - xhat*dgamma/N),  dgamma = rstd*(stat_b - mean*stat_a)
+ * (scale = bwd_scale); the first row of CTAs does dgamma += / dbeta +=. frozen != 0: out = scale*dpre, no
+ * barrier. `counter` is one zero-initialised 32-bit word per launch. If the grid cannot be co-resident
+ * (more tiles than SMs) the call falls back to the two-launch sequence through dx, which must then be given. */
+typedef struct idcb_bn_tail {
+    void* out;                   /* bf16, geometry of dx */
+    int out_pitch, out_coff;
+    const float* mean;
+    const float* rstd;
+    float count;
+    float* dgamma;               /* optional */
+    float* dbeta;
+    unsigned int* counter;
+    int frozen;
+} idcb_bn_tail;
+
 typedef struct idcb_conv_bwd_fused {
     int mode;
     const void* aux;
@@ -99,6 +123,7 @@ typedef struct idcb_conv_bwd_fused {
     int g_pitch, g_coff;
     float* stat_a;
     float* stat_b;
+    const idcb_bn_tail* tail;    /* optional (NULL = off) */
 } idcb_conv_bwd_fused;
 
 /* cuDNN convolution forward as called by Keras Conv2D (SURVEY 2.E K1/K2/K3/K6;
@@ -167,6 +192,17 @@ int idcb_bn_bwd_apply(int mode, const void* g, int g_is_float, int g_pitch, int 
                       int x_pitch, int x_coff, void* out, int o_pitch, int o_coff, const float* sa,
                       const float* sb, const float* mean, const float* rstd, const float* scale,
                       float count, float* dgamma, float* dbeta, long long M, int C, void* stream);
+/* DenseNet shared-buffer slice backward (mode 2 of idcb_bn_bwd_apply) that also finishes the bookkeeping of the
+ * block's most recent consumer BatchNorm in the same launch: dgamma/dbeta of that layer and its share of the
+ * S1/S2 accumulators (idcb_bn_bwd_coeffs would need a launch of its own). acc_s1/acc_s2 point at channel 0 of
+ * the block, the slice is channels [c_lo, c_lo + C); p_* describe the pending BatchNorm over channels [0, p_C)
+ * (p_sa == NULL: nothing pending). Replaces TF's FusedBatchNormGradV3 for the DenseNet BN layers
+ * (/root/reference/dist_model_tf_dense.py:131). */
+int idcb_bn_bwd_slice(const float* g, int g_pitch, int g_coff, const void* x, int x_pitch, int x_coff,
+                      void* out, int o_pitch, int o_coff, float* acc_s1, float* acc_s2, int c_lo,
+                      const float* mean, const float* rstd, float count, long long M, int C,
+                      const float* p_sa, const float* p_sb, const float* p_mean, const float* p_rstd,
+                      const float* p_scale, float* p_dgamma, float* p_dbeta, int p_C, void* stream);
 int idcb_channel_stats(const void* x, int pitch, int coff, long long M, int C, float* sum, float* sq,
                        void* stream);
 /* sum_g[c] += sum_p g, sum_gx[c] += sum_p g*x — BN backward sums for a dpre that is already in memory */
@@ -275,6 +311,12 @@ int idcb_allreduce_optim(const idcb_comm_world* w, void* const* grad, void* cons
  * MirroredStrategy, dist_model_tf_mobile.py:115-129): stats[p][0..n) of every rank is
  * replaced by the element-wise mean over ranks. n % 4 == 0. */
 int idcb_stat_mean(const idcb_comm_world* w, void* const* stats, void* mc_stats, long long n, void* stream);
+/* The same owner-computes kernel with an explicit factor: every rank's `stats` <- scale * sum over ranks.
+ * scale = 1 is the sum of a few metric scalars (loss sum, correct, count) over replicas / client groups
+ * without a library collective (the per-replica metric reduction of Keras fit/evaluate,
+ * /root/reference/dist_model_tf_mobile.py:136, and TFF's federated metric aggregation, fed_model.py:228). */
+int idcb_stat_reduce(const idcb_comm_world* w, void* const* stats, void* mc_stats, long long n, float scale,
+                     void* stream);
 /* Cap on the CTAs used by the communication kernels (0 = one per SM, the default). Used for gradient buckets
  * that are reduced while the backward pass is still running (SURVEY 8.1 "tile by tile as buckets become ready"). */
 int idcb_comm_set_max_ctas(int max_ctas);
@@ -302,10 +344,18 @@ int idcb_secagg_masked_sum(const idcb_comm_world* w, void* const* clients, void*
  * has given the whole GPU to its own arena, a process under a memory quota fixed at start-up, or code
  * that cannot tolerate the implicit device synchronisation of cudaMalloc/cudaFree.
  *   out[offset:offset+n] = mean over the k_clients rows of clients[k][offset:offset+n]
- * - n above the limit is refused with an error (use the caller-buffer entry point instead);
- * - the first call on each device looks the storage up (cudaGetSymbolAddress) and caches the address;
+ * - n above the limit is refused with an error (use the caller-buffer entry point instead); so are a
+ *   range that does not fit in a row (offset + n > stride) and pointers that are not 16-byte aligned;
+ * - the first call on each device looks the storage up (cudaGetSymbolAddress, serialised by a mutex) and
+ *   caches the address per device ordinal: make that first call outside any stream capture, and do not
+ *   call again on a device after cudaDeviceReset (the cached address would be stale);
  * - every call on a GPU reuses the same storage: calls whose kernels could overlap on the device
- *   (different streams) race with each other and must be serialised by the caller. */
+ *   (different streams) race with each other and must be serialised by the caller;
+ * - with ONE GPU no pairwise mask is ever generated (masks exist only between clients on different GPUs;
+ *   pairs on one GPU cancel and are skipped), so the staging area holds the plain fixed-point ring sum:
+ *   this call reproduces the masked sum's arithmetic, it hides nothing from the GPU that runs it;
+ * - the kernel contains a grid-wide barrier and is launched cooperatively: if its grid cannot be
+ *   co-resident on the device the launch fails with an error instead of waiting. */
 long long idcb_secagg_noalloc_max_elems(void);
 int idcb_secagg_mean_noalloc(const float* clients, float* out, int k_clients, long long stride,
                              long long offset, long long n, int frac_bits, unsigned long long session_seed,

@@ -216,3 +216,141 @@ def test_wgrad_prologue_and_offsets():
     y = C.conv_ref(g, a, wref)
     (gw,) = torch.autograd.grad(y, wref, dybuf[..., 32:64].float())
     _close(dw, gw, 1e-2)
+
+
+# ---------------------------------------------------------------------------------------------
+# Shapes that only the whole-model tests used to reach (round-1 review): strided / asymmetric stems with a
+# tap-packed K axis, wgrad with Cout that is not a multiple of 64, tiny-M mode-2 dgrad.
+# ---------------------------------------------------------------------------------------------
+STEM_CASES = [
+    # b, h, w, cin, cout, k, stride, padding
+    (4, 50, 50, 8, 64, 7, 2, ((3, 3), (3, 3))),      # DenseNet stem on IDC patches (RGB padded to 8)
+    (4, 32, 32, 8, 64, 7, 2, ((3, 3), (3, 3))),      # ... on CIFAR
+    (4, 50, 50, 8, 32, 3, 2, ((0, 1), (0, 1))),      # MobileNetV2 stem, Keras correct_pad on an even size
+    (4, 25, 25, 8, 32, 3, 2, ((1, 1), (1, 1))),      # ... odd size
+    (2, 13, 13, 96, 96, 3, 2, ((0, 1), (0, 1))),
+]
+
+
+@pytest.mark.parametrize("b,h,w,cin,cout,k,stride,padding", STEM_CASES)
+def test_fprop_strided_and_tap_packed(b, h, w, cin, cout, k, stride, padding):
+    torch.manual_seed(10)
+    g = C.geom(h, w, cin, cout, k, stride, padding)
+    x = _rand(b, h, w, cin)
+    wt = _rand(cout, k, k, cin, scale=(k * k * cin) ** -0.5)
+    y = torch.zeros(b, g.ho, g.wo, cout, device="cuda", dtype=torch.bfloat16)
+    s1 = torch.zeros(cout, device="cuda")
+    C.conv_fprop_raw(g, x, wt, y, stat_sum=s1)
+    torch.cuda.synchronize()
+    _close(y, C.conv_ref(g, x.float(), wt.float()))
+    _close(s1, y.float().reshape(-1, cout).sum(0), 1e-3)
+    # and its weight gradient (the same linearised (tap, channel) axis, now as the M axis)
+    dy = _rand(b, g.ho, g.wo, cout, scale=0.1)
+    dw = torch.zeros(cout, k, k, cin, device="cuda")
+    C.conv_wgrad_raw(g, x, dy, dw)
+    torch.cuda.synchronize()
+    wref = torch.zeros(cout, k, k, cin, device="cuda", requires_grad=True)
+    (gw,) = torch.autograd.grad(C.conv_ref(g, x.float(), wref), wref, dy.float())
+    _close(dw, gw, 1e-2)
+
+
+@pytest.mark.parametrize("cout", [24, 96, 160])
+def test_wgrad_cout_not_a_multiple_of_64(cout):
+    torch.manual_seed(11)
+    b, h, w, cin = 4, 7, 7, 192
+    g = C.geom(h, w, cin, cout, 1)
+    x = _rand(b, h, w, cin)
+    dy = _rand(b, h, w, cout, scale=0.1)
+    dw = torch.zeros(cout, 1, 1, cin, device="cuda")
+    C.conv_wgrad_raw(g, x, dy, dw)
+    torch.cuda.synchronize()
+    wref = torch.zeros(cout, 1, 1, cin, device="cuda", requires_grad=True)
+    (gw,) = torch.autograd.grad(C.conv_ref(g, x.float(), wref), wref, dy.float())
+    _close(dw, gw, 1e-2)
+
+
+def _mode2_reference(g, dy, wt, xraw, cin, sc, sh):
+    da = _dgrad_ref(g, dy, wt, (xraw.shape[0], g.h, g.w, cin))
+    xr = xraw[..., :cin].float()
+    return da * ((xr * sc + sh) > 0), xr
+
+
+@pytest.mark.parametrize("b,h,w", [(128, 1, 1), (1, 1, 1), (14, 3, 3)])
+def test_dgrad_mode2_tiny_m(b, h, w):
+    """M = 128 (exactly one tile), M = 1 and M = 126 (a tile with invalid rows)."""
+    torch.manual_seed(12)
+    cin, cout = 128, 32
+    g = C.geom(h, w, cin, cout, 3)
+    wt = _rand(cout, 3, 3, cin, scale=(9 * cout) ** -0.5)
+    dy = _rand(b, h, w, cout)
+    xraw = _rand(b, h, w, cin)
+    sc = torch.rand(cin, device="cuda") + 0.5
+    sh = torch.randn(cin, device="cuda") * 0.3
+    dpre = torch.zeros(b, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    sa = torch.zeros(cin, device="cuda")
+    sb = torch.zeros(cin, device="cuda")
+    C.conv_dgrad_raw(g, dy, wt, dpre, mode=2, aux=xraw, bwd_scale=sc, bwd_shift=sh, bwd_act=C.ACT_RELU,
+                     stat_a=sa, stat_b=sb)
+    torch.cuda.synchronize()
+    want, xr = _mode2_reference(g, dy, wt, xraw, cin, sc, sh)
+    _close(dpre, want)
+    _close(sa, want.reshape(-1, cin).sum(0), 2e-2)
+    _close(sb, (want * xr).reshape(-1, cin).sum(0), 2e-2)
+
+
+def _bn_backward_reference(dpre, x, mean, rstd, scale):
+    """dx, dgamma, dbeta of y = scale * (x - mean) * rstd / ... with batch statistics (rows = dim 0)"""
+    n = dpre.shape[0]
+    xhat = (x - mean) * rstd
+    dbeta = dpre.sum(0)
+    dgamma = (dpre * xhat).sum(0)
+    dx = scale * (dpre - dbeta / n - xhat * dgamma / n)
+    return dx, dgamma, dbeta
+
+
+@pytest.mark.parametrize("b,h,w,fused", [(4, 13, 13, True), (128, 1, 1, True), (14, 3, 3, True),
+                                         (128, 13, 13, False)])
+def test_dgrad_mode2_with_batchnorm_tail(b, h, w, fused):
+    """The BatchNorm backward finished inside the dgrad launch (grid barrier, tile parked in TMEM) equals
+    dgrad followed by the closed-form BN backward. The last case has more tiles than SMs: the native side must
+    take its two-launch route through dx and still produce the same numbers."""
+    torch.manual_seed(13)
+    cin, cout = 128, 32
+    g = C.geom(h, w, cin, cout, 3)
+    wt = _rand(cout, 3, 3, cin, scale=(9 * cout) ** -0.5)
+    dy = _rand(b, h, w, cout)
+    y1 = _rand(b, h, w, cin)
+    yf = y1.float().reshape(-1, cin)
+    mean = yf.mean(0)
+    rstd = (yf.var(0, unbiased=False) + 1e-5).rsqrt()
+    gamma = torch.rand(cin, device="cuda") + 0.5
+    beta = torch.randn(cin, device="cuda") * 0.3
+    sc = gamma * rstd
+    sh = beta - mean * sc
+    dpre = torch.zeros(b, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    out = torch.zeros(b, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    sa = torch.zeros(cin, device="cuda")
+    sb = torch.zeros(cin, device="cuda")
+    dgamma = torch.full((cin,), 0.25, device="cuda")       # accumulated into, not overwritten
+    dbeta = torch.full((cin,), -0.5, device="cuda")
+    counter = torch.zeros(64, device="cuda")
+    for rep in range(2):        # a second launch with a fresh counter word gives the same answer
+        sa.zero_(); sb.zero_(); counter.zero_()
+        tail = C.bn_tail(out, mean, rstd, b * h * w, counter=counter, dgamma=dgamma, dbeta=dbeta)
+        C.conv_dgrad_raw(g, dy, wt, dpre, mode=2, aux=y1, bwd_scale=sc, bwd_shift=sh, bwd_act=C.ACT_RELU,
+                         stat_a=sa, stat_b=sb, tail=tail)
+    torch.cuda.synchronize()
+    want_dpre, xr = _mode2_reference(g, dy, wt, y1, cin, sc, sh)
+    dx, dg, db = _bn_backward_reference(want_dpre.reshape(-1, cin), xr.reshape(-1, cin), mean, rstd, sc)
+    _close(out.reshape(-1, cin), dx, 3e-2)
+    _close(dgamma - 0.25, 2 * dg, 3e-2)
+    _close(dbeta + 0.5, 2 * db, 3e-2)
+    if fused:
+        assert dpre.abs().max().item() == 0, "dpre must not be written when the tail runs in the kernel"
+    # frozen BatchNorm: dx = scale * dpre, no statistics terms
+    out2 = torch.zeros_like(out)
+    tail = C.bn_tail(out2, mean, rstd, b * h * w, frozen=True)
+    C.conv_dgrad_raw(g, dy, wt, dpre, mode=2, aux=y1, bwd_scale=sc, bwd_shift=sh, bwd_act=C.ACT_RELU,
+                     stat_a=sa, stat_b=sb, tail=tail)
+    torch.cuda.synchronize()
+    _close(out2, want_dpre * sc, 2e-2)

@@ -294,3 +294,43 @@ def test_synth_patches_kernel():
     _lib.check(lib.idcb_synth_patches(C.c_void_p(x2.data_ptr()), None, C.c_longlong(64), C.c_int(50), C.c_int(50),
                                       C.c_int(3), C.c_ulonglong(7), C.c_uint(1), _lib.stream()))
     assert torch.equal(x, x2)        # counter-based: reproducible
+
+
+def test_bn_bwd_slice_folds_the_pending_consumer_batchnorm():
+    """idcb_bn_bwd_slice == bn_bwd_coeffs (S1/S2/dgamma/dbeta of the pending consumer) followed by the mode-2
+    slice backward, in one launch."""
+    from idc_models_b200.ops import kernels as K
+    torch.manual_seed(21)
+    M, ctot, pc, c_lo, cn = 4 * 13 * 13, 256, 160, 128, 32
+    G = torch.randn(4, 13, 13, ctot, device="cuda")
+    x = (torch.randn(4, 13, 13, ctot, device="cuda")).to(torch.bfloat16)
+    mean = torch.randn(ctot, device="cuda") * 0.1
+    rstd = torch.rand(ctot, device="cuda") + 0.5
+    p_sa, p_sb = torch.randn(pc, device="cuda"), torch.randn(pc, device="cuda")
+    p_scale = torch.rand(pc, device="cuda") + 0.5
+    s1_0, s2_0 = torch.randn(ctot, device="cuda"), torch.randn(ctot, device="cuda")
+    # two-launch reference
+    s1, s2 = s1_0.clone(), s2_0.clone()
+    dg_ref, db_ref = torch.ones(pc, device="cuda"), torch.ones(pc, device="cuda")
+    K.bn_bwd_coeffs(p_sa, p_sb, mean[:pc].contiguous(), rstd[:pc].contiguous(), p_scale, float(M), dgamma=dg_ref,
+                    dbeta=db_ref, acc_s1=s1[:pc], acc_s2=s2[:pc])
+    want = torch.zeros(4, 13, 13, cn, device="cuda", dtype=torch.bfloat16)
+    K.bn_bwd_apply(2, G, x, want, cn, float(M), sa=s1[c_lo:c_lo + cn], sb=s2[c_lo:c_lo + cn],
+                   mean=mean[c_lo:c_lo + cn], rstd=rstd[c_lo:c_lo + cn], g_coff=c_lo, x_coff=c_lo)
+    # fused
+    t1, t2 = s1_0.clone(), s2_0.clone()
+    dg, db = torch.ones(pc, device="cuda"), torch.ones(pc, device="cuda")
+    got = torch.zeros_like(want)
+    K.bn_bwd_slice(G, x, got, c_lo, cn, float(M), t1, t2, mean, rstd,
+                   pending=(p_sa, p_sb, mean[:pc].contiguous(), rstd[:pc].contiguous(), p_scale, dg, db))
+    torch.cuda.synchronize()
+    assert torch.equal(got, want)
+    assert torch.allclose(dg, dg_ref) and torch.allclose(db, db_ref)
+    outside = torch.ones(ctot, dtype=torch.bool, device="cuda")
+    outside[c_lo:c_lo + cn] = False
+    assert torch.allclose(t1[outside], s1[outside]) and torch.allclose(t2[outside], s2[outside])
+    # nothing pending: plain mode 2
+    got2 = torch.zeros_like(want)
+    K.bn_bwd_slice(G, x, got2, c_lo, cn, float(M), s1, s2, mean, rstd)
+    torch.cuda.synchronize()
+    assert torch.equal(got2, want)

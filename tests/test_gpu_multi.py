@@ -179,3 +179,80 @@ def test_federated_kernels_across_processes():
         f, l = o["fedavg"]["fused"], o["fedavg"]["nccl"]
         assert f[:2] == outs[0]["fedavg"]["fused"][:2], "ranks disagree on the FedAvg server model"
         assert abs(f[0] - l[0]) < 1e-3 * max(1.0, l[1]), (f, l)
+
+
+STRESS_WORKER = r'''
+import sys, json, ctypes as C, torch, torch.distributed as dist
+sys.path.insert(0, %r)
+from idc_models_b200.ops import _lib
+from idc_models_b200.parallel.symm import SymmAllocator
+from idc_models_b200.parallel.world import World
+world = World.from_env()
+dev, W, R = world.device, world.size, world.rank
+lib = _lib.cuda_lib()
+alloc = SymmAllocator(world)
+NMAX = 1 << 16
+grad, master, shadow = alloc.alloc(NMAX, torch.float32), alloc.alloc(NMAX, torch.float32), alloc.alloc(NMAX, torch.bfloat16)
+s1 = torch.zeros(NMAX, device=dev)
+ref = torch.zeros(NMAX, device=dev)             # what NCCL + a plain SGD step gives
+bad = torch.zeros(4, dtype=torch.int64, device=dev)
+gsh = torch.Generator().manual_seed(1234)        # shared by all ranks: the sequence of (n, offset, owner)
+gme = torch.Generator(device=dev).manual_seed(77 + R)
+mc = bool(grad.mc_ptr and master.mc_ptr and shadow.mc_ptr)
+vp = C.c_void_p
+ITERS = %d
+special = [4, 8, 4 * W - 4, 4 * W + 4, 4 * (W + 1) * 3, 1020, 4]
+for it in range(ITERS):
+    if it < len(special):
+        n = max(4, special[it])
+    else:
+        n = int(torch.randint(1, 4096, (1,), generator=gsh)) * 4
+    b = int(torch.randint(0, (NMAX - n) // 4 + 1, (1,), generator=gsh)) * 4
+    owner = int(torch.randint(0, W, (1,), generator=gsh)) if it %% 5 == 4 else -1
+    # integer-valued gradients: every summation order gives the same fp32 bits, so the comparison is exact
+    g = torch.randint(-8, 9, (n,), device=dev, generator=gme).float()
+    grad.tensor[b:b + n].copy_(g)
+    tot = g.clone()
+    dist.all_reduce(tot)
+    ref[b:b + n] += -0.5 * tot
+    cw = alloc.comm_world()
+    _lib.check(lib.idcb_allreduce_optim(
+        C.byref(cw), grad.ptrs(b), master.ptrs(b), shadow.ptrs(b), grad.mc(b) if mc else vp(0),
+        master.mc(b) if mc else vp(0), shadow.mc(b) if mc else vp(0), vp(s1.data_ptr() + 4 * b), vp(0),
+        C.c_longlong(n), C.c_int(1), C.c_float(0.5), C.c_float(0.0), C.c_float(0.0), C.c_float(1e-7),
+        C.c_float(1.0), C.c_int(owner), None, vp(0), _lib.stream()))
+    m = master.tensor
+    bad[0] += (m != ref).sum()                                     # element-wise, the whole buffer (untouched parts too)
+    bad[1] += (grad.tensor != 0).sum()                             # the consumed bucket is zero again, nothing else was dirtied
+    bad[2] += (shadow.tensor[b:b + n] != m[b:b + n].to(torch.bfloat16)).sum()
+torch.cuda.synchronize()
+chk = int(master.tensor.view(torch.int32).to(torch.int64).sum().item())
+outs = world.all_gather_object((bad.tolist(), chk, float(ref.abs().sum().item())))
+if R == 0:
+    print("RESULT " + json.dumps({"outs": outs, "multicast": mc, "iters": ITERS}))
+world.barrier()
+world.shutdown()
+'''
+
+
+@pytest.mark.skipif(NGPU < 2, reason="needs at least 2 GPUs")
+def test_fused_allreduce_stress_randomised_ranges_elementwise_vs_nccl():
+    """2,000 back-to-back launches of the fused all-reduce + optimizer kernel over random (offset, length, owner)
+    ranges — including n = 4, lengths that are not a multiple of world x 4 and the reduce-to-owner variant —
+    compared ELEMENT BY ELEMENT against NCCL all-reduce + the same SGD step. Gradients are small integers, so
+    the comparison is bit-exact whatever order the switch / the ring adds them in. This is the race check of
+    the epoch-flag barrier protocol (compute-sanitizer is closed on the pool)."""
+    script = ROOT / "build" / "_stress_worker.py"
+    script.parent.mkdir(exist_ok=True)
+    script.write_text(STRESS_WORKER % (str(ROOT), 2000))
+    n = min(NGPU, 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr",
+           "127.0.0.1", "--master-port", str(_free_port()), str(script)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-5000:]
+    res = json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][7:])
+    print(res)
+    for bad, chk, mag in res["outs"]:
+        assert bad[:3] == [0, 0, 0], f"mismatching elements (master, grad-not-zero, shadow): {bad}"
+        assert chk == res["outs"][0][1], "replicas differ"
+        assert mag > 0

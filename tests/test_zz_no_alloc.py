@@ -79,3 +79,42 @@ def test_noalloc_entry_point_refuses_oversized_ranges():
                                       C.c_ulonglong(1), L.stream())
     assert rc != 0
     assert b"exceeds the built-in staging area" in lib.idcb_last_error()
+
+
+def _call(lib, L, clients, out, k, stride, off, n, seed, stream=None):
+    return lib.idcb_secagg_mean_noalloc(C.c_void_p(clients.data_ptr()), C.c_void_p(out.data_ptr()), C.c_int(k),
+                                        C.c_longlong(stride), C.c_longlong(off), C.c_longlong(n), C.c_int(16),
+                                        C.c_ulonglong(seed), stream if stream is not None else L.stream())
+
+
+def test_noalloc_entry_point_at_its_size_limit_and_on_a_side_stream():
+    """The largest range the built-in staging area holds, launched on a stream that is not the default one
+    (the storage is per GPU, not per stream; the caller orders the calls)."""
+    L, lib = _lib()
+    n = lib.idcb_secagg_noalloc_max_elems()
+    torch.manual_seed(1)
+    clients = torch.randn(2, n, device="cuda")
+    want = _reference(L, lib, clients, 2, n, 0, n, 16, 77)
+    out = torch.zeros(n, dtype=torch.float32, device="cuda")
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        rc = _call(lib, L, clients, out, 2, n, 0, n, 77, C.c_void_p(side.cuda_stream))
+    assert rc == 0, lib.idcb_last_error().decode()
+    side.synchronize()
+    assert torch.equal(out, want)
+    assert (out - clients.mean(0)).abs().max().item() < 2e-5
+
+
+def test_noalloc_entry_point_checks_the_range_and_the_alignment():
+    L, lib = _lib()
+    x = torch.zeros(2, 64, device="cuda")
+    out = torch.zeros(64, device="cuda")
+    assert _call(lib, L, x, out, 2, 64, 32, 64, 1) != 0                 # offset + n > stride
+    assert b"does not fit in a client row" in lib.idcb_last_error()
+    assert _call(lib, L, x, out, 2, 64, -4, 8, 1) != 0                  # negative offset
+    rc = lib.idcb_secagg_mean_noalloc(C.c_void_p(x.data_ptr() + 4), C.c_void_p(out.data_ptr()), C.c_int(2),
+                                      C.c_longlong(60), C.c_longlong(0), C.c_longlong(8), C.c_int(16),
+                                      C.c_ulonglong(1), L.stream())
+    assert rc != 0 and b"16-byte aligned" in lib.idcb_last_error()
+    torch.cuda.synchronize()
