@@ -54,6 +54,9 @@ bool pdl_enabled();
 int make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols,
                       uint64_t row_pitch_elems, uint32_t box_rows, uint32_t box_cols);
 
+int make_tmap_im2col_bf16(CUtensorMap* map, const void* base, int B, int H, int W, int channels, int pitch,
+                          int KH, int KW, int stride, int pad_t, int pad_l, int Ho, int Wo, int pixels);
+
 #ifdef __CUDACC__
 // Launch with the programmatic-stream-serialization attribute (captured into CUDA graphs as a
 // programmatic dependency edge). Only for kernels that call pdl_wait() / pdl_enter().
@@ -213,6 +216,21 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
         ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)),
         "r"(c0), "r"(c1)
         : "memory");
+}
+
+// im2col tile load (tensor map from make_tmap_im2col_bf16): `pixels` output positions of one filter tap
+// starting at window origin (w, h) of image n, channels c .. c+63.
+__device__ __forceinline__ void tma_load_im2col(uint32_t smem_dst, const CUtensorMap* m, uint32_t bar, int c, int w,
+                                                int h, int n, int kw, int kh) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+        ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n),
+        "h"(static_cast<uint16_t>(kw)), "h"(static_cast<uint16_t>(kh))
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx_s(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
 
 // ---- tcgen05 / TMEM ---------------------------------------------------------------------------

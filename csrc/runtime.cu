@@ -88,6 +88,60 @@ int make_tmap_2d_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_
     return 0;
 }
 
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeIm2colFn get_im2col_fn() {
+    static EncodeIm2colFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeIm2colFn>(p);
+    });
+    return fn;
+}
+
+// im2col tensor map over an NHWC bf16 activation [B, H, W, pitch] (channel window of `channels` starting at
+// `base`): one cp.async.bulk.tensor.4d...im2col instruction then gathers `pixels` consecutive output positions
+// (raster order over w, h, n, with the convolution's stride) of ONE filter tap, 64 channels each, into a
+// 128-byte-swizzled [pixels][64] tile; positions whose input pixel falls into the zero padding, channels past
+// `channels` and images past B arrive as zeros.
+// Coordinates of a load: {first channel, wo*stride - pad_l, ho*stride - pad_t, image}, offsets {kw, kh}.
+int make_tmap_im2col_bf16(CUtensorMap* map, const void* base, int B, int H, int W, int channels, int pitch,
+                          int KH, int KW, int stride, int pad_t, int pad_l, int Ho, int Wo, int pixels) {
+    EncodeIm2colFn fn = get_im2col_fn();
+    IDCB_REQUIRE(fn != nullptr, "cuTensorMapEncodeIm2col entry point unavailable");
+    IDCB_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "TMA base must be 16-byte aligned");
+    IDCB_REQUIRE(pitch % 8 == 0 && stride >= 1 && stride <= 8 && pixels >= 1 && pixels <= 1024,
+                 "im2col tensor map: unsupported pitch/stride/box");
+    const int pad_b = (Ho - 1) * stride + KH - H - pad_t;     // implied far-side padding (may be negative)
+    const int pad_r = (Wo - 1) * stride + KW - W - pad_l;
+    int lower[2] = {-pad_l, -pad_t};                          // {W, H} order, like the dimensions after C
+    int upper[2] = {pad_r - (KW - 1), pad_b - (KH - 1)};
+    for (int i = 0; i < 2; ++i)
+        IDCB_REQUIRE(lower[i] >= -128 && lower[i] <= 127 && upper[i] >= -128 && upper[i] <= 127,
+                     "im2col tensor map: padding/kernel size out of the 8-bit corner range");
+    cuuint64_t gdim[4] = {(cuuint64_t)channels, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t gstride[3] = {(cuuint64_t)pitch * 2, (cuuint64_t)W * pitch * 2, (cuuint64_t)H * W * pitch * 2};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstride, lower, upper,
+                    64, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    IDCB_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeIm2col failed with CUresult %d", (int)r);
+    // Drivers up to 13.1 mis-encode im2col maps of tensors smaller than 128 KiB (one descriptor bit must be
+    // cleared; the same correction CUTLASS applies in cute/atom/copy_traits_sm90_im2col.hpp).
+    int drv = 0;
+    if (cudaDriverGetVersion(&drv) == cudaSuccess && drv <= 13010 &&
+        (unsigned long long)B * H * W * pitch * 2ull < 131072ull)
+        reinterpret_cast<unsigned long long*>(map)[1] &= ~(1ull << 21);
+    return 0;
+}
+
 }  // namespace idcb
 
 extern "C" const char* idcb_last_error(void) { return idcb::g_err; }

@@ -112,6 +112,11 @@ struct ConvArgs {
     // grid meets at a barrier (the accumulators stay in TMEM meanwhile), then each CTA turns its own dpre tile
     // into dx = s*(dpre - sa/N - xhat*dgamma/N) and the first row of CTAs emits dgamma / dbeta.
     // tail = 2 (frozen BN): dx = s * dpre, no barrier. Needs the whole grid co-resident (checked on the host).
+    // A operand through TMA im2col (one cp.async.bulk.tensor...im2col per k-block issued by one thread) instead
+    // of per-thread cp.async gathers. Possible when every 64-wide k-block lies inside one filter tap
+    // (single tap, or Cin a multiple of 64). Both operands are then written by the async proxy, so the plain path
+    // needs no generic->async fence at all; on the prologue path the transforming workers fence their own stores.
+    int a_tma;
     int tail;
     __nv_bfloat16* tail_out;
     int tail_pitch, tail_coff;
@@ -462,7 +467,8 @@ struct Gather {
 
 template <int kBN, bool kBMN, int kEpi>
 __global__ void __launch_bounds__(GemmCfg<kBMN>::kNT, (!kBMN || kEpi == 2 || kBN > 64) ? 1 : 2)
-conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ ConvArgs p) {
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_a,
+                 const __grid_constant__ ConvArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     using L = FwdSmem<kBN, kBMN>;
     using G = GemmCfg<kBMN>;
@@ -497,19 +503,23 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     if (threadIdx.x == 0) {
         for (int s = 0; s < nstages; ++s) {
             // transform path: one arrival per warp of the owning worker group; copy path: one per issuing thread; + TMA
-            mbar_init(&full_bar[s], has_pro ? kWork / 32 + 1 : G::kIssuers + 1);
+            // (with TMA im2col on the plain path one thread announces both operands' bytes)
+            mbar_init(&full_bar[s], has_pro ? kWork / 32 + 1 : (p.a_tma ? 1 : G::kIssuers + 1));
             mbar_init(&empty_bar[s], 1);  // one tcgen05.commit
         }
         mbar_init(acc_bar, 1);
         if (has_pro) {
             for (int s = 0; s < kRaw; ++s) {
-                mbar_init(&raw_full[s], G::kLoad);      // every loader thread's copies
+                mbar_init(&raw_full[s], p.a_tma ? 1 : G::kLoad);   // every loader thread's copies / one TMA issue
                 mbar_init(&raw_empty[s], kWork / 32);   // every warp of the group that owns the k-block has read it
             }
         }
         mbar_fence_init();
     }
-    if (warp == kTmaWarp && lane == 0) tma_prefetch_desc(&tmap_w);
+    if (warp == kTmaWarp && lane == 0) {
+        tma_prefetch_desc(&tmap_w);
+        if (p.a_tma) tma_prefetch_desc(&tmap_a);
+    }
     if (warp == kMmaWarp) tmem_alloc<kBN < 32 ? 32 : kBN>(tmem_slot);
     // everything above touched only this CTA's shared memory, TMEM and the kernel parameters; from here on
     // the kernel reads what its predecessors wrote
@@ -545,13 +555,30 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     if (threadIdx.x == 0) IDCB_STAMP(1);
+    // TMA im2col: window origin of the tile's first row; k-block kb = (tap kb / cblocks, channels 64 * (kb % cblocks))
+    int t_w = 0, t_h = 0, t_n = 0;
+    if (p.a_tma) {
+        t_n = fdiv(m0, p.d_hw);
+        const int rem = m0 - t_n * (p.Ho * p.Wo);
+        const int ho = fdiv(rem, p.d_wo);
+        t_h = ho * p.stride - p.pad_t;
+        t_w = (rem - ho * p.Wo) * p.stride - p.pad_l;
+    }
+    auto issue_a_tma = [&](uint32_t dst, uint32_t bar, int kb) {
+        const int tap = fdiv(kb, p.d_cb);
+        const int cb = kb - tap * cblocks;
+        const int kh = fdiv(tap, p.d_kw);
+        tma_load_im2col(dst, &tmap_a, bar, cb * kBK, t_w, t_h, t_n, tap - kh * p.KW, kh);
+    };
 
     if (warp < kWork / 32) {
         const int j = threadIdx.x & 7;       // 16-byte chunk inside the 128-byte row
         const int rbase = threadIdx.x >> 3;  // this thread owns tile rows rbase + 32 * i
         const uint32_t full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
         const uint32_t tile_off = sw128_offset(rbase, j);   // row i adds i * 4096 (raw slots use the same layout)
-        if (kBMN) {
+        if (kBMN && p.a_tma) {
+            // (dgrad, TMA im2col: the TMA warp feeds both operands; the workers go straight to the epilogue)
+        } else if (kBMN) {
             // ===================== dgrad: the workers issue the A copies =====================
             // The chunks land directly in the swizzled operand tile; the stage's "full" barrier hears from
             // every thread when its copies have completed. Nothing here waits for data, so up to `nstages`
@@ -628,7 +655,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                 const uint32_t a_dst = a_base + stage * kATileBytes;
 #pragma unroll
                 for (int i = 0; i < kGR; ++i) st_shared_v4(a_dst + i * (kGT * 16), v[i]);
-                // (the generic->async proxy fence for these stores is issued by the MMA thread after its wait)
+                // legacy path: the generic->async proxy fence for these stores is issued by the MMA thread after
+                // its wait; TMA path: every worker fences its own stores (they have nothing else in flight), which
+                // takes the fence off the single MMA thread's serial chain
+                if (p.a_tma) fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) {
                     mbar_arrive_s(full0 + stage * 8);
@@ -680,6 +710,25 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     } else if (warp < kTmaWarp) {
         // ===================== fprop loader warps: asynchronous copies only =====================
         const int lt = threadIdx.x - kWork;
+        if (p.a_tma) {
+            // one thread: raw activations of the prologue path into the raw ring (the plain path's A tiles are
+            // issued by the TMA warp together with the weights)
+            if (has_pro && lt == 0) {
+                const uint32_t raw0 = smem_u32(raw_tiles);
+                const uint32_t rfull0 = smem_u32(raw_full), rempty0 = smem_u32(raw_empty);
+                int slot = 0;
+                uint32_t rphase = 0;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    if (kb >= kRaw) mbar_wait_s(rempty0 + slot * 8, rphase ^ 1);
+                    mbar_arrive_expect_tx_s(rfull0 + slot * 8, kATileBytes);
+                    issue_a_tma(raw0 + slot * kRawBytes, rfull0 + slot * 8, kb);
+                    if (++slot == kRaw) {
+                        slot = 0;
+                        rphase ^= 1;
+                    }
+                }
+            }
+        } else {
         Gather<8, 16, kBMN> g;
         g.init(p, m0, lt);
         const uint32_t tile_off = sw128_offset(lt >> 3, lt & 7);   // row i adds i * 2048
@@ -712,6 +761,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                 }
             }
         }
+        }   // !a_tma
     } else if (warp == kTmaWarp) {
         // ===================== TMA producer for the weight operand =====================
         if (lane == 0) {
@@ -720,7 +770,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(&empty_bar[stage], phase ^ 1);
                 uint8_t* b_tile = b_tiles + stage * L::kBTileBytes;
-                mbar_arrive_expect_tx(&full_bar[stage], L::kBTileBytes);
+                const bool with_a = p.a_tma && !has_pro;
+                mbar_arrive_expect_tx(&full_bar[stage], L::kBTileBytes + (with_a ? kATileBytes : 0));
+                if (with_a) issue_a_tma(smem_u32(a_tiles + stage * kATileBytes), smem_u32(&full_bar[stage]), kb);
                 if (!kBMN) {
                     // K-major: rows = output channels, 64 linearised (tap, cin) K elements per row
                     tma_load_2d(b_tile, &tmap_w, &full_bar[stage], kb * kBK, n0);
@@ -752,7 +804,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                 // The producers' generic-proxy st.shared are ordered before this point by their release
                 // arrive; the generic->async proxy fence that must sit on that causality path is issued
                 // here, by the thread whose tcgen05.mma reads the tile (it has no loads in flight to drain).
-                fence_proxy_async_smem();
+                if (!p.a_tma) fence_proxy_async_smem();
                 tc_fence_after();
                 if (kb == 0) IDCB_STAMP(4);
                 const uint32_t a_addr = smem_u32(a_tiles + stage * kATileBytes);
@@ -1190,6 +1242,29 @@ static int pick_stages(int num_kb, bool has_pro, int stage_bytes, int other_byte
     return s < 1 ? 1 : s;
 }
 
+// IDCB_CONV_TMA=0 keeps the per-thread cp.async gathers for the activation operand (A/B measurements)
+static bool tma_a_enabled() {
+    static const int v = [] { const char* e = getenv("IDCB_CONV_TMA"); return e ? atoi(e) : 1; }();
+    return v != 0;
+}
+
+// Decide whether the activation operand of this fprop / dgrad launch can come through TMA im2col and, if so,
+// encode its tensor map (box = 128 output positions x 64 channels of one filter tap).
+static int prep_a_tma(CUtensorMap* tm, ConvArgs& a) {
+    a.a_tma = 0;
+    const int taps = a.KH * a.KW;
+    if (!tma_a_enabled() || !(taps == 1 || a.Cin % 64 == 0) || a.stride > 8) return 0;
+    const int pad_b = (a.Ho - 1) * a.stride + a.KH - a.H - a.pad_t, pad_r = (a.Wo - 1) * a.stride + a.KW - a.W - a.pad_l;
+    const int c[4] = {-a.pad_l, -a.pad_t, pad_r - (a.KW - 1), pad_b - (a.KH - 1)};
+    for (int i = 0; i < 4; ++i)
+        if (c[i] < -128 || c[i] > 127) return 0;
+    if (make_tmap_im2col_bf16(tm, a.x + a.x_coff, a.B, a.H, a.W, a.Cin, a.x_pitch, a.KH, a.KW, a.stride, a.pad_t,
+                              a.pad_l, a.Ho, a.Wo, kBM))
+        return 1;
+    a.a_tma = 1;
+    return 0;
+}
+
 template <int kBN, bool kBMN, int kEpi>
 static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     using L = FwdSmem<kBN, kBMN>;
@@ -1224,7 +1299,9 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
                      "conv_dgrad: a %u x %u grid with a BatchNorm tail cannot be co-resident", grid.x, grid.y);
     }
     a.dbg = g_dbg;
-    IDCB_CHECK(launch_pdl(kern, grid, dim3(GemmCfg<kBMN>::kNT), smem, st, tm, a));
+    CUtensorMap tma = tm;      // placeholder when the gather path is used
+    if (prep_a_tma(&tma, a)) return 1;
+    IDCB_CHECK(launch_pdl(kern, grid, dim3(GemmCfg<kBMN>::kNT), smem, st, tm, tma, a));
     return 0;
 }
 
