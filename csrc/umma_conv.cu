@@ -205,17 +205,46 @@ __device__ __forceinline__ void load_row_bf16(const __nv_bfloat16* rowptr, bool 
     }
 }
 
+// kW bf16 values held in registers as 16-byte groups -> float
+template <int kW>
+__device__ __forceinline__ void unpack_row_bf16(const uint4 (&q)[kW / 8], float (&out)[kW]) {
+#pragma unroll
+    for (int g = 0; g < kW / 8; ++g) {
+        const uint32_t w[4] = {q[g].x, q[g].y, q[g].z, q[g].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            out[g * 8 + 2 * e] = bf16_lo(w[e]);
+            out[g * 8 + 2 * e + 1] = bf16_hi(w[e]);
+        }
+    }
+}
+// the raw 16-byte groups of a bf16 row segment (zeros where n >= limit or the row is invalid); issued early so that
+// the global latency overlaps the main loop
+template <int kW>
+__device__ __forceinline__ void prefetch_row_bf16(const __nv_bfloat16* rowptr, bool rowvalid, int nb, int limit,
+                                                  uint4 (&q)[kW / 8]) {
+#pragma unroll
+    for (int g = 0; g < kW / 8; ++g) {
+        q[g] = make_uint4(0u, 0u, 0u, 0u);
+        if (rowvalid && nb + g * 8 < limit) q[g] = *reinterpret_cast<const uint4*>(rowptr + g * 8);
+    }
+}
+
 // One kW-column slab of the fused epilogue for the row owned by this thread.
 // es_scale / es_shift (mode 2): the consumer's forward scale/shift for this slab's columns, staged in shared
 // memory by the CTA (zero beyond Cout).
+// `auxq`: the slab's aux row segment, already in registers (kEpi 1 / 2: prefetched before the main loop ended).
 template <int kEpi, int kW>
 __device__ __forceinline__ void epilogue_slab(const ConvArgs& p, uint32_t taddr, int m, bool mvalid,
-                                              int nb, int lane, const float* es_scale, const float* es_shift) {
+                                              int nb, int lane, const float* es_scale, const float* es_shift,
+                                              const uint4 (&auxq)[kW / 8]) {
     float vv[kW];
     tmem_ld_cols<kW>(taddr, vv);
     float xr[kW];
     const bool need_aux = (kEpi != 0) || (p.aux != nullptr);
-    if (need_aux)
+    if (kEpi != 0)
+        unpack_row_bf16<kW>(auxq, xr);
+    else if (need_aux)
         load_row_bf16<kW>(p.aux + static_cast<size_t>(m) * p.aux_pitch + p.aux_coff + nb, mvalid, nb,
                           p.Cout, xr);
     if (kEpi == 0) {
@@ -315,11 +344,11 @@ __device__ __forceinline__ void epilogue_slab(const ConvArgs& p, uint32_t taddr,
 template <int kW>
 __device__ __forceinline__ void tail_slab(const ConvArgs& p, uint32_t taddr, int m, bool mvalid, int nb,
                                           const float* es_scale, const float* es_shift, const float* es_b,
-                                          const float* es_c) {
+                                          const float* es_c, const uint4 (&auxq)[kW / 8]) {
     float vv[kW];
     tmem_ld_cols<kW>(taddr, vv);
     float xr[kW];
-    load_row_bf16<kW>(p.aux + static_cast<size_t>(m) * p.aux_pitch + p.aux_coff + nb, mvalid, nb, p.Cout, xr);
+    unpack_row_bf16<kW>(auxq, xr);
     const int act = p.bwd_act;
     uint32_t packed[kW / 2];
 #pragma unroll
@@ -521,38 +550,44 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         if (p.a_tma) tma_prefetch_desc(&tmap_a);
     }
     if (warp == kMmaWarp) tmem_alloc<kBN < 32 ? 32 : kBN>(tmem_slot);
-    // everything above touched only this CTA's shared memory, TMEM and the kernel parameters; from here on
-    // the kernel reads what its predecessors wrote
-    pdl_wait();
-    if (threadIdx.x == 0) IDCB_STAMP(0);
-    if (p.bn_sum != nullptr) {
-        // BatchNorm finalised from the batch sums by every CTA for itself (the publication of the
-        // coefficients and the moving-statistics update happen at the very end of the kernel)
-        const float inv = 1.f / p.bn_count;
-        for (int c = threadIdx.x; c < p.Cin; c += kNT) {
-            const float mean = p.bn_sum[c] * inv;
-            const float var = fmaxf(p.bn_sq[c] * inv - mean * mean, 0.f);
-            const float sc = p.bn_gamma[c] * rsqrtf(var + p.bn_eps);
-            s_scale[c] = sc;
-            s_shift[c] = p.bn_beta[c] - mean * sc;
-        }
-    } else if (has_pro) {
-        for (int c = threadIdx.x; c < p.Cin; c += kNT) {
-            s_scale[c] = p.pro_scale[c];
-            s_shift[c] = p.pro_shift[c];
-        }
-    }
-    if (kEpi == 2) {
-        // the consumer's forward scale/shift for this CTA's columns (BN + activation backward in the epilogue)
-        for (int c = threadIdx.x; c < kBN; c += kNT) {
-            const bool nv = n0 + c < p.Cout;
-            s_scale[c] = nv ? p.bwd_scale[n0 + c] : 0.f;
-            s_shift[c] = nv ? p.bwd_shift[n0 + c] : 0.f;
-        }
-    }
+    // Everything above touched only this CTA's shared memory, TMEM and the kernel parameters, so it (and the
+    // CTA-wide barrier that publishes it) runs while the predecessor kernel is still finishing.
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    // from here on the kernel reads what its predecessors wrote
+    pdl_wait();
+    if (threadIdx.x == 0) IDCB_STAMP(0);
+    if (warp < kWork / 32) {
+        // Per-channel prologue / epilogue constants, staged by the worker warps only: the TMA, loader and MMA
+        // threads are already issuing the first operand loads while these global reads are in flight.
+        if (p.bn_sum != nullptr) {
+            // BatchNorm finalised from the batch sums by every CTA for itself (the publication of the
+            // coefficients and the moving-statistics update happen at the very end of the kernel)
+            const float inv = 1.f / p.bn_count;
+            for (int c = threadIdx.x; c < p.Cin; c += kWork) {
+                const float mean = p.bn_sum[c] * inv;
+                const float var = fmaxf(p.bn_sq[c] * inv - mean * mean, 0.f);
+                const float sc = p.bn_gamma[c] * rsqrtf(var + p.bn_eps);
+                s_scale[c] = sc;
+                s_shift[c] = p.bn_beta[c] - mean * sc;
+            }
+        } else if (has_pro) {
+            for (int c = threadIdx.x; c < p.Cin; c += kWork) {
+                s_scale[c] = p.pro_scale[c];
+                s_shift[c] = p.pro_shift[c];
+            }
+        }
+        if (kEpi == 2) {
+            // the consumer's forward scale/shift for this CTA's columns (BN + activation backward in the epilogue)
+            for (int c = threadIdx.x; c < kBN; c += kWork) {
+                const bool nv = n0 + c < p.Cout;
+                s_scale[c] = nv ? p.bwd_scale[n0 + c] : 0.f;
+                s_shift[c] = nv ? p.bwd_shift[n0 + c] : 0.f;
+            }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(kWork) : "memory");    // the workers among themselves
+    }
     const uint32_t tmem_base = *tmem_slot;
     if (threadIdx.x == 0) IDCB_STAMP(1);
     // TMA im2col: window origin of the tile's first row; k-block kb = (tap kb / cblocks, channels 64 * (kb % cblocks))
@@ -570,6 +605,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         const int kh = fdiv(tap, p.d_kw);
         tma_load_im2col(dst, &tmap_a, bar, cb * kBK, t_w, t_h, t_n, tap - kh * p.KW, kh);
     };
+
+    // epilogue geometry of a worker thread: warp w owns TMEM lanes 32*(w%4).. and column half w/4
+    constexpr int kHalf = kBN / 2;               // columns per warp
+    constexpr int kW = (kHalf >= 32 && (kBMN || kBN < 128)) ? 32 : 16;    // slab width (register budget)
+    constexpr int kSlabs = kHalf / kW;
+    const int quad = warp & 3;
+    const int half = (warp >> 2) & 1;
+    const int m = m0 + quad * 32 + lane;
+    const bool mvalid = m < p.M;
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+    uint4 auxq[kSlabs][kW / 8];      // modes 1 / 2: this thread's aux row (also reused by the BatchNorm tail pass)
 
     if (warp < kWork / 32) {
         const int j = threadIdx.x & 7;       // 16-byte chunk inside the 128-byte row
@@ -671,21 +717,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
 
         // ===================== epilogue =====================
         if (threadIdx.x == 0) IDCB_STAMP(3);
+        // the aux rows of modes 1 / 2 (ReLU mask source / raw activation) are fetched now, under the main loop
+        if (kEpi != 0) {
+#pragma unroll
+            for (int it = 0; it < kSlabs; ++it)
+                prefetch_row_bf16<kW>(p.aux + static_cast<size_t>(m) * p.aux_pitch + p.aux_coff + n0 + half * kHalf + it * kW,
+                                      mvalid, n0 + half * kHalf + it * kW, p.Cout, auxq[it]);
+        }
         mbar_wait(acc_bar, 0);
         tc_fence_after();
         if (threadIdx.x == 0) IDCB_STAMP(6);
-        constexpr int kHalf = kBN / 2;               // columns per warp
-        constexpr int kW = (kHalf >= 32 && (kBMN || kBN < 128)) ? 32 : 16;    // slab width (register budget)
-        const int quad = warp & 3;
-        const int half = warp >> 2;
-        const int m = m0 + quad * 32 + lane;
-        const bool mvalid = m < p.M;
-        const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-#pragma unroll 1
-        for (int cc = half * kHalf; cc < (half + 1) * kHalf; cc += kW) {
+#pragma unroll
+        for (int it = 0; it < kSlabs; ++it) {
+            const int cc = half * kHalf + it * kW;
             const int nb = n0 + cc;
-            if (nb >= p.Cout) break;  // warp-uniform
-            epilogue_slab<kEpi, kW>(p, t_row + cc, m, mvalid, nb, lane, s_scale + cc, s_shift + cc);
+            if (nb < p.Cout)   // warp-uniform
+                epilogue_slab<kEpi, kW>(p, t_row + cc, m, mvalid, nb, lane, s_scale + cc, s_shift + cc, auxq[it]);
         }
         tc_fence_before();
         // Publication of the BatchNorm coefficients for the backward pass + moving-statistics update: one CTA,
@@ -870,18 +917,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         __syncthreads();
         tc_fence_after();
         if (warp < kWork / 32) {
-            constexpr int kHalf = kBN / 2;
-            constexpr int kW = (kHalf >= 32 && (kBMN || kBN < 128)) ? 32 : 16;
-            const int quad = warp & 3;
-            const int half = warp >> 2;
-            const int m = m0 + quad * 32 + lane;
-            const bool mvalid = m < p.M;
-            const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-#pragma unroll 1
-            for (int cc = half * kHalf; cc < (half + 1) * kHalf; cc += kW) {
+#pragma unroll
+            for (int it = 0; it < kSlabs; ++it) {
+                const int cc = half * kHalf + it * kW;
                 const int nb = n0 + cc;
-                if (nb >= p.Cout) break;  // warp-uniform
-                tail_slab<kW>(p, t_row + cc, m, mvalid, nb, s_scale + cc, s_shift + cc, s_cb + cc, s_cc + cc);
+                if (nb < p.Cout)   // warp-uniform
+                    tail_slab<kW>(p, t_row + cc, m, mvalid, nb, s_scale + cc, s_shift + cc, s_cb + cc, s_cc + cc,
+                                  auxq[it]);
             }
             tc_fence_before();
         }
@@ -908,7 +950,8 @@ struct WgradArgs {
     const float* pro_scale;
     const float* pro_shift;
     int pro_act;
-    float* dw;  // fp32 [Cout][KH*KW*Cin], accumulated with red.add
+    float* dw;  // fp32 [Cout][KH*KW*Cin] (row pitch dw_pitch), accumulated with red.add
+    int dw_pitch;
     int splits;
     int kb_per_split;  // 64-position blocks per split
     int stages;
@@ -1146,7 +1189,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 #pragma unroll
                 for (int e = 0; e < kW; ++e) {
                     const int n = n0 + cc + e;
-                    if (n < p.Cout) atomicAdd(p.dw + static_cast<size_t>(n) * ktot + krow, vv[e]);
+                    if (n < p.Cout) atomicAdd(p.dw + static_cast<size_t>(n) * p.dw_pitch + krow, vv[e]);
                 }
             }
         }
@@ -1250,10 +1293,12 @@ static bool tma_a_enabled() {
 
 // Decide whether the activation operand of this fprop / dgrad launch can come through TMA im2col and, if so,
 // encode its tensor map (box = 128 output positions x 64 channels of one filter tap).
-static int prep_a_tma(CUtensorMap* tm, ConvArgs& a) {
+// `per_tap_blocks`: the kernel walks whole 64-wide channel blocks per tap (dgrad), so any channel count works —
+// TMA zero-fills the channels past Cin; fprop's linearised (tap, channel) K axis needs Cin % 64 == 0 or one tap.
+static int prep_a_tma(CUtensorMap* tm, ConvArgs& a, bool per_tap_blocks) {
     a.a_tma = 0;
     const int taps = a.KH * a.KW;
-    if (!tma_a_enabled() || !(taps == 1 || a.Cin % 64 == 0) || a.stride > 8) return 0;
+    if (!tma_a_enabled() || !(per_tap_blocks || taps == 1 || a.Cin % 64 == 0) || a.stride > 8) return 0;
     const int pad_b = (a.Ho - 1) * a.stride + a.KH - a.H - a.pad_t, pad_r = (a.Wo - 1) * a.stride + a.KW - a.W - a.pad_l;
     const int c[4] = {-a.pad_l, -a.pad_t, pad_r - (a.KW - 1), pad_b - (a.KH - 1)};
     for (int i = 0; i < 4; ++i)
@@ -1300,7 +1345,7 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     }
     a.dbg = g_dbg;
     CUtensorMap tma = tm;      // placeholder when the gather path is used
-    if (prep_a_tma(&tma, a)) return 1;
+    if (prep_a_tma(&tma, a, kBMN)) return 1;
     IDCB_CHECK(launch_pdl(kern, grid, dim3(GemmCfg<kBMN>::kNT), smem, st, tm, tma, a));
     return 0;
 }
@@ -1339,6 +1384,9 @@ static int check_geom(const idcb_conv_desc* d) {
                  "conv: pitches/offsets must be multiples of 8 channels");
     IDCB_REQUIRE(d->kh >= 1 && d->kw >= 1 && d->kh * d->kw <= 49, "conv: bad kernel size");
     IDCB_REQUIRE(d->stride >= 1, "conv: bad stride");
+    IDCB_REQUIRE(d->w_pitch >= 0 && d->w_off >= 0 && d->w_pitch % 8 == 0 && d->w_off % 8 == 0 &&
+                     (d->w_pitch == 0 || d->w_pitch >= d->kh * d->kw * d->cin),
+                 "conv: bad weight window (pitch %d, offset %d)", d->w_pitch, d->w_off);
     const long long m = 1LL * d->batch * d->ho * d->wo;
     IDCB_REQUIRE(m > 0 && m < (1LL << 30), "conv: bad problem size");
     return 0;
@@ -1397,8 +1445,9 @@ extern "C" int idcb_conv_fprop(const idcb_conv_desc* d, const void* x, const voi
     }
     CUtensorMap tm;
     const int kbn = pick_bn(a.M, d->cout);
-    if (make_tmap_2d_bf16(&tm, w, d->cout, (uint64_t)d->kh * d->kw * d->cin,
-                          (uint64_t)d->kh * d->kw * d->cin, kbn, 64))
+    const uint64_t wk = (uint64_t)d->kh * d->kw * d->cin;
+    if (make_tmap_2d_bf16(&tm, static_cast<const __nv_bfloat16*>(w) + d->w_off, d->cout, wk,
+                          d->w_pitch ? (uint64_t)d->w_pitch : wk, kbn, 64))
         return 1;
     if (kbn == 32) return launch_gemm<32, false, 0>(tm, a, st);
     if (kbn == 64) return launch_gemm<64, false, 0>(tm, a, st);
@@ -1466,8 +1515,9 @@ extern "C" int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const vo
     IDCB_REQUIRE(a.y != nullptr || a.gacc != nullptr || a.tail != 0, "conv_dgrad: no output given");
     CUtensorMap tm;
     // weight view [Cout rows][taps*Cin cols]; MN-major boxes are 64 cols x 64 rows
-    if (make_tmap_2d_bf16(&tm, w, d->cout, (uint64_t)d->kh * d->kw * d->cin,
-                          (uint64_t)d->kh * d->kw * d->cin, 64, 64))
+    const uint64_t wk = (uint64_t)d->kh * d->kw * d->cin;
+    if (make_tmap_2d_bf16(&tm, static_cast<const __nv_bfloat16*>(w) + d->w_off, d->cout, wk,
+                          d->w_pitch ? (uint64_t)d->w_pitch : wk, 64, 64))
         return 1;
     int rc;
     if (kbn == 32) {
@@ -1504,7 +1554,8 @@ extern "C" int idcb_conv_wgrad(const idcb_conv_desc* d, const void* x, const voi
     a.M = d->batch * d->ho * d->wo;
     a.Cout = d->cout;
     a.pro_scale = pro_scale; a.pro_shift = pro_shift; a.pro_act = pro_act;
-    a.dw = dw;
+    a.dw = dw + d->w_off;
+    a.dw_pitch = d->w_pitch ? d->w_pitch : d->kh * d->kw * d->cin;
     const int kbn = d->cout <= 32 ? 32 : (d->cout <= 64 ? 64 : 128);
     const int total_kb = ceil_div(a.M, 64);
     const int base_ctas = ceil_div(a.KH * a.KW * a.Cin, 128) * ceil_div(a.Cout, kbn);

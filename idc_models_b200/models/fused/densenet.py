@@ -100,6 +100,8 @@ class DenseNetExecutor(FusedExecutor):
                 dl.i_bn0, dl.i_c1, dl.i_bn1, dl.i_c2 = idx(n + "_0_bn"), idx(n + "_1_conv"), idx(n + "_1_bn"), idx(n + "_2_conv")
                 dl.g1 = OC.geom(h, w, dl.cin, 4 * GROWTH, 1)
                 dl.g2 = OC.geom(h, w, 4 * GROWTH, GROWTH, 3)
+                if h == 1 and w == 1:
+                    dl.g2 = OC.centre_tap(dl.g2)      # a 3x3 filter over one pixel: only its centre tap is ever used
                 dl.y1 = torch.zeros(batch, h, w, 4 * GROWTH, dtype=bf, device=dev)
                 dl.o_sum1, dl.o_sq1 = sc.reserve(4 * GROWTH), sc.reserve(4 * GROWTH)
                 dl.bwd = ft <= dl.i_c2

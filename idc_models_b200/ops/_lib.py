@@ -24,7 +24,7 @@ vp = C.c_void_p
 class ConvDesc(C.Structure):
     _fields_ = [(n, C.c_int) for n in (
         "batch", "h", "w", "cin", "ho", "wo", "cout", "kh", "kw", "stride", "pad_t", "pad_l",
-        "x_pitch", "x_coff", "y_pitch", "y_coff")]
+        "x_pitch", "x_coff", "y_pitch", "y_coff", "w_pitch", "w_off")]
 
 
 class ConvFused(C.Structure):

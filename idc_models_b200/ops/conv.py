@@ -36,6 +36,8 @@ class ConvGeom:
     pad_l: int
     pad_b: int
     pad_r: int
+    w_pitch: int = 0     # weight window (include/idcb200.h: idcb_conv_desc): row pitch / first element, 0 = dense
+    w_off: int = 0
 
     @property
     def ho(self) -> int:
@@ -66,7 +68,17 @@ def geom(h: int, w: int, cin: int, cout: int, k: int, stride: int = 1, padding="
 
 def _desc(g: ConvGeom, batch: int, x_pitch: int, x_coff: int, y_pitch: int, y_coff: int) -> _lib.ConvDesc:
     return _lib.ConvDesc(batch, g.h, g.w, g.cin, g.ho, g.wo, g.cout, g.kh, g.kw, g.stride, g.pad_t,
-                         g.pad_l, x_pitch, x_coff, y_pitch, y_coff)
+                         g.pad_l, x_pitch, x_coff, y_pitch, y_coff, g.w_pitch, g.w_off)
+
+
+def centre_tap(g: ConvGeom) -> ConvGeom:
+    """A k x k stride-1 SAME convolution whose input is a single pixel only ever multiplies its centre tap (every
+    other tap sees zero padding): the same result — forward, data gradient and weight gradient, the untouched
+    taps' gradients being exactly zero — comes from a 1x1 convolution over the window w[:, k//2, k//2, :] of the
+    weight tensor, with 1/k^2 of the MMA work."""
+    assert g.h == 1 and g.w == 1 and g.stride == 1 and g.kh == g.kw and g.pad_t == g.kh // 2 == g.pad_l
+    c = (g.kh // 2) * g.kw + g.kw // 2
+    return ConvGeom(1, 1, g.cin, g.cout, 1, 1, 1, 0, 0, 0, 0, w_pitch=g.kh * g.kw * g.cin, w_off=c * g.cin)
 
 
 def _chk(t: torch.Tensor, dtype, name: str) -> None:

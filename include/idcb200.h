@@ -43,6 +43,11 @@ typedef struct idcb_conv_desc {
                                     correct_pad asymmetry are expressed through these + ho/wo) */
     int x_pitch, x_coff;         /* addressing of the input  activation (or of dx in dgrad) */
     int y_pitch, y_coff;         /* addressing of the output activation (or of dy in dgrad/wgrad) */
+    int w_pitch, w_off;          /* weight window: elements between consecutive output-channel rows of the weight /
+                                    weight-gradient tensor (0 = kh*kw*cin, dense) and element offset of the first
+                                    weight used. Lets a kh x kw descriptor address a sub-window of a larger
+                                    filter: a 3x3 SAME convolution on a 1x1 image only ever touches its centre tap,
+                                    so it runs as a 1x1 convolution over w[:, 1, 1, :] (pitch 9*cin, offset 4*cin). */
 } idcb_conv_desc;
 
 /* Activation codes used by prologues/epilogues. */

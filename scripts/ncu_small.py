@@ -19,6 +19,7 @@ w1 = (torch.randn(128, 1, 1, cin, device=dev) * 0.05).to(torch.bfloat16)
 w3 = (torch.randn(32, 3, 3, 128, device=dev) * 0.05).to(torch.bfloat16)
 dy3 = torch.randn(b, h, h, 32, device=dev).to(torch.bfloat16)
 dy1 = torch.zeros(b, h, h, 128, device=dev, dtype=torch.bfloat16)
+dpre = torch.zeros_like(dy1)
 G = torch.zeros(b, h, h, 1024, device=dev)
 sc1, sh1 = torch.ones(cin, device=dev), torch.zeros(cin, device=dev)
 sc3, sh3 = torch.ones(128, device=dev), torch.zeros(128, device=dev)
@@ -32,7 +33,7 @@ for rep in range(2):
     C.conv_fprop_raw(g3, y1, w3, buf, y_coff=cin, pro_scale=sc3, pro_shift=sh3, pro_act=1, stat_sum=s[2][:32],
                      stat_sq=s[3][:32])
     ctr.zero_()
-    C.conv_dgrad_raw(g3, dy3, w3, None, dx_pitch=128, mode=2, aux=y1, bwd_scale=sc3, bwd_shift=sh3, bwd_act=1,
+    C.conv_dgrad_raw(g3, dy3, w3, dpre, mode=2, aux=y1, bwd_scale=sc3, bwd_shift=sh3, bwd_act=1,
                      stat_a=s[4][:128], stat_b=s[5][:128],
                      tail=C.bn_tail(dy1, mean, rstd, b * h * h, counter=ctr))
     C.conv_dgrad_raw(g1, dy1, w1, None, dx_pitch=1024, mode=2, aux=buf, bwd_scale=sc1, bwd_shift=sh1, bwd_act=1,

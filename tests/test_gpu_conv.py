@@ -354,3 +354,36 @@ def test_dgrad_mode2_with_batchnorm_tail(b, h, w, fused):
                      stat_a=sa, stat_b=sb, tail=tail)
     torch.cuda.synchronize()
     _close(out2, want_dpre * sc, 2e-2)
+
+
+def test_centre_tap_window_equals_the_full_3x3_on_one_pixel():
+    """A 3x3 SAME convolution over 1x1 images through the weight-window descriptor (1x1 over w[:, 1, 1, :]):
+    forward, data gradient and weight gradient equal the full 3x3 reference; the other taps' gradients stay zero."""
+    torch.manual_seed(14)
+    b, cin, cout = 128, 128, 32
+    g3 = C.geom(1, 1, cin, cout, 3)
+    g = C.centre_tap(g3)
+    x = _rand(b, 1, 1, cin)
+    wt = _rand(cout, 3, 3, cin, scale=cin ** -0.5)
+    y = torch.zeros(b, 1, 1, cout, device="cuda", dtype=torch.bfloat16)
+    sc = torch.rand(cin, device="cuda") + 0.5
+    sh = torch.randn(cin, device="cuda") * 0.3
+    C.conv_fprop_raw(g, x, wt, y, pro_scale=sc, pro_shift=sh, pro_act=C.ACT_RELU)
+    a = torch.relu(x.float() * sc + sh).to(torch.bfloat16).float()
+    want = C.conv_ref(g3, a, wt.float())
+    torch.cuda.synchronize()
+    _close(y, want)
+    dy = _rand(b, 1, 1, cout)
+    dx = torch.zeros(b, 1, 1, cin, device="cuda", dtype=torch.bfloat16)
+    C.conv_dgrad_raw(g, dy, wt, dx)
+    torch.cuda.synchronize()
+    _close(dx, _dgrad_ref(g3, dy, wt, (b, 1, 1, cin)))
+    dw = torch.zeros(cout, 3, 3, cin, device="cuda")
+    C.conv_wgrad_raw(g, x, dy, dw, pro_scale=sc, pro_shift=sh, pro_act=C.ACT_RELU)
+    torch.cuda.synchronize()
+    wref = torch.zeros(cout, 3, 3, cin, device="cuda", requires_grad=True)
+    (gw,) = torch.autograd.grad(C.conv_ref(g3, a, wref), wref, dy.float())
+    _close(dw, gw, 1e-2)
+    off = dw.clone()
+    off[:, 1, 1, :] = 0
+    assert off.abs().max().item() == 0
