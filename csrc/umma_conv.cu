@@ -117,6 +117,13 @@ struct ConvArgs {
     // (single tap, or Cin a multiple of 64). Both operands are then written by the async proxy, so the plain path
     // needs no generic->async fence at all; on the prologue path the transforming workers fence their own stores.
     int a_tma;
+    // fprop only: the K loop split over a thread-block cluster of `ksplit` CTAs along grid z (1 = off). CTA r of
+    // the cluster runs k-blocks [r * ceil(nkb / ksplit), ...); ranks > 0 push their fp32 partial tile into rank 0's
+    // shared memory (st.shared::cluster, buffer at byte offset red_off of the aligned dynamic shared memory,
+    // laid out [source][column group of 4][row][4 floats]); after a cluster barrier rank 0 adds them to its own
+    // accumulator in the ordinary epilogue. Small-M layers (DenseNet blocks 3-4: 1 to 9 row tiles) otherwise run
+    // their whole K loop, BatchNorm prologue included, on a handful of SMs.
+    int ksplit, red_off;
     int tail;
     __nv_bfloat16* tail_out;
     int tail_pitch, tail_coff;
@@ -237,9 +244,20 @@ __device__ __forceinline__ void prefetch_row_bf16(const __nv_bfloat16* rowptr, b
 template <int kEpi, int kW>
 __device__ __forceinline__ void epilogue_slab(const ConvArgs& p, uint32_t taddr, int m, bool mvalid,
                                               int nb, int lane, const float* es_scale, const float* es_shift,
-                                              const uint4 (&auxq)[kW / 8]) {
+                                              const uint4 (&auxq)[kW / 8], uint32_t red = 0u, int red_n = 0,
+                                              uint32_t red_stride = 0u) {
     float vv[kW];
     tmem_ld_cols<kW>(taddr, vv);
+    if (red != 0u) {
+        // K split over a cluster: add the partial tiles the other ranks pushed into this CTA's shared memory
+        for (int r = 0; r < red_n; ++r) {
+#pragma unroll
+            for (int g4 = 0; g4 < kW / 4; ++g4) {
+                const float4 t = ld_shared_f4(red + static_cast<uint32_t>(r) * red_stride + static_cast<uint32_t>(g4) * 2048u);
+                vv[g4 * 4 + 0] += t.x; vv[g4 * 4 + 1] += t.y; vv[g4 * 4 + 2] += t.z; vv[g4 * 4 + 3] += t.w;
+            }
+        }
+    }
     float xr[kW];
     const bool need_aux = (kEpi != 0) || (p.aux != nullptr);
     if (kEpi != 0)
@@ -414,7 +432,8 @@ struct Gather {
     uint32_t vlo[kR], vhi[kR];   // tap-validity bits 0..31 / 32..48
     int cur_c, cur_tap, cur_kw, cur_off, row_wrap, span;
 
-    __device__ __forceinline__ void init(const ConvArgs& p, int m0, int t) {
+    // kb_first: first k-block this CTA runs (fprop K split over a cluster; 0 otherwise)
+    __device__ __forceinline__ void init(const ConvArgs& p, int m0, int t, int kb_first = 0) {
         const int j = t & 7, rb = t >> 3;
 #pragma unroll
         for (int i = 0; i < kR; ++i) {
@@ -441,8 +460,9 @@ struct Gather {
             vlo[i] = static_cast<uint32_t>(vm);
             vhi[i] = static_cast<uint32_t>(vm >> 32);
         }
-        cur_tap = kBMN ? 0 : static_cast<int>(fdiv(j * 8, p.d_cin));
-        cur_c = j * 8 - cur_tap * p.Cin;
+        const int klin = (kBMN ? 0 : kb_first * kBK) + j * 8;
+        cur_tap = kBMN ? 0 : static_cast<int>(fdiv(klin, p.d_cin));
+        cur_c = klin - cur_tap * p.Cin;
         const int kh0 = fdiv(cur_tap, p.d_kw);
         cur_kw = cur_tap - kh0 * p.KW;
         cur_off = (kh0 * p.W + cur_kw) * p.x_pitch;
@@ -526,7 +546,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     const int taps = p.KH * p.KW;
     const int cblocks = (p.Cin + kBK - 1) / kBK;                 // dgrad: k-blocks per tap
     const int ktot = taps * p.Cin;                              // fprop: linearised K extent
-    const int num_kb = kBMN ? taps * cblocks : (ktot + kBK - 1) / kBK;
+    const int num_kb_total = kBMN ? taps * cblocks : (ktot + kBK - 1) / kBK;
+    // K split over the cluster (fprop): this CTA's k-blocks are [kb0, kb0 + num_kb) of the layer's
+    const int ksplit = kBMN ? 1 : p.ksplit;
+    const int krank = ksplit > 1 ? static_cast<int>(blockIdx.z) : 0;
+    const int kb_per = (num_kb_total + ksplit - 1) / ksplit;
+    const int kb0 = krank * kb_per;
+    const int num_kb = (kb0 + kb_per > num_kb_total ? num_kb_total : kb0 + kb_per) - kb0;   // >= 1 (host)
     pdl_launch_dependents();
 
     if (threadIdx.x == 0) {
@@ -561,11 +587,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     if (warp < kWork / 32) {
         // Per-channel prologue / epilogue constants, staged by the worker warps only: the TMA, loader and MMA
         // threads are already issuing the first operand loads while these global reads are in flight.
+        // a K-split CTA of a single-tap convolution only needs the channels of its own k-blocks (the CTA that
+        // publishes the coefficients at the end needs them all)
+        int c_lo = 0, c_hi = p.Cin;
+        if (ksplit > 1 && taps == 1 && !(blockIdx.x == 0 && blockIdx.y == 0 && krank == 0)) {
+            c_lo = kb0 * kBK;
+            c_hi = (kb0 + num_kb) * kBK < p.Cin ? (kb0 + num_kb) * kBK : p.Cin;
+        }
         if (p.bn_sum != nullptr) {
             // BatchNorm finalised from the batch sums by every CTA for itself (the publication of the
             // coefficients and the moving-statistics update happen at the very end of the kernel)
             const float inv = 1.f / p.bn_count;
-            for (int c = threadIdx.x; c < p.Cin; c += kWork) {
+            for (int c = c_lo + threadIdx.x; c < c_hi; c += kWork) {
                 const float mean = p.bn_sum[c] * inv;
                 const float var = fmaxf(p.bn_sq[c] * inv - mean * mean, 0.f);
                 const float sc = p.bn_gamma[c] * rsqrtf(var + p.bn_eps);
@@ -573,7 +606,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                 s_shift[c] = p.bn_beta[c] - mean * sc;
             }
         } else if (has_pro) {
-            for (int c = threadIdx.x; c < p.Cin; c += kWork) {
+            for (int c = c_lo + threadIdx.x; c < c_hi; c += kWork) {
                 s_scale[c] = p.pro_scale[c];
                 s_shift[c] = p.pro_shift[c];
             }
@@ -599,7 +632,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         t_h = ho * p.stride - p.pad_t;
         t_w = (rem - ho * p.Wo) * p.stride - p.pad_l;
     }
-    auto issue_a_tma = [&](uint32_t dst, uint32_t bar, int kb) {
+    auto issue_a_tma = [&](uint32_t dst, uint32_t bar, int kb_local) {
+        const int kb = kb0 + kb_local;
         const int tap = fdiv(kb, p.d_cb);
         const int cb = kb - tap * cblocks;
         const int kh = fdiv(tap, p.d_kw);
@@ -616,6 +650,40 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     const bool mvalid = m < p.M;
     const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
     uint4 auxq[kSlabs][kW / 8];      // modes 1 / 2: this thread's aux row (also reused by the BatchNorm tail pass)
+    const uint32_t trow = static_cast<uint32_t>(quad * 32 + lane);          // this thread's row of the tile
+    const uint32_t red_base = smem_u32(smem) + static_cast<uint32_t>(p.red_off);   // K-split partial tiles (rank 0)
+    auto run_epilogue = [&]() {
+        const uint32_t red = ksplit > 1 ? red_base + trow * 16u : 0u;
+#pragma unroll
+        for (int it = 0; it < kSlabs; ++it) {
+            const int cc = half * kHalf + it * kW;
+            const int nb = n0 + cc;
+            if (nb < p.Cout)   // warp-uniform
+                epilogue_slab<kEpi, kW>(p, t_row + cc, m, mvalid, nb, lane, s_scale + cc, s_shift + cc, auxq[it],
+                                        red != 0u ? red + static_cast<uint32_t>(cc / 4) * 2048u : 0u, ksplit - 1,
+                                        kBN * 512u);
+        }
+        tc_fence_before();
+        // Publication of the BatchNorm coefficients for the backward pass + moving-statistics update: one CTA,
+        // after everything latency-critical (global stores in flight would stall any later release/fence).
+        if (!kBMN && p.bn_sum != nullptr && blockIdx.x == 0 && blockIdx.y == 0) {
+            const float inv = 1.f / p.bn_count;
+            for (int c = threadIdx.x; c < p.Cin; c += kWork) {
+                const float mean = p.bn_sum[c] * inv;
+                const float var = fmaxf(p.bn_sq[c] * inv - mean * mean, 0.f);
+                const float rstd = rsqrtf(var + p.bn_eps);
+                p.bn_scale_out[c] = s_scale[c];
+                p.bn_shift_out[c] = s_shift[c];
+                p.bn_mean_out[c] = mean;
+                p.bn_rstd_out[c] = rstd;
+                if (p.bn_mmean != nullptr) {
+                    const float unbiased = p.bn_count > 1.f ? var * (p.bn_count / (p.bn_count - 1.f)) : var;
+                    p.bn_mmean[c] = p.bn_mmean[c] * p.bn_momentum + mean * (1.f - p.bn_momentum);
+                    p.bn_mvar[c] = p.bn_mvar[c] * p.bn_momentum + unbiased * (1.f - p.bn_momentum);
+                }
+            }
+        }
+    };
 
     if (warp < kWork / 32) {
         const int j = threadIdx.x & 7;       // 16-byte chunk inside the 128-byte row
@@ -654,7 +722,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             constexpr int kGroups = 1, kGT = kWork / kGroups, kGR = 1024 / kGT;   // (2 groups of 128 threads measured: no gain)
             const int grp = threadIdx.x / kGT, gt = threadIdx.x % kGT;
             Gather<kGR, kGT / 8, kBMN> g;   // used for its (tap, channel) cursor and padding masks only
-            g.init(p, m0, gt);
+            g.init(p, m0, gt, kb0);
             const uint32_t goff = sw128_offset(gt >> 3, gt & 7);   // row i adds i * kGT * 16
             const uint32_t a_base = smem_u32(a_tiles) + goff;
             const uint32_t raw_base = smem_u32(raw_tiles) + goff;
@@ -727,33 +795,24 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         mbar_wait(acc_bar, 0);
         tc_fence_after();
         if (threadIdx.x == 0) IDCB_STAMP(6);
+        if (krank != 0) {
+            // K split, rank > 0: the fp32 partial tile goes into rank 0's shared memory
+            const uint32_t dst0 = cluster_map_shared(red_base, 0) + static_cast<uint32_t>(krank - 1) * (kBN * 512u) + trow * 16u;
 #pragma unroll
-        for (int it = 0; it < kSlabs; ++it) {
-            const int cc = half * kHalf + it * kW;
-            const int nb = n0 + cc;
-            if (nb < p.Cout)   // warp-uniform
-                epilogue_slab<kEpi, kW>(p, t_row + cc, m, mvalid, nb, lane, s_scale + cc, s_shift + cc, auxq[it]);
-        }
-        tc_fence_before();
-        // Publication of the BatchNorm coefficients for the backward pass + moving-statistics update: one CTA,
-        // after everything latency-critical (global stores in flight would stall any later release/fence).
-        if (!kBMN && p.bn_sum != nullptr && blockIdx.x == 0 && blockIdx.y == 0) {
-            const float inv = 1.f / p.bn_count;
-            for (int c = threadIdx.x; c < p.Cin; c += kWork) {
-                const float mean = p.bn_sum[c] * inv;
-                const float var = fmaxf(p.bn_sq[c] * inv - mean * mean, 0.f);
-                const float rstd = rsqrtf(var + p.bn_eps);
-                p.bn_scale_out[c] = s_scale[c];
-                p.bn_shift_out[c] = s_shift[c];
-                p.bn_mean_out[c] = mean;
-                p.bn_rstd_out[c] = rstd;
-                if (p.bn_mmean != nullptr) {
-                    const float unbiased = p.bn_count > 1.f ? var * (p.bn_count / (p.bn_count - 1.f)) : var;
-                    p.bn_mmean[c] = p.bn_mmean[c] * p.bn_momentum + mean * (1.f - p.bn_momentum);
-                    p.bn_mvar[c] = p.bn_mvar[c] * p.bn_momentum + unbiased * (1.f - p.bn_momentum);
+            for (int it = 0; it < kSlabs; ++it) {
+                const int cc = half * kHalf + it * kW;
+                if (n0 + cc < p.Cout) {
+                    float vv[kW];
+                    tmem_ld_cols<kW>(t_row + cc, vv);
+#pragma unroll
+                    for (int g4 = 0; g4 < kW / 4; ++g4)
+                        st_cluster_f4(dst0 + static_cast<uint32_t>(cc / 4 + g4) * 2048u, vv[g4 * 4 + 0], vv[g4 * 4 + 1],
+                                      vv[g4 * 4 + 2], vv[g4 * 4 + 3]);
                 }
             }
+            tc_fence_before();
         }
+        // (the epilogue proper follows the role split: a K-split rank 0 first waits for its peers' partial tiles)
     } else if (warp < kTmaWarp) {
         // ===================== fprop loader warps: asynchronous copies only =====================
         const int lt = threadIdx.x - kWork;
@@ -777,7 +836,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             }
         } else {
         Gather<8, 16, kBMN> g;
-        g.init(p, m0, lt);
+        g.init(p, m0, lt, kb0);
         const uint32_t tile_off = sw128_offset(lt >> 3, lt & 7);   // row i adds i * 2048
         if (has_pro) {
             const uint32_t raw_base = smem_u32(raw_tiles) + tile_off;
@@ -822,7 +881,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
                 if (with_a) issue_a_tma(smem_u32(a_tiles + stage * kATileBytes), smem_u32(&full_bar[stage]), kb);
                 if (!kBMN) {
                     // K-major: rows = output channels, 64 linearised (tap, cin) K elements per row
-                    tma_load_2d(b_tile, &tmap_w, &full_bar[stage], kb * kBK, n0);
+                    tma_load_2d(b_tile, &tmap_w, &full_bar[stage], (kb0 + kb) * kBK, n0);
                 } else {
                     // MN-major: rows = K (the original Cout), 64 N elements per row, per 64-wide chunk
                     const int tap = kb / cblocks;
@@ -875,6 +934,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         __syncwarp();
     }
     if (threadIdx.x == 0) IDCB_STAMP(7);
+    if (ksplit > 1) {
+        // every thread of every CTA of the cluster: the partial tiles are in rank 0's shared memory after this
+        cluster_arrive_release();
+        cluster_wait_acquire();
+    }
+    if (krank == 0 && warp < kWork / 32) run_epilogue();
     __syncthreads();
     if (threadIdx.x == 0) IDCB_STAMP(8);
     if (kEpi == 2 && p.tail != 0) {
@@ -1285,6 +1350,12 @@ static int pick_stages(int num_kb, bool has_pro, int stage_bytes, int other_byte
     return s < 1 ? 1 : s;
 }
 
+// IDCB_CONV_KSPLIT=0 turns the cluster K split of small fprop launches off (A/B measurements)
+static bool ksplit_enabled() {
+    static const int v = [] { const char* e = getenv("IDCB_CONV_KSPLIT"); return e ? atoi(e) : 1; }();
+    return v != 0;
+}
+
 // IDCB_CONV_TMA=0 keeps the per-thread cp.async gathers for the activation operand (A/B measurements)
 static bool tma_a_enabled() {
     static const int v = [] { const char* e = getenv("IDCB_CONV_TMA"); return e ? atoi(e) : 1; }();
@@ -1318,9 +1389,25 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     const int extra = kBarBytes + 2 * (int)sizeof(float) * ((a.Cin > 128 ? a.Cin : 128) + 4) + 64 +
                       (kEpi == 2 ? 1024 : 0);   // mode 2 with a BatchNorm tail: two more 128-float tables
     const bool has_pro = !kBMN && (a.pro_scale != nullptr || a.bn_sum != nullptr);
-    a.stages = pick_stages(num_kb, has_pro, L::kStageBytes, 1024 + (has_pro ? kRaw * kRawBytes : 0) + extra,
+    // K split over a cluster (fprop of layers with few tiles): as many ranks as keep the grid within the SM count
+    // and leave every rank enough k-blocks to pay for the cluster launch, the partial-tile push and the barrier
+    int ksplit = 1;
+    if (!kBMN && ksplit_enabled()) {
+        const long long tiles = 1LL * ceil_div(a.M, kBM) * ceil_div(a.Cout, kBN);
+        static const int min_kb = [] { const char* e = getenv("IDCB_CONV_KSPLIT_MINKB"); int v = e ? atoi(e) : 4; return v > 0 ? v : 4; }();
+        for (int cand = 4; cand >= 2; cand /= 2)
+            if (tiles * cand <= num_sms() && num_kb >= min_kb * cand && (cand - 1) * ceil_div(num_kb, cand) < num_kb) {
+                ksplit = cand;
+                break;
+            }
+    }
+    const int red_bytes = ksplit > 1 ? (ksplit - 1) * kBN * 512 : 0;
+    a.ksplit = ksplit;
+    a.stages = pick_stages(ceil_div(num_kb, ksplit), has_pro, L::kStageBytes,
+                           1024 + (has_pro ? kRaw * kRawBytes : 0) + extra + red_bytes + 16,
                            kBMN ? 1LL * ceil_div(a.M, kBM) * ceil_div(a.Cout, kBN) : 0);
-    const size_t smem = 1024 + a.stages * L::kStageBytes + (has_pro ? kRaw * kRawBytes : 0) + extra;
+    a.red_off = (a.stages * L::kStageBytes + (has_pro ? kRaw * kRawBytes : 0) + extra + 15) & ~15;
+    const size_t smem = 1024 + a.red_off + red_bytes;
     IDCB_REQUIRE(smem <= 227 * 1024, "conv: Cin=%d needs %zu bytes of shared memory", a.Cin, smem);
     IDCB_REQUIRE(1LL * a.B * a.H * a.W * a.x_pitch < (1LL << 31), "conv: input tensor too large for 32-bit offsets");
     a.d_hw = make_fdiv(a.Ho * a.Wo);
@@ -1336,7 +1423,7 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
                                         227 * 1024));
         attr_set[dev] = true;
     }
-    dim3 grid(ceil_div(a.M, kBM), ceil_div(a.Cout, kBN), 1);
+    dim3 grid(ceil_div(a.M, kBM), ceil_div(a.Cout, kBN), ksplit);
     if (kEpi == 2 && a.tail == 1) {
         int per_sm = 0;
         IDCB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, GemmCfg<kBMN>::kNT, smem));
@@ -1346,7 +1433,7 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     a.dbg = g_dbg;
     CUtensorMap tma = tm;      // placeholder when the gather path is used
     if (prep_a_tma(&tma, a, kBMN)) return 1;
-    IDCB_CHECK(launch_pdl(kern, grid, dim3(GemmCfg<kBMN>::kNT), smem, st, tm, tma, a));
+    IDCB_CHECK(launch_pdl_cluster(kern, grid, dim3(GemmCfg<kBMN>::kNT), smem, st, ksplit, tm, tma, a));
     return 0;
 }
 
