@@ -133,6 +133,18 @@ struct ConvArgs {
     float* tail_dgamma;
     float* tail_dbeta;
     unsigned int* tail_counter;   // zero at launch
+    // tail = 3 (DenseNet block buffer; mode 2 accumulating into G, N tile = 32): besides the BatchNorm in front of
+    // THIS convolution (tail_mean / tail_rstd / tail_dgamma / tail_dbeta describe it), the gradient of the 32
+    // buffer channels [sl_c0, sl_c0 + 32) — the slice the next-lower layer produced — is final once this kernel's
+    // reductions have landed. After a grid barrier the CTAs of that N tile read G back, fold this BatchNorm's share
+    // of the batch-statistics correction into S1 / S2 on the fly and write the slice gradient
+    //   dy = G - S1/N - xhat * S2/N   (bf16, to tail_out),
+    // and one of them does the bookkeeping idcb_bn_bwd_coeffs would do (dgamma, dbeta, S1/S2 of the other channels).
+    float* sl_acc_s1;
+    float* sl_acc_s2;
+    const float* sl_mean;         // the block buffer's batch statistics, indexed by block channel
+    const float* sl_rstd;
+    int sl_c0;
 };
 
 #define IDCB_STAMP(i)                                                                     \
@@ -394,6 +406,31 @@ __device__ __forceinline__ void tail_slab(const ConvArgs& p, uint32_t taddr, int
     }
 }
 
+// tail = 3: the finished gradient of a block-buffer slice for the row owned by this thread:
+// out = G + B*x + C (G read back from L2; x = the raw buffer row, already in registers)
+template <int kW>
+__device__ __forceinline__ void slice_slab(const ConvArgs& p, int m, bool mvalid, int nb, const float* es_b,
+                                           const float* es_c, const uint4 (&auxq)[kW / 8]) {
+    if (!mvalid) return;
+    float xr[kW];
+    unpack_row_bf16<kW>(auxq, xr);
+    const float* grow = p.gacc + static_cast<size_t>(m) * p.g_pitch + p.g_coff + nb;
+    uint32_t packed[kW / 2];
+#pragma unroll
+    for (int g4 = 0; g4 < kW / 4; ++g4) {
+        const float4 g = __ldcg(reinterpret_cast<const float4*>(grow + g4 * 4));
+        const float4 cb = *reinterpret_cast<const float4*>(es_b + g4 * 4);
+        const float4 cc = *reinterpret_cast<const float4*>(es_c + g4 * 4);
+        packed[g4 * 2 + 0] = pack_bf16x2(g.x + fmaf(cb.x, xr[g4 * 4 + 0], cc.x), g.y + fmaf(cb.y, xr[g4 * 4 + 1], cc.y));
+        packed[g4 * 2 + 1] = pack_bf16x2(g.z + fmaf(cb.z, xr[g4 * 4 + 2], cc.z), g.w + fmaf(cb.w, xr[g4 * 4 + 3], cc.w));
+    }
+    __nv_bfloat16* orow = p.tail_out + static_cast<size_t>(m) * p.tail_pitch + p.tail_coff + (nb - p.sl_c0);
+#pragma unroll
+    for (int g = 0; g < kW / 8; ++g)
+        *reinterpret_cast<uint4*>(orow + g * 8) =
+            make_uint4(packed[4 * g], packed[4 * g + 1], packed[4 * g + 2], packed[4 * g + 3]);
+}
+
 template <int kBN, bool kBMN>
 struct FwdSmem {
     static constexpr int kBTileBytes = kBMN ? ((kBN + 63) / 64) * 8192 : kBN * 128;
@@ -515,7 +552,7 @@ struct Gather {
 };
 
 template <int kBN, bool kBMN, int kEpi>
-__global__ void __launch_bounds__(GemmCfg<kBMN>::kNT, (!kBMN || kEpi == 2 || kBN > 64) ? 1 : 2)
+__global__ void __launch_bounds__(GemmCfg<kBMN>::kNT, (!kBMN || kBN > 64 || (kEpi == 2 && kBN > 32)) ? 1 : 2)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_a,
                  const __grid_constant__ ConvArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -942,7 +979,60 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     if (krank == 0 && warp < kWork / 32) run_epilogue();
     __syncthreads();
     if (threadIdx.x == 0) IDCB_STAMP(8);
-    if (kEpi == 2 && p.tail != 0) {
+    if (kEpi == 2 && kBN == 32 && p.tail == 3) {
+        float* s_cb = s_scale + 256;
+        float* s_cc = s_scale + 384;
+        // every CTA: its G reductions and column sums (issued before the __syncthreads above) are published and it
+        // is counted; only the CTAs of the slice's N tile wait for the rest of the grid
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(p.tail_counter, 1u);
+        }
+        if (n0 == p.sl_c0) {
+            if (threadIdx.x == 0) {
+                const unsigned int total = gridDim.x * gridDim.y;
+                unsigned int seen;
+                long long t0 = clock64();
+                do {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.tail_counter) : "memory");
+                    if (seen < total && clock64() - t0 > 8000000000LL) __trap();   // a grid that is not co-resident
+                } while (seen < total);
+            }
+            __syncthreads();
+            const float invn = 1.f / p.tail_count;
+            if (threadIdx.x < kBN) {
+                const int c = threadIdx.x, n = n0 + c;
+                const float a = __ldcg(p.stat_a + n), b = __ldcg(p.stat_b + n), sc = s_scale[c];
+                const float dg = p.tail_rstd[n] * (b - p.tail_mean[n] * a);
+                const float s1 = __ldcg(p.sl_acc_s1 + n) + sc * a, s2 = __ldcg(p.sl_acc_s2 + n) + sc * dg;
+                const float rt = p.sl_rstd[n], mt = p.sl_mean[n];
+                s_cb[c] = -rt * s2 * invn;
+                s_cc[c] = -s1 * invn + rt * mt * s2 * invn;
+            }
+            if (blockIdx.x == 0) {
+                // this BatchNorm's parameter gradients and its S1 / S2 share for every channel outside the slice
+                for (int pc = threadIdx.x; pc < p.Cout; pc += kNT) {
+                    const float a = __ldcg(p.stat_a + pc), b = __ldcg(p.stat_b + pc), sc = p.bwd_scale[pc];
+                    const float dg = p.tail_rstd[pc] * (b - p.tail_mean[pc] * a);
+                    if (p.tail_dgamma != nullptr) p.tail_dgamma[pc] += dg;
+                    if (p.tail_dbeta != nullptr) p.tail_dbeta[pc] += a;
+                    if (pc < p.sl_c0 || pc >= p.sl_c0 + kBN) {
+                        p.sl_acc_s1[pc] += sc * a;
+                        p.sl_acc_s2[pc] += sc * dg;
+                    }
+                }
+            }
+            __syncthreads();
+            if (warp < kWork / 32) {
+#pragma unroll
+                for (int it = 0; it < kSlabs; ++it) {
+                    const int cc = half * kHalf + it * kW;
+                    slice_slab<kW>(p, m, mvalid, n0 + cc, s_cb + cc, s_cc + cc, auxq[it]);
+                }
+            }
+            __syncthreads();
+        }
+    } else if (kEpi == 2 && p.tail != 0) {
         float* s_cb = s_scale + 256;
         float* s_cc = s_scale + 384;
         if (p.tail == 1) {
@@ -1421,14 +1511,30 @@ static int launch_gemm(const CUtensorMap& tm, ConvArgs& a, cudaStream_t st) {
     if (!attr_set[dev]) {
         IDCB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         227 * 1024));
+        // the whole unified array as shared memory: these kernels do not use L1, and co-residency of several
+        // small-tile CTAs per SM (what the grid-barrier tails rely on) must not depend on the carve-out the
+        // driver would otherwise pick per launch
+        IDCB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        cudaSharedmemCarveoutMaxShared));
         attr_set[dev] = true;
     }
     dim3 grid(ceil_div(a.M, kBM), ceil_div(a.Cout, kBN), ksplit);
-    if (kEpi == 2 && a.tail == 1) {
-        int per_sm = 0;
-        IDCB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, GemmCfg<kBMN>::kNT, smem));
+    if (kEpi == 2 && (a.tail == 1 || a.tail == 3)) {
+        // CTAs of this launch that fit on one SM at the same time. Computed from the kernel's own resource use
+        // (registers in 512-register warp granules out of 64 K, shared memory incl. the 1 KiB the driver reserves per
+        // CTA out of 228 KiB, 2048 threads): cudaOccupancyMaxActiveBlocksPerMultiprocessor answers for the carve-out
+        // it assumes rather than the one the launch gets, and reported 1 where ncu shows 2 resident CTAs.
+        cudaFuncAttributes fa;
+        IDCB_CHECK(cudaFuncGetAttributes(&fa, kern));
+        const int threads = GemmCfg<kBMN>::kNT;
+        const int regs_per_cta = ((fa.numRegs * 32 + 511) / 512) * 512 * (threads / 32);
+        int per_sm = 65536 / (regs_per_cta > 0 ? regs_per_cta : 1);
+        const int by_smem = static_cast<int>((228 * 1024) / (smem + fa.sharedSizeBytes + 1024));
+        if (by_smem < per_sm) per_sm = by_smem;
+        if (2048 / threads < per_sm) per_sm = 2048 / threads;
         IDCB_REQUIRE(static_cast<long long>(grid.x) * grid.y <= static_cast<long long>(per_sm) * num_sms(),
-                     "conv_dgrad: a %u x %u grid with a BatchNorm tail cannot be co-resident", grid.x, grid.y);
+                     "conv_dgrad: a %u x %u grid with a grid-barrier tail cannot be co-resident (%d CTAs of %zu bytes per SM)",
+                     grid.x, grid.y, per_sm, smem);
     }
     a.dbg = g_dbg;
     CUtensorMap tma = tm;      // placeholder when the gather path is used
@@ -1577,7 +1683,7 @@ extern "C" int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const vo
         IDCB_REQUIRE(f->gacc == nullptr || (f->g_pitch % 4 == 0 && f->g_coff % 4 == 0),
                      "conv_dgrad: G pitch/offset must be multiples of 4");
     }
-    const int kbn = pick_bn(a.M, d->cin);
+    int kbn = pick_bn(a.M, d->cin);
     bool split_tail = false;
     if (f && f->tail != nullptr) {
         const idcb_bn_tail* t = f->tail;
@@ -1598,6 +1704,22 @@ extern "C" int idcb_conv_dgrad(const idcb_conv_desc* d, const void* dy, const vo
             IDCB_REQUIRE(a.y != nullptr, "conv_dgrad: the tail does not fit on the device and no dx buffer was given");
             split_tail = true;
         }
+    }
+    if (f && f->slice != nullptr) {
+        const idcb_slice_tail* t = f->slice;
+        IDCB_REQUIRE(mode == 2 && a.gacc && a.stat_a && a.stat_b && a.tail == 0 && !split_tail && a.g_coff == 0,
+                     "conv_dgrad: a slice tail needs mode 2 into G (channel offset 0), both column sums and no BatchNorm tail");
+        IDCB_REQUIRE(t->out && t->acc_s1 && t->acc_s2 && t->mean && t->rstd && t->bn_mean && t->bn_rstd && t->counter &&
+                         t->count > 0.f && t->out_pitch % 8 == 0 && t->out_coff % 8 == 0,
+                     "conv_dgrad: incomplete slice tail");
+        IDCB_REQUIRE(t->c0 % 32 == 0 && t->c0 + 32 <= d->cin, "conv_dgrad: the slice must be one 32-channel N tile inside the output");
+        kbn = 32;
+        a.tail = 3;
+        a.tail_out = static_cast<__nv_bfloat16*>(t->out);
+        a.tail_pitch = t->out_pitch; a.tail_coff = t->out_coff;
+        a.tail_mean = t->bn_mean; a.tail_rstd = t->bn_rstd; a.tail_count = t->count;
+        a.tail_dgamma = t->dgamma; a.tail_dbeta = t->dbeta; a.tail_counter = t->counter;
+        a.sl_acc_s1 = t->acc_s1; a.sl_acc_s2 = t->acc_s2; a.sl_mean = t->mean; a.sl_rstd = t->rstd; a.sl_c0 = t->c0;
     }
     IDCB_REQUIRE(a.y != nullptr || a.gacc != nullptr || a.tail != 0, "conv_dgrad: no output given");
     CUtensorMap tm;

@@ -106,6 +106,8 @@ class DenseNetExecutor(FusedExecutor):
                 dl.o_sum1, dl.o_sq1 = sc.reserve(4 * GROWTH), sc.reserve(4 * GROWTH)
                 dl.bwd = ft <= dl.i_c2
                 dl.o_ctr = sc.reserve(64) if dl.bwd else None     # grid-barrier word of the dgrad + BN-tail launch
+                dl.o_ctr2 = sc.reserve(64) if dl.bwd else None    # ... and of the 1x1 dgrad + slice-tail launch
+                dl.li = li
                 dl.bn0 = BNState(self, n + "_0_bn", dl.cin, sc, dl.bwd and ft <= dl.i_bn0)
                 dl.bn1 = BNState(self, n + "_1_bn", 4 * GROWTH, sc, dl.bwd and ft <= dl.i_bn1)
                 blk.layers.append(dl)
@@ -119,7 +121,9 @@ class DenseNetExecutor(FusedExecutor):
             if blk.needG:
                 blk.G = torch.zeros(batch, h, w, blk.ctot, dtype=torch.float32, device=dev)
                 blk.o_s1, blk.o_s2 = sc.reserve(blk.ctot), sc.reserve(blk.ctot)
-                blk.dy3 = torch.zeros(batch, h, w, GROWTH, dtype=bf, device=dev)
+                # two copies: a layer's slice gradient may be written (by the layer above's 1x1 dgrad) while the
+                # previous layer's weight-gradient kernel is still reading its own on the side stream
+                blk.dy3 = [torch.zeros(batch, h, w, GROWTH, dtype=bf, device=dev) for _ in range(2)]
                 blk.dpre1 = torch.zeros(batch, h, w, 4 * GROWTH, dtype=bf, device=dev)
                 blk.dy1 = torch.zeros(batch, h, w, 4 * GROWTH, dtype=bf, device=dev)
                 blk.cA = torch.zeros(blk.ctot, device=dev)
@@ -284,6 +288,8 @@ class DenseNetExecutor(FusedExecutor):
     wgrad_side_stream = True
     # finish BN1's backward inside the 3x3 dgrad launch (IDCB_BN_TAIL=0: separate bn_bwd_apply launch)
     bn_tail = os.environ.get("IDCB_BN_TAIL", "1") != "0"
+    # produce the next-lower layer's slice gradient inside the 1x1 dgrad launch (IDCB_SLICE_TAIL=0: own launch)
+    slice_tail = os.environ.get("IDCB_SLICE_TAIL", "1") != "0"
 
     def _wgrad(self, *args, **kw) -> None:
         if not self.wgrad_side_stream:
@@ -341,14 +347,18 @@ class DenseNetExecutor(FusedExecutor):
                         self._consumer_bn_backward(blk, blk.bn_t)
             if not blk.needG:
                 break
+            slice_done = False      # this layer's slice gradient already came out of the 1x1 dgrad of the layer above
             for dl in reversed(blk.layers):
                 if not dl.bwd:
                     break
-                self._wgrad_join()          # the previous layer's wgrads still read dy3 / dy1
-                self._finalize_slice(blk, dl.cin, GROWTH, blk.dy3)
+                self._wgrad_join()          # the previous layer's wgrads still read dy1 (and the other dy3 copy)
+                dy3 = blk.dy3[dl.li & 1]
+                if not slice_done:
+                    self._finalize_slice(blk, dl.cin, GROWTH, dy3)
+                slice_done = False
                 w2 = dl.name + "_2_conv/kernel"
                 if dl.i_c2 in tr:
-                    self._wgrad(dl.g2, dl.y1, blk.dy3, self.gw(w2), pro_scale=dl.bn1.scale,
+                    self._wgrad(dl.g2, dl.y1, dy3, self.gw(w2), pro_scale=dl.bn1.scale,
                                       pro_shift=dl.bn1.shift, pro_act=ACT_RELU)
                 if ft > dl.i_bn1:
                     continue
@@ -360,7 +370,7 @@ class DenseNetExecutor(FusedExecutor):
                 if self.bn_tail and ft <= dl.i_c1:
                     tail = OC.bn_tail(blk.dy1, bn1.mean, bn1.rstd, blk.count, counter=sc.view(dl.o_ctr, 1),
                                       dgamma=bn1.dgamma, dbeta=bn1.dbeta, frozen=not bn1.trainable)
-                OC.conv_dgrad_raw(dl.g2, blk.dy3, self.w16(w2), blk.dpre1, mode=2, aux=dl.y1,
+                OC.conv_dgrad_raw(dl.g2, dy3, self.w16(w2), blk.dpre1, mode=2, aux=dl.y1,
                                   bwd_scale=bn1.scale, bwd_shift=bn1.shift, bwd_act=ACT_RELU,
                                   stat_a=bn1.sa, stat_b=bn1.sb, tail=tail)
                 if ft > dl.i_c1:
@@ -380,10 +390,23 @@ class DenseNetExecutor(FusedExecutor):
                                       pro_shift=bn0.shift, pro_act=ACT_RELU)
                 if ft > dl.i_bn0:
                     continue
+                # The layer below produced buffer channels [cin - 32, cin): this dgrad is their last writer, so their
+                # finished gradient (and this BatchNorm's bookkeeping) comes out of the same launch.
+                below = blk.layers[dl.li - 1] if dl.li > 0 else None
+                st = None
+                if (self.slice_tail and below is not None and below.bwd and bn0.trainable
+                        and OC.slice_tail_fits(blk.buf.numel() // blk.ctot, dl.cin)):
+                    self._flush_pending()
+                    st = OC.slice_tail(blk.dy3[below.li & 1], below.cin, sc.view(blk.o_s1, blk.ctot),
+                                       sc.view(blk.o_s2, blk.ctot), blk.bn_t.mean, blk.bn_t.rstd, bn0.mean, bn0.rstd,
+                                       blk.count, sc.view(dl.o_ctr2, 1), dgamma=bn0.dgamma, dbeta=bn0.dbeta)
                 OC.conv_dgrad_raw(dl.g1, blk.dy1, self.w16(w1), None, dx_pitch=blk.ctot, mode=2, aux=blk.buf,
                                   bwd_scale=bn0.scale, bwd_shift=bn0.shift, bwd_act=ACT_RELU, gacc=blk.G,
-                                  stat_a=bn0.sa, stat_b=bn0.sb)
-                self._consumer_bn_backward(blk, bn0)
+                                  stat_a=bn0.sa, stat_b=bn0.sb, slice_tail=st)
+                if st is not None:
+                    slice_done = True
+                else:
+                    self._consumer_bn_backward(blk, bn0)
             self._wgrad_join()
             self._flush_pending()       # the block's first BatchNorm: its gradients are part of the announcement
             self.grads_ready(self._block_offsets[bi])

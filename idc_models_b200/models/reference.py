@@ -44,8 +44,9 @@ class RefExecutor:
         return t
 
     def forward(self, x: torch.Tensor, training: bool, upto: str | None = None,
-                generator: torch.Generator | None = None) -> torch.Tensor:
-        """x: [B, H, W, C] float32 in [0,1]. Returns the output of the last layer (or of ``upto``)."""
+                generator: torch.Generator | None = None, capture: dict | None = None) -> torch.Tensor:
+        """x: [B, H, W, C] float32 in [0,1]. Returns the output of the last layer (or of ``upto``).
+        ``capture``: filled with every layer's output (NCHW, gradients retained) for layer-isolated tests."""
         net = self.net
         vals: dict[str, torch.Tensor] = {}
         out = None
@@ -133,6 +134,10 @@ class RefExecutor:
             if self.emulate_bf16 and k in ("input", "conv", "dwconv", "bn", "act", "maxpool", "avgpool", "add"):
                 out = out + (out.to(torch.bfloat16).to(out.dtype) - out).detach()
             vals[sp.name] = out
+            if capture is not None:
+                if out.requires_grad:
+                    out.retain_grad()
+                capture[sp.name] = out
             if upto is not None and sp.name == upto:
                 break
         return out

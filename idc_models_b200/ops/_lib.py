@@ -52,12 +52,20 @@ class BnTail(C.Structure):
     ]
 
 
+class SliceTail(C.Structure):
+    _fields_ = [
+        ("out", vp), ("out_pitch", C.c_int), ("out_coff", C.c_int), ("acc_s1", vp), ("acc_s2", vp),
+        ("mean", vp), ("rstd", vp), ("bn_mean", vp), ("bn_rstd", vp), ("dgamma", vp), ("dbeta", vp),
+        ("count", C.c_float), ("counter", vp), ("c0", C.c_int),
+    ]
+
+
 class ConvBwdFused(C.Structure):
     _fields_ = [
         ("mode", C.c_int), ("aux", vp), ("aux_pitch", C.c_int), ("aux_coff", C.c_int),
         ("bwd_scale", vp), ("bwd_shift", vp), ("bwd_act", C.c_int),
         ("gacc", vp), ("g_pitch", C.c_int), ("g_coff", C.c_int),
-        ("stat_a", vp), ("stat_b", vp), ("tail", vp),
+        ("stat_a", vp), ("stat_b", vp), ("tail", vp), ("slice", vp),
     ]
 
 

@@ -115,7 +115,7 @@ def conv_fprop_raw(g: ConvGeom, x: torch.Tensor, w: torch.Tensor, y: torch.Tenso
 def conv_dgrad_raw(g: ConvGeom, dy: torch.Tensor, w: torch.Tensor, dx: torch.Tensor | None, *,
                    dy_coff: int = 0, dx_coff: int = 0, dx_pitch: int | None = None, mode: int = 0,
                    aux=None, aux_coff: int = 0, bwd_scale=None, bwd_shift=None, bwd_act: int = ACT_NONE,
-                   gacc=None, g_coff: int = 0, stat_a=None, stat_b=None, tail=None) -> None:
+                   gacc=None, g_coff: int = 0, stat_a=None, stat_b=None, tail=None, slice_tail=None) -> None:
     """dx = epi(conv^T(dy, w)); see include/idcb200.h for the epilogue modes. ``tail`` (bn_tail(...)): finish
     the BatchNorm backward of the mode-2 epilogue in the same launch."""
     _chk(dy, torch.bfloat16, "dy"); _chk(w, torch.bfloat16, "w"); _chk(dx, torch.bfloat16, "dx")
@@ -128,7 +128,8 @@ def conv_dgrad_raw(g: ConvGeom, dy: torch.Tensor, w: torch.Tensor, dx: torch.Ten
                           _lib.ptr(bwd_scale), _lib.ptr(bwd_shift), bwd_act, _lib.ptr(gacc),
                           gacc.shape[-1] if gacc is not None else 0, g_coff, _lib.ptr(stat_a),
                           _lib.ptr(stat_b),
-                          C.cast(C.pointer(tail), C.c_void_p) if tail is not None else C.c_void_p(0))
+                          C.cast(C.pointer(tail), C.c_void_p) if tail is not None else C.c_void_p(0),
+                          C.cast(C.pointer(slice_tail), C.c_void_p) if slice_tail is not None else C.c_void_p(0))
     lib = _lib.cuda_lib()
     _lib.check(lib.idcb_conv_dgrad(C.byref(d), _lib.ptr(dy), _lib.ptr(w), _lib.ptr(dx), C.byref(f),
                                    _lib.stream()))
@@ -154,6 +155,21 @@ def bn_tail(out: torch.Tensor, mean, rstd, count, counter=None, dgamma=None, dbe
     p = _lib.ptr
     return _lib.BnTail(p(out), out.shape[-1], out_coff, p(mean), p(rstd), float(count), p(dgamma), p(dbeta),
                        p(counter), 1 if frozen else 0)
+
+
+def slice_tail(out: torch.Tensor, c0: int, acc_s1, acc_s2, mean, rstd, bn_mean, bn_rstd, count, counter,
+               dgamma=None, dbeta=None, out_coff: int = 0) -> _lib.SliceTail:
+    """The finished gradient of block-buffer channels [c0, c0 + 32) produced inside the mode-2 dgrad launch that
+    writes them last (include/idcb200.h: idcb_slice_tail)."""
+    p = _lib.ptr
+    return _lib.SliceTail(p(out), out.shape[-1], out_coff, p(acc_s1), p(acc_s2), p(mean), p(rstd), p(bn_mean),
+                          p(bn_rstd), p(dgamma), p(dbeta), float(count), p(counter), int(c0))
+
+
+def slice_tail_fits(rows: int, cin: int) -> bool:
+    """co-residency rule of the slice tail: 128-row x 32-column tiles, two CTAs per SM"""
+    sms = _lib.cuda_lib().idcb_device_sm_count()
+    return -(-rows // 128) * -(-cin // 32) <= 2 * sms
 
 
 def bn_inline(sum_, sq, gamma, beta, count, eps, momentum, scale_out, shift_out, mean_out, rstd_out,

@@ -117,6 +117,29 @@ typedef struct idcb_bn_tail {
     int frozen;
 } idcb_bn_tail;
 
+/* Mode 2 accumulating into a DenseNet block's gradient buffer G (g_coff = 0), optional: when this dgrad is the last
+ * writer of the 32 buffer channels [c0, c0 + 32), their finished gradient
+ *   out = G - S1/N - xhat * S2/N        (what idcb_bn_bwd_slice computes in a launch of its own)
+ * is produced in the same launch after a grid barrier, with the BatchNorm in front of THIS convolution (bn_mean /
+ * bn_rstd, scale = bwd_scale, column sums stat_a / stat_b) folded into S1 / S2 on the fly; one CTA also does that
+ * BatchNorm's bookkeeping (dgamma +=, dbeta +=, S1/S2 += for the channels outside the slice). The launch uses
+ * 32-wide N tiles and needs ceil(M/128) * ceil(cin/32) CTAs co-resident (2 per SM), else it is refused. */
+typedef struct idcb_slice_tail {
+    void* out;                   /* bf16 [M, out_pitch], 32 channels at out_coff */
+    int out_pitch, out_coff;
+    float* acc_s1;               /* S1 / S2 accumulators, indexed by block channel */
+    float* acc_s2;
+    const float* mean;           /* batch statistics of the block buffer (for xhat), by block channel */
+    const float* rstd;
+    const float* bn_mean;        /* the BatchNorm in front of this convolution */
+    const float* bn_rstd;
+    float* dgamma;               /* optional */
+    float* dbeta;
+    float count;
+    unsigned int* counter;       /* one zeroed 32-bit word per launch */
+    int c0;
+} idcb_slice_tail;
+
 typedef struct idcb_conv_bwd_fused {
     int mode;
     const void* aux;
@@ -129,6 +152,7 @@ typedef struct idcb_conv_bwd_fused {
     float* stat_a;
     float* stat_b;
     const idcb_bn_tail* tail;    /* optional (NULL = off) */
+    const idcb_slice_tail* slice;/* optional (NULL = off) */
 } idcb_conv_bwd_fused;
 
 /* cuDNN convolution forward as called by Keras Conv2D (SURVEY 2.E K1/K2/K3/K6;

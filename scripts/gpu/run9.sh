@@ -1,0 +1,5 @@
+#!/bin/bash
+timeout 900 python -m pytest tests/test_gpu_conv.py tests/test_gpu_models.py tests/test_gpu_kernels.py -m gpu -x -q 2>&1 | tail -12
+run() { echo "== $M $*"; env "$@" timeout 300 python bench.py --model $M --steps 20 --warmup 5 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['ms_per_step'], d['value'], d['e2e']['value'], d['gpu_launches'])"; }
+M=densenet121
+run IDCB_SLICE_TAIL=1; run IDCB_SLICE_TAIL=0

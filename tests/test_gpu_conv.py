@@ -387,3 +387,57 @@ def test_centre_tap_window_equals_the_full_3x3_on_one_pixel():
     off = dw.clone()
     off[:, 1, 1, :] = 0
     assert off.abs().max().item() == 0
+
+
+@pytest.mark.parametrize("b,h,w,cin", [(128, 3, 3, 512), (128, 1, 1, 992), (32, 6, 6, 96)])
+def test_dgrad_mode2_with_slice_tail(b, h, w, cin):
+    """The 1x1 dgrad that is the last writer of a DenseNet block-buffer slice also emits that slice's finished
+    gradient and its BatchNorm's bookkeeping: equal to dgrad + idcb_bn_bwd_slice with the pending fold."""
+    from idc_models_b200.ops import kernels as K
+    torch.manual_seed(15)
+    ctot, cout = 1024, 128
+    M = b * h * w
+    g = C.geom(h, w, cin, cout, 1)
+    wt = _rand(cout, 1, 1, cin, scale=cout ** -0.5)
+    dy = _rand(b, h, w, cout)
+    buf = _rand(b, h, w, ctot)
+    bf_ = buf.float().reshape(-1, ctot)
+    mean = bf_.mean(0)
+    rstd = (bf_.var(0, unbiased=False) + 1e-5).rsqrt()
+    gamma = torch.rand(cin, device="cuda") + 0.5
+    sc = gamma * rstd[:cin]
+    sh = torch.randn(cin, device="cuda") * 0.1 - mean[:cin] * sc
+    G0 = torch.randn(b, h, w, ctot, device="cuda")
+    s1_0, s2_0 = torch.randn(ctot, device="cuda"), torch.randn(ctot, device="cuda")
+    c0 = cin - 32
+
+    def run(fused):
+        G = G0.clone()
+        s1, s2 = s1_0.clone(), s2_0.clone()
+        sa, sb = torch.zeros(cin, device="cuda"), torch.zeros(cin, device="cuda")
+        dgm, dbt = torch.ones(cin, device="cuda"), torch.ones(cin, device="cuda")
+        out = torch.zeros(b, h, w, 32, device="cuda", dtype=torch.bfloat16)
+        ctr = torch.zeros(64, device="cuda")
+        st = None
+        if fused:
+            assert C.slice_tail_fits(M, cin)
+            st = C.slice_tail(out, c0, s1, s2, mean, rstd, mean[:cin].contiguous(), rstd[:cin].contiguous(), M, ctr,
+                              dgamma=dgm, dbeta=dbt)
+        C.conv_dgrad_raw(g, dy, wt, None, dx_pitch=ctot, mode=2, aux=buf, bwd_scale=sc, bwd_shift=sh,
+                         bwd_act=C.ACT_RELU, gacc=G, stat_a=sa, stat_b=sb, slice_tail=st)
+        if not fused:
+            K.bn_bwd_slice(G, buf, out, c0, 32, float(M), s1, s2, mean, rstd,
+                           pending=(sa, sb, mean[:cin].contiguous(), rstd[:cin].contiguous(), sc, dgm, dbt))
+        torch.cuda.synchronize()
+        return G, s1, s2, dgm, dbt, out
+
+    Gf, s1f, s2f, dgf, dbf, outf = run(True)
+    Gr, s1r, s2r, dgr, dbr, outr = run(False)
+    _close(Gf, Gr, 1e-3)
+    _close(outf, outr, 2e-2)
+    _close(dgf, dgr, 1e-3)
+    _close(dbf, dbr, 1e-3)
+    outside = torch.ones(ctot, dtype=torch.bool, device="cuda")
+    outside[c0:c0 + 32] = False
+    _close(s1f[outside], s1r[outside], 1e-3)
+    _close(s2f[outside], s2r[outside], 1e-3)
