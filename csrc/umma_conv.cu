@@ -44,6 +44,10 @@ namespace idcb {
 constexpr int kBM = 128;      // UMMA M (rows of the accumulator = TMEM lanes)
 constexpr int kBK = 64;       // K elements per pipeline stage (one 128-byte swizzle row)
 constexpr int kMaxStages = 8;
+#ifndef IDCB_XFORM_GROUPS
+#define IDCB_XFORM_GROUPS 1
+#endif
+constexpr int kXformGroups = IDCB_XFORM_GROUPS;   // worker-warp groups that transform alternate k-blocks (prologue path); 2 measured slower: DenseNet-121 3.86 vs 3.78 ms
 constexpr int kRaw = 6;                          // k-blocks of raw activations in flight per CTA (transform path)
 constexpr int kBarBytes = 256;                    // barrier block: full/empty/acc/raw_full/raw_empty + TMEM slot
 constexpr int kRawBytes = kBM * 128;             // one k-block of raw 16-byte chunks, [chunk row i][thread]
@@ -596,14 +600,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         for (int s = 0; s < nstages; ++s) {
             // transform path: one arrival per warp of the owning worker group; copy path: one per issuing thread; + TMA
             // (with TMA im2col on the plain path one thread announces both operands' bytes)
-            mbar_init(&full_bar[s], has_pro ? kWork / 32 + 1 : (p.a_tma ? 1 : G::kIssuers + 1));
+            mbar_init(&full_bar[s], has_pro ? kWork / 32 / kXformGroups + 1 : (p.a_tma ? 1 : G::kIssuers + 1));
             mbar_init(&empty_bar[s], 1);  // one tcgen05.commit
         }
         mbar_init(acc_bar, 1);
         if (has_pro) {
             for (int s = 0; s < kRaw; ++s) {
                 mbar_init(&raw_full[s], p.a_tma ? 1 : G::kLoad);   // every loader thread's copies / one TMA issue
-                mbar_init(&raw_empty[s], kWork / 32);   // every warp of the group that owns the k-block has read it
+                mbar_init(&raw_empty[s], kWork / 32 / kXformGroups);   // every warp of the group that owns the k-block has read it
             }
         }
         mbar_fence_init();
@@ -756,7 +760,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
             // release-arrive on the "full" barrier retires at once.
             // The worker warps can be split into kGroups groups that take alternate k-blocks (more time per
             // group for its dependent wait -> load -> transform -> store -> arrive chain); one group is fastest.
-            constexpr int kGroups = 1, kGT = kWork / kGroups, kGR = 1024 / kGT;   // (2 groups of 128 threads measured: no gain)
+            constexpr int kGroups = kXformGroups, kGT = kWork / kGroups, kGR = 1024 / kGT;
             const int grp = threadIdx.x / kGT, gt = threadIdx.x % kGT;
             Gather<kGR, kGT / 8, kBMN> g;   // used for its (tap, channel) cursor and padding masks only
             g.init(p, m0, gt, kb0);

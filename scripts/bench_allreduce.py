@@ -83,8 +83,10 @@ if world.rank == 0:
         # (N-1)/N of fp32 weights + bf16 shadow out
         s_in = 4 * n * (N - 1) / N
         s_out = 6 * n * (N - 1) / N
-        roof_us = max(s_in, s_out) / 770e9 * 1e6
+        roof_us = max(s_in, s_out) / 770e9 * 1e6          # measured peer-copy bandwidth per direction (B200_PROFILING.md)
+        roof900 = max(s_in, s_out) / 900e9 * 1e6          # nominal NVLink 5 figure
         print(json.dumps({"case": name, "path": kind, "n_gpus": N, "elements": n, "us": round(us, 1),
-                          "roofline_us_770GBs": round(roof_us, 1), "fraction_of_roofline": round(roof_us / us, 3)}))
+                          "roofline_us_770GBs": round(roof_us, 1), "fraction_of_roofline": round(roof_us / us, 3),
+                          "roofline_us_900GBs": round(roof900, 1), "fraction_of_900": round(roof900 / us, 3)}))
 world.barrier()
 world.shutdown()
