@@ -277,6 +277,7 @@ struct PoolArgs {
     const float* scale; const float* shift; int act;
     int is_max;
     float* stat_sum; float* stat_sq;
+    unsigned char* argmax;   // optional (max): window index kh*k+kw of the first maximum, one byte per output element
 };
 
 __global__ void pool_fwd_kernel(PoolArgs p) {
@@ -292,8 +293,9 @@ __global__ void pool_fwd_kernel(PoolArgs p) {
         const int ho = static_cast<int>(pos % p.Ho);
         const int b = static_cast<int>(pos / p.Ho);
         float acc[8];
+        unsigned char am[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) acc[e] = p.is_max ? -3.0e38f : 0.f;
+        for (int e = 0; e < 8; ++e) { acc[e] = p.is_max ? -3.0e38f : 0.f; am[e] = 0; }
         bool any = false;
         for (int kh = 0; kh < p.k; ++kh) {
             const int hi = ho * p.stride - p.pad + kh;
@@ -316,8 +318,9 @@ __global__ void pool_fwd_kernel(PoolArgs p) {
                         f.y = __bfloat162float(__float2bfloat16_rn(f.y));
                     }
                     if (p.is_max) {
-                        acc[2 * e] = fmaxf(acc[2 * e], f.x);
-                        acc[2 * e + 1] = fmaxf(acc[2 * e + 1], f.y);
+                        // strict '>' in row-major window order: ties go to the first maximum (cuDNN / TF / PyTorch)
+                        if (f.x > acc[2 * e]) { acc[2 * e] = f.x; am[2 * e] = static_cast<unsigned char>(kh * p.k + kw); }
+                        if (f.y > acc[2 * e + 1]) { acc[2 * e + 1] = f.y; am[2 * e + 1] = static_cast<unsigned char>(kh * p.k + kw); }
                     } else {
                         acc[2 * e] += f.x;
                         acc[2 * e + 1] += f.y;
@@ -337,6 +340,12 @@ __global__ void pool_fwd_kernel(PoolArgs p) {
         }
         const long long opos = (static_cast<long long>(b * p.Ho + ho) * p.Wo + wo);
         *reinterpret_cast<uint4*>(p.y + opos * p.y_pitch + p.y_coff + c) = o;
+        if (p.argmax != nullptr) {
+            uint2 pk;
+            pk.x = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
+            pk.y = am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24);
+            *reinterpret_cast<uint2*>(p.argmax + opos * p.C + c) = pk;
+        }
     }
 }
 
@@ -356,6 +365,7 @@ struct PoolBwdArgs {
     int is_max;
     int relu_mask;   // dx *= (x > 0)
     float* stat_a; float* stat_b;
+    const unsigned char* argmax;   // optional (max): what the forward pass recorded; replaces the value comparison
 };
 
 __global__ void pool_bwd_kernel(PoolBwdArgs p) {
@@ -403,7 +413,20 @@ __global__ void pool_bwd_kernel(PoolBwdArgs p) {
                 const long long op = (static_cast<long long>(b * p.Ho + ho) * p.Wo + wo);
                 uint4 dv = *reinterpret_cast<const uint4*>(p.dy + op * p.dy_pitch + p.dy_coff + c);
                 const uint32_t* dw = reinterpret_cast<const uint32_t*>(&dv);
-                if (p.is_max) {
+                if (p.is_max && p.argmax != nullptr) {
+                    // the forward pass recorded which window element won: no re-evaluation of the activation, no
+                    // tie-breaking scan over the earlier window elements
+                    const uint2 pk = *reinterpret_cast<const uint2*>(p.argmax + op * p.C + c);
+                    const unsigned me = static_cast<unsigned>((hi - (ho * p.stride - p.pad)) * p.k + (wi - (wo * p.stride - p.pad)));
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float2 d = unpack_bf16x2(dw[e]);
+                        const unsigned a0 = ((e < 2 ? pk.x : pk.y) >> (16 * (e & 1))) & 0xFFu;
+                        const unsigned a1 = ((e < 2 ? pk.x : pk.y) >> (16 * (e & 1) + 8)) & 0xFFu;
+                        if (a0 == me) g[2 * e] += d.x;
+                        if (a1 == me) g[2 * e + 1] += d.y;
+                    }
+                } else if (p.is_max) {
                     uint4 yv = *reinterpret_cast<const uint4*>(p.y + op * p.y_pitch + p.y_coff + c);
                     const uint32_t* yw = reinterpret_cast<const uint32_t*>(&yv);
                     float ymax[8], dd[8];
@@ -475,17 +498,27 @@ __global__ void pool_bwd_kernel(PoolBwdArgs p) {
         *reinterpret_cast<uint4*>(p.dx + pos * p.dx_pitch + p.dx_coff + c) = o;
     }
     if (p.stat_a == nullptr) return;
-    for (int pass = 0; pass < 2; ++pass) {
-        if (pass == 1 && p.stat_b == nullptr) break;
-        __syncthreads();
+    // block-wide sums of the 8 channels: warp shuffles, then one partial per warp through shared memory
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) s_a[threadIdx.x][e] = pass ? sb[e] : sa[e];
-        __syncthreads();
-        if (threadIdx.x < 8) {
-            float t = 0.f;
-            for (int r = 0; r < (int)blockDim.x; ++r) t += s_a[r][threadIdx.x];
-            atomicAdd((pass ? p.stat_b : p.stat_a) + c + threadIdx.x, t);
+    for (int e = 0; e < 8; ++e) {
+        sa[e] = warp_sum(sa[e]);
+        sb[e] = warp_sum(sb[e]);
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            s_a[wid][e] = sa[e];
+            s_a[8 + wid][e] = sb[e];
         }
+    }
+    __syncthreads();
+    if (threadIdx.x < 16) {
+        const int which = threadIdx.x >> 3, e = threadIdx.x & 7;
+        float t = 0.f;
+        for (int w2 = 0; w2 < static_cast<int>(blockDim.x >> 5); ++w2) t += s_a[which * 8 + w2][e];
+        if (which == 0) atomicAdd(p.stat_a + c + e, t);
+        else if (p.stat_b != nullptr) atomicAdd(p.stat_b + c + e, t);
     }
 }
 
@@ -778,7 +811,7 @@ extern "C" int idcb_channel_stats2(const void* g, int g_pitch, int g_coff, const
 }
 
 extern "C" int idcb_pool_fwd(const idcb_pool_desc* d, const void* x, void* y, const float* scale,
-                             const float* shift, int act, void* stream) {
+                             const float* shift, int act, unsigned char* argmax, void* stream) {
     IDCB_REQUIRE(d && d->c % 8 == 0 && d->x_pitch % 8 == 0 && d->y_pitch % 8 == 0 &&
                      d->x_coff % 8 == 0 && d->y_coff % 8 == 0, "pool_fwd: alignment");
     PoolArgs p{};
@@ -787,6 +820,7 @@ extern "C" int idcb_pool_fwd(const idcb_pool_desc* d, const void* x, void* y, co
     p.B = d->batch; p.H = d->h; p.W = d->w; p.C = d->c; p.Ho = d->ho; p.Wo = d->wo;
     p.k = d->k; p.stride = d->stride; p.pad = d->pad;
     p.scale = scale; p.shift = shift; p.act = act; p.is_max = d->is_max;
+    p.argmax = d->is_max ? argmax : nullptr;
     const long long items = 1LL * p.B * p.Ho * p.Wo * (p.C / 8);
     if (items == 0) return 0;
     IDCB_CHECK(launch_pdl(pool_fwd_kernel, ew_grid(items, 256), 256, 0, (cudaStream_t)stream, p));
@@ -797,7 +831,7 @@ extern "C" int idcb_pool_fwd(const idcb_pool_desc* d, const void* x, void* y, co
 extern "C" int idcb_pool_bwd(const idcb_pool_desc* d, const void* x, const void* y, const void* dy,
                              int dy_pitch, int dy_coff, void* dx, int dx_pitch, int dx_coff,
                              const float* scale, const float* shift, int act, int relu_mask,
-                             float* stat_a, float* stat_b, void* stream) {
+                             float* stat_a, float* stat_b, const unsigned char* argmax, void* stream) {
     IDCB_REQUIRE(d && d->c % 8 == 0 && d->x_pitch % 8 == 0 && d->y_pitch % 8 == 0 &&
                      dy_pitch % 8 == 0 && dx_pitch % 8 == 0 && dy_coff % 8 == 0 && dx_coff % 8 == 0,
                  "pool_bwd: alignment");
@@ -810,6 +844,7 @@ extern "C" int idcb_pool_bwd(const idcb_pool_desc* d, const void* x, const void*
     p.k = d->k; p.stride = d->stride; p.pad = d->pad;
     p.scale = scale; p.shift = shift; p.act = act; p.is_max = d->is_max; p.relu_mask = relu_mask;
     p.stat_a = stat_a; p.stat_b = stat_b;
+    p.argmax = d->is_max ? argmax : nullptr;
     const long long npos = 1LL * p.B * p.H * p.W;
     if (npos == 0) return 0;
     int gx = static_cast<int>(ceil_div_ll(npos, 256));

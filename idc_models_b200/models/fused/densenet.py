@@ -71,6 +71,7 @@ class DenseNetExecutor(FusedExecutor):
         p.stem_bwd = ft <= idx("conv1/bn")
         p.bn_stem = BNState(self, "conv1/bn", 64, sc, p.stem_bwd)
         h2, w2 = (h1 + 2 - 3) // 2 + 1, (w1 + 2 - 3) // 2 + 1
+        p.pool1_arg = torch.zeros(batch, h2, w2, 64, dtype=torch.uint8, device=dev) if p.stem_bwd else None
         if p.stem_bwd:
             p.dpool1 = torch.zeros(batch, h2, w2, 64, dtype=bf, device=dev)
             p.dpre_stem = torch.zeros(batch, h1, w1, 64, dtype=bf, device=dev)
@@ -179,7 +180,8 @@ class DenseNetExecutor(FusedExecutor):
         self._bn_forward(p.bn_stem, training, sc.view(p.o_stem_sum, 64), sc.view(p.o_stem_sq, 64),
                          float(p.s0.numel() // 64))
         b0 = p.blocks[0]
-        K.pool_fwd(p.s0, b0.buf, 64, 3, 2, 1, True, scale=p.bn_stem.scale, shift=p.bn_stem.shift, act=ACT_RELU)
+        K.pool_fwd(p.s0, b0.buf, 64, 3, 2, 1, True, scale=p.bn_stem.scale, shift=p.bn_stem.shift, act=ACT_RELU,
+                   argmax=p.pool1_arg if training else None)
         if stats:
             K.channel_stats(b0.buf, 64, sc.view(b0.o_sum, 64), sc.view(b0.o_sq, 64))
         # ---- dense blocks ----------------------------------------------------------------------------
@@ -417,7 +419,7 @@ class DenseNetExecutor(FusedExecutor):
         self._finalize_slice(b0, 0, 64, p.dpool1)
         bn = p.bn_stem
         K.pool_bwd(p.s0, b0.buf, p.dpool1, p.dpre_stem, 64, 3, 2, 1, True, scale=bn.scale, shift=bn.shift,
-                   act=ACT_RELU, stat_a=bn.sa, stat_b=bn.sb)
+                   act=ACT_RELU, stat_a=bn.sa, stat_b=bn.sb, argmax=p.pool1_arg)
         if ft > self.net.get_layer("conv1/conv").index:
             if bn.trainable:
                 K.bn_bwd_coeffs(bn.sa, bn.sb, bn.mean, bn.rstd, bn.scale, float(p.s0.numel() // 64),

@@ -127,17 +127,19 @@ def pool_desc(x, y, channels, k, stride, pad, is_max, x_coff=0, y_coff=0) -> Poo
     return PoolDesc(b, h, w, channels, ho, wo, k, stride, pad, 1 if is_max else 0, xp, x_coff, yp, y_coff)
 
 
-def pool_fwd(x, y, channels, k, stride, pad=0, is_max=True, x_coff=0, y_coff=0, scale=None, shift=None, act=0):
+def pool_fwd(x, y, channels, k, stride, pad=0, is_max=True, x_coff=0, y_coff=0, scale=None, shift=None, act=0,
+             argmax=None):
+    """``argmax`` (uint8 [B, Ho, Wo, channels], max pooling): records the winning window element for pool_bwd"""
     d = pool_desc(x, y, channels, k, stride, pad, is_max, x_coff, y_coff)
-    _call(_lib.cuda_lib().idcb_pool_fwd, C.byref(d), _p(x), _p(y), _p(scale), _p(shift), C.c_int(act))
+    _call(_lib.cuda_lib().idcb_pool_fwd, C.byref(d), _p(x), _p(y), _p(scale), _p(shift), C.c_int(act), _p(argmax))
 
 
 def pool_bwd(x, y, dy, dx, channels, k, stride, pad=0, is_max=True, x_coff=0, y_coff=0, dy_coff=0,
-             dx_coff=0, scale=None, shift=None, act=0, relu_mask=False, stat_a=None, stat_b=None):
+             dx_coff=0, scale=None, shift=None, act=0, relu_mask=False, stat_a=None, stat_b=None, argmax=None):
     d = pool_desc(x, y, channels, k, stride, pad, is_max, x_coff, y_coff)
     _call(_lib.cuda_lib().idcb_pool_bwd, C.byref(d), _p(x), _p(y), _p(dy), C.c_int(dy.shape[-1]),
           C.c_int(dy_coff), _p(dx), C.c_int(dx.shape[-1]), C.c_int(dx_coff), _p(scale), _p(shift),
-          C.c_int(act), C.c_int(1 if relu_mask else 0), _p(stat_a), _p(stat_b))
+          C.c_int(act), C.c_int(1 if relu_mask else 0), _p(stat_a), _p(stat_b), _p(argmax))
 
 
 def pack_input(x_f32: torch.Tensor, y_bf16: torch.Tensor):

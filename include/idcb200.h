@@ -246,12 +246,15 @@ typedef struct idcb_pool_desc {
     int batch, h, w, c, ho, wo, k, stride, pad, is_max;
     int x_pitch, x_coff, y_pitch, y_coff;
 } idcb_pool_desc;
+/* `argmax` (max pooling, optional): one byte per output element [B, Ho, Wo, C] = index kh*k+kw of the first
+ * maximum of the window; written by the forward pass and, when given to the backward pass, used instead of
+ * comparing re-evaluated activations (an overlapping pool otherwise needs a tie-breaking scan per window). */
 int idcb_pool_fwd(const idcb_pool_desc* d, const void* x, void* y, const float* scale,
-                  const float* shift, int act, void* stream);
+                  const float* shift, int act, unsigned char* argmax, void* stream);
 int idcb_pool_bwd(const idcb_pool_desc* d, const void* x, const void* y, const void* dy, int dy_pitch,
                   int dy_coff, void* dx, int dx_pitch, int dx_coff, const float* scale,
                   const float* shift, int act, int relu_mask, float* stat_a, float* stat_b,
-                  void* stream);
+                  const unsigned char* argmax, void* stream);
 
 /* ---- input packing / casts --------------------------------------------------------------------- */
 /* convert_image_dtype + channel padding to 8 (dist_model_tf_mobile.py:37-40 produces fp32 [0,1]) */

@@ -334,3 +334,40 @@ def test_bn_bwd_slice_folds_the_pending_consumer_batchnorm():
     K.bn_bwd_slice(G, x, got2, c_lo, cn, float(M), s1, s2, mean, rstd)
     torch.cuda.synchronize()
     assert torch.equal(got2, want)
+
+
+def test_pool_max_backward_through_recorded_argmax():
+    """Overlapping 3x3/2 max pool with the BatchNorm+ReLU prologue (DenseNet's pool1): the backward pass driven by
+    the argmax bytes the forward pass recorded gives exactly what the value-comparing backward pass gives (first
+    maximum wins a tie in both), including the BatchNorm-backward column sums."""
+    torch.manual_seed(31)
+    b, h, c = 4, 25, 64
+    x = bf(b, h, h, c)
+    # plenty of exact ties: quantise the input coarsely
+    x = (x.float() * 2).round().div(2).to(torch.bfloat16)
+    sc, sh = torch.rand(c, device=DEV) + 0.5, torch.randn(c, device=DEV) * 0.3
+    y = torch.zeros(b, 13, 13, c, device=DEV, dtype=torch.bfloat16)
+    arg = torch.full((b, 13, 13, c), 255, device=DEV, dtype=torch.uint8)
+    K.pool_fwd(x, y, c, 3, 2, 1, True, scale=sc, shift=sh, act=1, argmax=arg)
+    y2 = torch.zeros_like(y)
+    K.pool_fwd(x, y2, c, 3, 2, 1, True, scale=sc, shift=sh, act=1)
+    assert torch.equal(y, y2) and int(arg.max()) <= 8
+    dy = bf(b, 13, 13, c)
+    outs = []
+    for use_arg in (True, False):
+        dx = torch.zeros(b, h, h, c, device=DEV, dtype=torch.bfloat16)
+        sa, sb = torch.zeros(c, device=DEV), torch.zeros(c, device=DEV)
+        K.pool_bwd(x, y, dy, dx, c, 3, 2, 1, True, scale=sc, shift=sh, act=1, stat_a=sa, stat_b=sb,
+                   argmax=arg if use_arg else None)
+        torch.cuda.synchronize()
+        outs.append((dx, sa, sb))
+    assert torch.equal(outs[0][0], outs[1][0])
+    close(outs[0][1], outs[1][1], 1e-4)
+    close(outs[0][2], outs[1][2], 1e-4)
+    # and against autograd where the window maximum is unique
+    a = torch.relu(x.float() * sc + sh).to(torch.bfloat16).float().permute(0, 3, 1, 2).requires_grad_(True)
+    yr = F.max_pool2d(F.pad(a, (1, 1, 1, 1)), 3, 2)
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    want = a.grad.permute(0, 2, 3, 1) * ((x.float() * sc + sh) > 0)
+    frac_bad = ((outs[0][0].float() - want).abs() > 2e-2 * (want.abs().max() + 1e-6)).float().mean().item()
+    assert frac_bad < 0.02, frac_bad
