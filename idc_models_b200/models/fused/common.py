@@ -73,6 +73,15 @@ class FusedExecutor:
         if self.grad_hook is not None and self._hook_live:
             self.grad_hook.ready(int(offset))
 
+    def announcement_fires(self, offset: int) -> bool:
+        """True if announcing ``offset`` now would launch a gradient bucket (lets an executor skip the side-stream
+        join an announcement needs when the schedule would merge it into a later bucket anyway)."""
+        h = self.grad_hook
+        if h is None or not self._hook_live:
+            return False
+        fires = getattr(h, "fires", None)
+        return bool(fires(int(offset))) if fires is not None else True
+
     _hook_live = False
 
     def _run_hooked(self, plan, training: bool, grad_scale: float) -> None:

@@ -235,6 +235,40 @@ class MobileNetV2Executor(FusedExecutor):
             fn(*args, **kw)
         self._wg_pending = True
 
+    # ---- gradient announcements: once the backward pass has left inverted-residual block bi, every
+    # gradient of block bi and of everything above it is final, so that part of the flat gradient buffer can be
+    # all-reduced while the blocks below are still being differentiated
+    def _block_offsets_table(self) -> list:
+        st = self.net.store
+        offs = []
+        block_id = 0
+        while True:
+            prefix = "expanded_conv_" if block_id == 0 else f"block_{block_id}_"
+            names = [pp.name for l in self.net.layers if l.spec.name.startswith(prefix) for pp in l.spec.params
+                     if st.slots[pp.name].trainable_kind]
+            if not names:
+                break
+            offs.append(min(st.slots[n].offset for n in names))
+            block_id += 1
+        return offs
+
+    def grad_ready_offsets(self) -> list:
+        self._blk_off = self._block_offsets_table()
+        return sorted(self._blk_off, reverse=True)
+
+    def _announce(self, bi: int) -> None:
+        if not hasattr(self, "_blk_off"):
+            self._blk_off = self._block_offsets_table()
+        if bi >= len(self._blk_off):
+            return
+        off = self._blk_off[bi]
+        if not self.announcement_fires(off):
+            return          # merged into a later bucket: no need to wait for the weight-gradient stream now
+        if getattr(self, "_wg_pending", False):
+            torch.cuda.current_stream().wait_stream(self._wg_stream)
+            self._wg_pending = False
+        self.grads_ready(off)
+
     def _backward(self, p) -> None:
         try:
             self._backward_impl(p)
@@ -308,6 +342,7 @@ class MobileNetV2Executor(FusedExecutor):
                             if prev is not None and prev.bwd:
                                 OC.conv_dgrad_raw(b.ge, b.de_raw, self.w16(b.prefix + "expand/kernel"),
                                                   prev.dout, mode=0, aux=b.dout if b.add else None)
+                                self._announce(bi)
                                 continue
                     else:
                         # first block: the depthwise conv reads the stem directly

@@ -232,6 +232,9 @@ class OverlapSchedule:
         lib.idcb_comm_set_max_ctas(C.c_int(0))
         self._forked = True
 
+    def fires(self, offset: int) -> bool:
+        return self._next < len(self.plan) - 1 and offset <= self.plan[self._next][0]
+
     def ready(self, offset: int) -> None:
         while self._next < len(self.plan) - 1 and offset <= self.plan[self._next][0]:
             _, b, e = self.plan[self._next]

@@ -53,6 +53,26 @@ for comm in ("nccl", "fused", "fused_overlap", "fused_overlap_graph", "nccl_cent
         res["stat_mean_err"] = (m.store.stats.cpu() - want).abs().max().item()
         res["stat_spread"] = (torch.stack(allst).max(0).values - torch.stack(allst).min(0).values).max().item()
     res[comm] = (m.store.master.double().sum().item(), m.store.master.double().abs().sum().item(), mc)
+# MobileNetV2: buckets announced per inverted-residual block from inside the backward pass
+for comm in ("nccl", "fused_overlap", "fused_overlap_graph"):
+    strategy = MirroredStrategy(world=world, comm=comm.split("_")[0])
+    strategy.overlap = "overlap" in comm
+    strategy.overlap_min_bucket = 2048
+    with strategy.scope():
+        m = build_transfer_model("mobilenet_v2_tiny", device=world.device, seed=0)
+        m.base.trainable = True
+        m.compile(optimizer=SGD(learning_rate=1e-2), loss="bce", metrics=["accuracy"])
+    m.executor.use_graphs = comm.endswith("graph")
+    if "overlap" in comm:
+        assert strategy._overlap is not None and len(strategy._overlap.plan) >= 2, "no MobileNetV2 overlap schedule"
+        res["mb_buckets"] = len(strategy._overlap.plan)
+    g = torch.Generator().manual_seed(0)
+    gb = 32 * world.size
+    x = torch.rand(gb, 50, 50, 3, generator=g).to(world.device); y = (torch.rand(gb, generator=g) > 0.5).float().to(world.device)
+    for _ in range(3):
+        m.train_on_batch(x, y)
+    torch.cuda.synchronize()
+    res["mb_" + comm] = (m.store.master.double().sum().item(), m.store.master.double().abs().sum().item())
 outs = world.all_gather_object(res)
 if world.rank == 0:
     print("RESULT " + json.dumps(outs))
@@ -88,6 +108,10 @@ def test_fused_allreduce_matches_nccl_path_across_processes():
         for k in ("fused_overlap", "fused_overlap_graph", "nccl_central", "fused_central"):
             assert o[k][:2] == outs[0][k][:2], "replicas are not bit-identical"
             assert abs(o[k][0] - o["nccl"][0]) < 1e-4 * max(1.0, abs(o["nccl"][1])), (k, o[k], o["nccl"])
+        for k in ("mb_fused_overlap", "mb_fused_overlap_graph"):
+            assert o[k] == outs[0][k], "MobileNetV2 replicas are not bit-identical"
+            assert abs(o[k][0] - o["mb_nccl"][0]) < 1e-4 * max(1.0, abs(o["mb_nccl"][1])), (k, o[k], o["mb_nccl"])
+        assert o["mb_buckets"] >= 2
     print("multicast (NVLS) used by the fused path:", outs[0]["fused"][2])
 
 
