@@ -486,15 +486,22 @@ __global__ void __launch_bounds__(kCommThreads) secagg_kernel(SecAggArgs a) {
             const float4 w = *reinterpret_cast<const float4*>(a.clients[pr.rank] + kl * a.stride + a.offset + (i << 2));
             acc.x += quantise(w.x, scale); acc.y += quantise(w.y, scale);
             acc.z += quantise(w.z, scale); acc.w += quantise(w.w, scale);
-            for (int j = 0; j < total; ++j) {
-                if (j / a.k_local == pr.rank) continue;   // same-GPU pairs cancel inside this partial sum
-                const int lo = k < j ? k : j, hi = k < j ? j : k;
-                const uint4 m = philox4x32_10(static_cast<uint32_t>(i), static_cast<uint32_t>(i >> 32),
-                                              static_cast<uint32_t>(lo), static_cast<uint32_t>(hi),
-                                              static_cast<uint32_t>(a.session_seed),
-                                              static_cast<uint32_t>(a.session_seed >> 32));
-                if (k < j) { acc.x += m.x; acc.y += m.y; acc.z += m.z; acc.w += m.w; }
-                else       { acc.x -= m.x; acc.y -= m.y; acc.z -= m.z; acc.w -= m.w; }
+            // Every pair (k, j) with j on ANOTHER GPU needs its own mask block (pairs on this GPU cancel inside this
+            // partial sum and are skipped). Walking the peers rank by rank keeps the division out of the loop and makes
+            // the sign a per-peer constant: clients of a higher rank have higher ids (k < j: add), of a lower rank
+            // lower ids (subtract).
+            for (int pq = 0; pq < pr.world; ++pq) {
+                if (pq == pr.rank) continue;
+                const bool add = pq > pr.rank;
+                for (int jl = 0; jl < a.k_local; ++jl) {
+                    const int j = pq * a.k_local + jl;
+                    const uint4 m = philox4x32_10(static_cast<uint32_t>(i), static_cast<uint32_t>(i >> 32),
+                                                  static_cast<uint32_t>(add ? k : j), static_cast<uint32_t>(add ? j : k),
+                                                  static_cast<uint32_t>(a.session_seed),
+                                                  static_cast<uint32_t>(a.session_seed >> 32));
+                    if (add) { acc.x += m.x; acc.y += m.y; acc.z += m.z; acc.w += m.w; }
+                    else     { acc.x -= m.x; acc.y -= m.y; acc.z -= m.z; acc.w -= m.w; }
+                }
             }
         }
         *reinterpret_cast<uint4*>(a.ybuf[pr.rank] + (i << 2)) = acc;

@@ -145,9 +145,52 @@ def bench_secure(world, args, comm: str) -> dict:
             "nvlink_roofline_us": round(roof_us, 3)}
 
 
+def bench_secure_size(world, args) -> dict:
+    """The masked-sum kernel alone at model size (default: MobileNetV2's 2.26 M floats, 8 clients per GPU): the regime
+    where the pairwise Philox masks, not the NVLink traffic, are the cost. Needs >= 2 GPUs (pairs on
+    one GPU cancel and generate nothing)."""
+    import ctypes as C
+    from idc_models_b200.ops import _lib
+    from idc_models_b200.parallel.symm import SymmAllocator
+    dev, N = world.device, world.size
+    lib = _lib.cuda_lib()
+    alloc = SymmAllocator(world)
+    n = -(-args.secure_floats // 4) * 4
+    k = args.secure_clients_per_gpu
+    clients = alloc.alloc(k * n, torch.float32)
+    clients.tensor.normal_(0, 0.05)
+    ybuf = alloc.alloc(n, torch.int32)
+    out = alloc.alloc(n, torch.float32)
+    cw = alloc.comm_world()
+    vp = C.c_void_p
+
+    def launch():
+        _lib.check(lib.idcb_secagg_masked_sum(C.byref(cw), clients.ptrs(), ybuf.ptrs(), ybuf.mc(), out.ptrs(), out.mc(),
+                                              C.c_int(k), C.c_longlong(n), C.c_longlong(0), C.c_longlong(n), C.c_int(16),
+                                              C.c_ulonglong(1234), _lib.stream()))
+
+    ms = timed(world, launch, args.agg_reps, warm=3)
+    want = clients.tensor.view(k, n).double().sum(0)
+    if world.is_distributed:
+        dist.all_reduce(want)
+    err = (out.tensor[:n].double() - want / (k * N)).abs().max().item()
+    words = k * (N - 1) * k * n                       # 32-bit mask words generated per GPU
+    philox_calls = words / 4
+    # Philox4x32-10: 10 rounds x (2 wide multiplies + 4 xor + 2 key adds) ~ 100 integer operations per call; INT32 peak of a
+    # B200 ~ 148 SMs x 128 lanes x 1.965 GHz
+    int_ops = philox_calls * 100
+    peak = 148 * 128 * 1.965e9
+    return {"bench": "secure_masked_sum_at_model_size", "n_gpus": N, "clients_per_gpu": k, "clients": k * N, "floats": n,
+            "kernel_us": round(ms * 1e3, 1), "max_abs_err_vs_float_mean": err, "mask_words_per_gpu": words,
+            "mask_words_per_s": round(words / (ms * 1e-3), 1), "int32_ops_estimate": int_ops,
+            "fraction_of_int32_peak_estimate": round(int_ops / (ms * 1e-3) / peak, 3),
+            "nvlink_bytes_in_per_gpu": (N - 1) / N * n * 8}
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
-    ap.add_argument("--mode", default="all", choices=["fedavg", "secure", "all"])
+    ap.add_argument("--mode", default="all", choices=["fedavg", "secure", "secure_size", "all"])
+    ap.add_argument("--secure-floats", type=int, default=2257984, help="secure_size: protected floats (MobileNetV2)")
     ap.add_argument("--comm", default="both", choices=["fused", "nccl", "both"])
     ap.add_argument("--arch", default="mobilenet_v2")
     ap.add_argument("--rounds", type=int, default=3)
@@ -167,6 +210,11 @@ def main() -> int:
         return 2
     comms = ["fused", "nccl"] if args.comm == "both" else [args.comm]
     modes = ["fedavg", "secure"] if args.mode == "all" else [args.mode]
+    if args.mode == "secure_size":
+        res = bench_secure_size(world, args)
+        if world.rank == 0:
+            print(json.dumps(res), flush=True)
+        modes = []
     for mode in modes:
         for comm in comms:
             res = (bench_fedavg if mode == "fedavg" else bench_secure)(world, args, comm)
