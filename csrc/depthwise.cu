@@ -6,6 +6,8 @@
 // thread per 8 channels, 16-byte accesses laid out so that a warp touches whole 128-byte lines (DwLane),
 // fused BN prologue/epilogue bookkeeping instead of separate BN kernels. Reference: DepthwiseConv2D layers inside tf.keras.applications.MobileNetV2
 // (/root/reference/dist_model_tf_mobile.py:119), executed by TF's depthwise CUDA kernels.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "../include/idcb200.h"
 
@@ -253,7 +255,9 @@ static dim3 dw_grid(long long npos, int C, int pos_per_thread = 1) {
     long long gx = ceil_div_ll(npos, 1LL * ppb * pos_per_thread);
     // every block ends with per-channel atomics (statistics / weight gradient): the number of blocks, not the
     // data volume, sets the contention on those few hundred addresses
-    const long long cap = (pos_per_thread > 1 ? 1LL : 2LL) * num_sms();
+    static const int cap_fd = [] { const char* e = getenv("IDCB_DW_BLOCKS_PER_SM"); int v = e ? atoi(e) : 2; return v > 0 ? v : 2; }();
+    static const int cap_w = [] { const char* e = getenv("IDCB_DW_WGRAD_BLOCKS_PER_SM"); int v = e ? atoi(e) : 1; return v > 0 ? v : 1; }();
+    const long long cap = 1LL * (pos_per_thread > 1 ? cap_w : cap_fd) * num_sms();
     if (gx > cap) gx = cap;
     if (gx < 1) gx = 1;
     return dim3(static_cast<unsigned>(gx), 1);

@@ -10,6 +10,8 @@ asymmetric padding of the stride-2 depthwise convs and of ``Conv1`` is expressed
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from ...ops import conv as OC
@@ -104,6 +106,7 @@ class MobileNetV2Executor(FusedExecutor):
                 b.d_raw = z(ho, wo, b.cexp)
                 b.st_d = _Stat(sc, b.cexp)
                 b.bn_d = BNState(self, b.prefix + "depthwise_BN", b.cexp, sc, ft <= b.i_dbn)
+                b.o_ctr = sc.reserve(64)        # grid-barrier word of the project dgrad + BatchNorm-tail launch
                 b.i_p, b.i_pbn = idx(b.prefix + "project"), idx(b.prefix + "project_BN")
                 b.gp = OC.geom(ho, wo, b.cexp, c, 1)
                 b.p_raw = z(ho, wo, c)
@@ -150,6 +153,16 @@ class MobileNetV2Executor(FusedExecutor):
         else:
             bn.fold()
 
+    def _pro(self, bn: BNState, training: bool, st: _Stat, count: float) -> dict:
+        """kwargs that make ``bn`` + activation the operand prologue of the consuming tensor-core conv: a training-mode
+        BatchNorm is finalised INSIDE that kernel from the batch sums (no finalisation launch)."""
+        if training and bn.trainable:
+            bn._folded_at = None
+            return {"bn": OC.bn_inline(st.sum, st.sq, bn.gamma, bn.beta, count, bn.eps, bn.momentum, bn.scale,
+                                       bn.shift, bn.mean, bn.rstd, bn.mmean, bn.mvar)}
+        bn.fold()
+        return {"pro_scale": bn.scale, "pro_shift": bn.shift}
+
     @staticmethod
     def _cnt(t: torch.Tensor) -> float:
         return float(t.numel() // t.shape[-1])
@@ -179,11 +192,9 @@ class MobileNetV2Executor(FusedExecutor):
             a, q = ss(b.st_d)
             K.dwconv_fprop(b.gd, dw_in, self.w16(b.prefix + "depthwise/depthwise_kernel"), b.d_raw,
                            scale=dw_bn.scale, shift=dw_bn.shift, act=ACT_RELU6, stat_sum=a, stat_sq=q)
-            self._bn(b.bn_d, tr, b.st_d, self._cnt(b.d_raw))
             a, q = ss(b.st_p)
-            OC.conv_fprop_raw(b.gp, b.d_raw, self.w16(b.prefix + "project/kernel"), b.p_raw,
-                              pro_scale=b.bn_d.scale, pro_shift=b.bn_d.shift, pro_act=ACT_RELU6,
-                              stat_sum=a, stat_sq=q)
+            OC.conv_fprop_raw(b.gp, b.d_raw, self.w16(b.prefix + "project/kernel"), b.p_raw, pro_act=ACT_RELU6,
+                              stat_sum=a, stat_sq=q, **self._pro(b.bn_d, tr, b.st_d, self._cnt(b.d_raw)))
             self._bn(b.bn_p, tr, b.st_p, self._cnt(b.p_raw))
             K.affine_act(b.p_raw, b.out, b.cout, b.bn_p.scale, b.bn_p.shift, ACT_NONE,
                          res=cur if b.add else None)
@@ -223,6 +234,7 @@ class MobileNetV2Executor(FusedExecutor):
     # Weight-gradient kernels (1x1 and depthwise) run on a side stream beside the data-gradient chain: every
     # buffer they read is per-block and written once per step, so the only join is at the end of the backward.
     wgrad_side_stream = True
+    bn_tail = os.environ.get("IDCB_BN_TAIL", "1") != "0"
 
     def _side(self, fn, *args, **kw) -> None:
         if not self.wgrad_side_stream:
@@ -314,14 +326,24 @@ class MobileNetV2Executor(FusedExecutor):
                                   pro_scale=b.bn_d.scale, pro_shift=b.bn_d.shift, pro_act=ACT_RELU6)
             stop = ft > b.i_dbn
             if not stop:
+                need = ft <= b.i_d
+                # the depthwise BatchNorm's backward rides in the project dgrad launch (column sums, grid barrier, the
+                # tile parked in TMEM); the native side falls back to dgrad + bn_bwd_apply where the grid has more tiles
+                # than SMs
+                tail = None
+                if need and self.bn_tail:
+                    tail = OC.bn_tail(b.dd_raw, b.bn_d.mean, b.bn_d.rstd, self._cnt(b.d_raw),
+                                      counter=p.scratch.view(b.o_ctr, 1), dgamma=b.bn_d.dgamma, dbeta=b.bn_d.dbeta,
+                                      frozen=not b.bn_d.trainable)
                 OC.conv_dgrad_raw(b.gp, b.dp_raw, self.w16(b.prefix + "project/kernel"), b.dpre_d, mode=2,
                                   aux=b.d_raw, bwd_scale=b.bn_d.scale, bwd_shift=b.bn_d.shift,
-                                  bwd_act=ACT_RELU6, stat_a=b.bn_d.sa, stat_b=b.bn_d.sb)
-                need = ft <= b.i_d
-                self._bn_bwd(b.bn_d, self._cnt(b.d_raw), b.c_d, need)
+                                  bwd_act=ACT_RELU6, stat_a=b.bn_d.sa, stat_b=b.bn_d.sb, tail=tail)
+                if tail is None:
+                    self._bn_bwd(b.bn_d, self._cnt(b.d_raw), b.c_d, need)
                 stop = not need
             if not stop:
-                self._bn_apply(b.dpre_d, b.d_raw, b.dd_raw, b.cexp)
+                if tail is None:
+                    self._bn_apply(b.dpre_d, b.d_raw, b.dd_raw, b.cexp)
                 dw_in, dw_bn = (b.e_raw, b.bn_e) if b.has_expand else (p.s_raw, p.bn_stem)
                 if b.i_d in tr:
                     self._side(K.dwconv_wgrad, b.gd, dw_in, b.dd_raw, self.gw(b.prefix + "depthwise/depthwise_kernel"),

@@ -54,7 +54,10 @@ class ChainExecutor(FusedExecutor):
                 k, s = sp.attrs["k"], sp.attrs["stride"]
                 ho, wo = (hh - k) // s + 1, (ww - k) // s + 1
                 y = torch.zeros(batch, ho, wo, cc, dtype=torch.bfloat16, device=dev)
-                p.steps.append(dict(kind="maxpool", layer=layer, x=cur, y=y, k=k, s=s, c=cc, dy=None))
+                # one byte per output element: which window element won (the backward pass reads it instead of
+                # re-comparing values)
+                arg = torch.zeros(batch, ho, wo, cc, dtype=torch.uint8, device=dev)
+                p.steps.append(dict(kind="maxpool", layer=layer, x=cur, y=y, k=k, s=s, c=cc, dy=None, arg=arg))
                 cur, cur_shape = y, (ho, wo, cc)
             elif sp.kind == "gap":
                 p.feat, p.feat_shape = cur, cur_shape
@@ -103,7 +106,7 @@ class ChainExecutor(FusedExecutor):
                 OC.conv_fprop_raw(st["geom"], st["x"], self.w16(name), st["y"], epi_shift=bias,
                                   epi_act=ACT_RELU if st["relu"] else ACT_NONE)
             else:
-                K.pool_fwd(st["x"], st["y"], st["c"], st["k"], st["s"], 0, True)
+                K.pool_fwd(st["x"], st["y"], st["c"], st["k"], st["s"], 0, True, argmax=st["arg"] if training else None)
         hl = p.head_layer
         hh, ww, cc = p.feat_shape
         wname, bname = hl.spec.params[0].name, hl.spec.params[1].name
@@ -139,7 +142,7 @@ class ChainExecutor(FusedExecutor):
                 if prev["kind"] == "conv" and prev["bias"] and pl.index in self.trainable:
                     db = self.gw(pl.spec.params[1].name)
                 K.pool_bwd(st["x"], st["y"], st["dy"], prev["dy"], st["c"], st["k"], st["s"], 0, True,
-                           relu_mask=(prev["kind"] == "conv" and prev["relu"]), stat_a=db)
+                           relu_mask=(prev["kind"] == "conv" and prev["relu"]), stat_a=db, argmax=st["arg"])
             else:
                 layer = st["layer"]
                 g = st["geom"]

@@ -327,6 +327,9 @@ def main_fed(argv: list) -> dict:
         return pretrained_model
 
     pretrained_model = pretrained(labeled_ds, path_data, train=toTrain)
+    # every rank pre-trained (or loaded) on its own: the weight-gradient kernels accumulate with atomics, so the copies
+    # differ in the last bits. The federation starts from ONE model: rank 0's.
+    strategy.sync_variables(pretrained_model.store)
 
     def create_tf_dataset_for_client_fn(client_id):
         return labeled_ds.skip(client_id * CLIENT_SIZE).take(CLIENT_SIZE)
