@@ -35,6 +35,10 @@ __device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&v)[8]) {
         v[2 * e + 1] = f.y;
     }
 }
+__device__ __forceinline__ void ldw8(const float* p, float (&v)[8]) {
+    const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+}
 __device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&v)[8]) {
     uint4 q;
     uint32_t* w = reinterpret_cast<uint32_t*>(&q);
@@ -74,6 +78,7 @@ __device__ __forceinline__ void block_reduce8_atomic(const float (&v)[8], float*
     }
 }
 
+template <bool kSmemW>
 __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
     pdl_enter();
     __shared__ float sh[256][9];
@@ -85,9 +90,18 @@ __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
         sc[e] = p.scale ? p.scale[c + e] : 1.f;
         sf[e] = p.scale ? p.shift[c + e] : 0.f;
     }
-    float wk[9][8];
+    // kSmemW (layers with many positions per thread): the 3x3 weights of every channel, fp32, in shared memory —
+    // 72 registers per thread less than holding this thread's 9 x 8 values, which is the difference between one
+    // and three resident blocks per SM. Small layers keep them in registers (no fill, no barrier).
+    extern __shared__ float wsm[];
+    float wk[kSmemW ? 1 : 9][8];
+    if (kSmemW) {
+        for (int i = threadIdx.x; i < 9 * p.C; i += blockDim.x) wsm[i] = __bfloat162float(p.w[i]);
+        __syncthreads();
+    } else {
 #pragma unroll
-    for (int t = 0; t < 9; ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
+        for (int t = 0; t < (kSmemW ? 1 : 9); ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
+    }
     float sa[8], sb[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) sa[e] = sb[e] = 0.f;
@@ -111,11 +125,18 @@ __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
                 if (wi < 0 || wi >= p.W) continue;
                 float xv[8];
                 load8(p.x + (static_cast<size_t>(b * p.H + hi) * p.W + wi) * p.x_pitch + p.x_coff + c, xv);
+                float wv[8];
+                if (kSmemW) {
+                    ldw8(wsm + (kh * 3 + kw) * p.C + c, wv);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) wv[e] = wk[kSmemW ? 0 : kh * 3 + kw][e];
+                }
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
                     float a = xv[e];
                     if (p.scale) a = __bfloat162float(__float2bfloat16_rn(apply_act(fmaf(a, sc[e], sf[e]), p.act)));
-                    acc[e] = fmaf(a, wk[kh * 3 + kw][e], acc[e]);
+                    acc[e] = fmaf(a, wv[e], acc[e]);
                 }
             }
         }
@@ -131,6 +152,7 @@ __global__ void __launch_bounds__(256) dw_fprop_kernel(DwArgs p) {
     if (p.stat_b) block_reduce8_atomic(sb, p.stat_b, sh, L);
 }
 
+template <bool kSmemW>
 __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
     pdl_enter();
     __shared__ float sh[256][9];
@@ -142,9 +164,18 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
         sc[e] = p.scale ? p.scale[c + e] : 1.f;
         sf[e] = p.scale ? p.shift[c + e] : 0.f;
     }
-    float wk[9][8];
+    // kSmemW (layers with many positions per thread): the 3x3 weights of every channel, fp32, in shared memory —
+    // 72 registers per thread less than holding this thread's 9 x 8 values, which is the difference between one
+    // and three resident blocks per SM. Small layers keep them in registers (no fill, no barrier).
+    extern __shared__ float wsm[];
+    float wk[kSmemW ? 1 : 9][8];
+    if (kSmemW) {
+        for (int i = threadIdx.x; i < 9 * p.C; i += blockDim.x) wsm[i] = __bfloat162float(p.w[i]);
+        __syncthreads();
+    } else {
 #pragma unroll
-    for (int t = 0; t < 9; ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
+        for (int t = 0; t < (kSmemW ? 1 : 9); ++t) load8(p.w + static_cast<size_t>(t) * p.C + c, wk[t]);
+    }
     float sa[8], sb[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) sa[e] = sb[e] = 0.f;
@@ -172,8 +203,15 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(DwArgs p) {
                 if (wo >= p.Wo) continue;
                 float dv[8];
                 load8(p.dy + (static_cast<size_t>(b * p.Ho + ho) * p.Wo + wo) * p.dy_pitch + p.dy_coff + c, dv);
+                float wv[8];
+                if (kSmemW) {
+                    ldw8(wsm + (kh * 3 + kw) * p.C + c, wv);
+                } else {
 #pragma unroll
-                for (int e = 0; e < 8; ++e) g[e] = fmaf(dv[e], wk[kh * 3 + kw][e], g[e]);
+                    for (int e = 0; e < 8; ++e) wv[e] = wk[kSmemW ? 0 : kh * 3 + kw][e];
+                }
+#pragma unroll
+                for (int e = 0; e < 8; ++e) g[e] = fmaf(dv[e], wv[e], g[e]);
             }
         }
         float xv[8];
@@ -250,14 +288,20 @@ static int fill(DwArgs& p, const idcb_conv_desc* d) {
     return 0;
 }
 
-static dim3 dw_grid(long long npos, int C, int pos_per_thread = 1) {
+// the shared-memory-weights variant pays a fill + barrier per block: worth it once every thread has several positions
+static bool dw_use_smem_weights(long long npos, int C) {
+    static const long long thr = [] { const char* e = getenv("IDCB_DW_SMEM_MIN_ITEMS"); return e ? atoll(e) : 1LL; }();
+    return npos * (C / 8) >= thr * 3 * 256 * num_sms();
+}
+
+static dim3 dw_grid(long long npos, int C, int pos_per_thread = 1, int blocks_per_sm = 0) {
     const int ppb = 256 / (C / 8);                          // positions per block pass (see DwLane)
     long long gx = ceil_div_ll(npos, 1LL * ppb * pos_per_thread);
     // every block ends with per-channel atomics (statistics / weight gradient): the number of blocks, not the
     // data volume, sets the contention on those few hundred addresses
     static const int cap_fd = [] { const char* e = getenv("IDCB_DW_BLOCKS_PER_SM"); int v = e ? atoi(e) : 2; return v > 0 ? v : 2; }();
-    static const int cap_w = [] { const char* e = getenv("IDCB_DW_WGRAD_BLOCKS_PER_SM"); int v = e ? atoi(e) : 1; return v > 0 ? v : 1; }();
-    const long long cap = 1LL * (pos_per_thread > 1 ? cap_w : cap_fd) * num_sms();
+    static const int cap_w = [] { const char* e = getenv("IDCB_DW_WGRAD_BLOCKS_PER_SM"); int v = e ? atoi(e) : 2; return v > 0 ? v : 2; }();
+    const long long cap = 1LL * (blocks_per_sm > 0 ? blocks_per_sm : (pos_per_thread > 1 ? cap_w : cap_fd)) * num_sms();
     if (gx > cap) gx = cap;
     if (gx < 1) gx = 1;
     return dim3(static_cast<unsigned>(gx), 1);
@@ -278,7 +322,10 @@ extern "C" int idcb_dwconv_fprop(const idcb_conv_desc* d, const void* x, const v
     p.scale = scale; p.shift = shift; p.act = act; p.stat_a = stat_sum; p.stat_b = stat_sq;
     const long long npos = 1LL * p.B * p.Ho * p.Wo;
     if (npos == 0) return 0;
-    IDCB_CHECK(launch_pdl(dw_fprop_kernel, dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream, p));
+    if (dw_use_smem_weights(npos, p.C))
+        IDCB_CHECK(launch_pdl(dw_fprop_kernel<true>, dw_grid(npos, p.C, 1, 3), 256, 9 * p.C * sizeof(float), (cudaStream_t)stream, p));
+    else
+        IDCB_CHECK(launch_pdl(dw_fprop_kernel<false>, dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream, p));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
@@ -296,7 +343,10 @@ extern "C" int idcb_dwconv_dgrad(const idcb_conv_desc* d, const void* dy, const 
     IDCB_REQUIRE(!(scale || stat_b) || x != nullptr, "dwconv_dgrad: x needed for the fused backward");
     const long long npos = 1LL * p.B * p.H * p.W;
     if (npos == 0) return 0;
-    IDCB_CHECK(launch_pdl(dw_dgrad_kernel, dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream, p));
+    if (dw_use_smem_weights(npos, p.C))
+        IDCB_CHECK(launch_pdl(dw_dgrad_kernel<true>, dw_grid(npos, p.C, 1, 3), 256, 9 * p.C * sizeof(float), (cudaStream_t)stream, p));
+    else
+        IDCB_CHECK(launch_pdl(dw_dgrad_kernel<false>, dw_grid(npos, p.C), 256, 0, (cudaStream_t)stream, p));
     IDCB_LAUNCH_CHECK();
     return 0;
 }
