@@ -529,6 +529,18 @@ __global__ void pool_bwd_kernel(PoolBwdArgs p) {
 __global__ void pack_input_kernel(const float* __restrict__ x, __nv_bfloat16* y, long long npos,
                                   int cin, int cpad) {
     pdl_enter();
+    if (cpad == 8 && cin <= 8) {
+        // one thread per position: cin scalar loads, one 16-byte store
+        for (long long pos = blockIdx.x * (long long)blockDim.x + threadIdx.x; pos < npos;
+             pos += (long long)gridDim.x * blockDim.x) {
+            float v[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) v[c] = c < cin ? x[pos * cin + c] : 0.f;
+            *reinterpret_cast<uint4*>(y + pos * 8) =
+                make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+        }
+        return;
+    }
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < npos * cpad;
          i += (long long)gridDim.x * blockDim.x) {
         const long long pos = i / cpad;
@@ -860,8 +872,7 @@ extern "C" int idcb_pool_bwd(const idcb_pool_desc* d, const void* x, const void*
 extern "C" int idcb_pack_input(const float* x, void* y, long long npos, int cin, int cpad,
                                void* stream) {
     if (npos == 0) return 0;
-    IDCB_CHECK(launch_pdl(pack_input_kernel, ew_grid(npos * cpad, 256), 256, 0, (cudaStream_t)stream, x, (bf)y, npos, cin,
-                                                                                  cpad));
+IDCB_CHECK(launch_pdl(pack_input_kernel, ew_grid(cpad == 8 && cin <= 8 ? npos : npos * cpad, 256), 256, 0, (cudaStream_t)stream, x, (bf)y, npos, cin, cpad));
     IDCB_LAUNCH_CHECK();
     return 0;
 }

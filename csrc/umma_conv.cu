@@ -677,6 +677,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         const int kb = kb0 + kb_local;
         const int tap = fdiv(kb, p.d_cb);
         const int cb = kb - tap * cblocks;
+        if (p.a_tma == 2) {
+            // 1x1 stride-1 convolution: the operand is a plain [M, channels] matrix -> tiled 2-D load
+            asm volatile(
+                "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                ::"r"(dst), "l"(reinterpret_cast<uint64_t>(&tmap_a)), "r"(bar), "r"(cb * kBK), "r"(m0) : "memory");
+            return;
+        }
         const int kh = fdiv(tap, p.d_kw);
         tma_load_im2col(dst, &tmap_a, bar, cb * kBK, t_w, t_h, t_n, tap - kh * p.KW, kh);
     };
@@ -1468,6 +1475,14 @@ static int prep_a_tma(CUtensorMap* tm, ConvArgs& a, bool per_tap_blocks) {
     const int c[4] = {-a.pad_l, -a.pad_t, pad_r - (a.KW - 1), pad_b - (a.KH - 1)};
     for (int i = 0; i < 4; ++i)
         if (c[i] < -128 || c[i] > 127) return 0;
+    static const int tiled_1x1 = [] { const char* e = getenv("IDCB_CONV_TMA_TILED_1X1"); return e ? atoi(e) : 1; }();
+    if (tiled_1x1 && taps == 1 && a.stride == 1 && a.pad_t == 0 && a.pad_l == 0 && a.Ho == a.H && a.Wo == a.W) {
+        // a 1x1 stride-1 convolution reads a plain [M, Cin] matrix (row pitch x_pitch): tiled 2-D boxes of 128 rows x 64
+        // channels, rows past M and channels past Cin zero-filled
+        if (make_tmap_2d_bf16(tm, a.x + a.x_coff, (uint64_t)a.M, (uint64_t)a.Cin, (uint64_t)a.x_pitch, kBM, kBK)) return 1;
+        a.a_tma = 2;
+        return 0;
+    }
     if (make_tmap_im2col_bf16(tm, a.x + a.x_coff, a.B, a.H, a.W, a.Cin, a.x_pitch, a.KH, a.KW, a.stride, a.pad_t,
                               a.pad_l, a.Ho, a.Wo, kBM))
         return 1;
