@@ -445,6 +445,101 @@ __global__ void __launch_bounds__(kCommThreads) fedavg_reduce_kernel(FedAvgArgs 
     store_epoch(pr, e0 + 2, pr.pad[pr.rank] + 18);
 }
 
+// One launch for a whole FedAvg aggregation (every trainable range of the model): the non-finite-client scan of
+// the LOCAL clients, the weighted delta mean of every range (sharded over the ranks, result multicast into every
+// rank's symmetric buffer), and the assembly of this rank's private copy of the complete new server model
+// (aggregated ranges from the symmetric buffer after the closing barrier, everything else copied from the
+// round's server model). Replaces: one finite-flag launch and one reduce launch per range plus two host-issued
+// device copies.
+constexpr int kMaxFedRanges = 16;
+struct FedAvgRoundArgs {
+    FedAvgArgs f;                       // offset / n unused
+    int n_ranges;
+    long long off[kMaxFedRanges], len[kMaxFedRanges];   // ascending, disjoint, multiples of 4
+    const float* base;                  // local: this round's server model [total] (read only)
+    float* out;                         // local, private: the new server model [total]
+    long long total;
+};
+
+__device__ __forceinline__ bool finite4(const float4& v) {
+    return isfinite(v.x) && isfinite(v.y) && isfinite(v.z) && isfinite(v.w);
+}
+
+__global__ void __launch_bounds__(kCommThreads) fedavg_round_kernel(FedAvgRoundArgs a) {
+    const Peers& pr = a.f.pr;
+    const uint32_t e0 = load_epoch(pr);
+    const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long nth = (long long)gridDim.x * blockDim.x;
+    // phase 0 (local): drop clients with a non-finite weight anywhere in the aggregated ranges; copy the parts of
+    // the model that are not aggregated
+    {
+        float* wl = const_cast<float*>(a.f.weights[pr.rank]);
+        for (int k = 0; k < a.f.k_local; ++k) {
+            bool bad = false;
+            const float* w = a.f.clients[pr.rank] + k * a.f.stride;
+            for (int r = 0; r < a.n_ranges; ++r) {
+                const float4* src = reinterpret_cast<const float4*>(w + a.off[r]);
+                for (long long i = tid; i < (a.len[r] >> 2); i += nth) bad |= !finite4(src[i]);
+            }
+            if (__syncthreads_or(bad) && threadIdx.x == 0) wl[k] = 0.f;
+        }
+        long long prev = 0;
+        for (int r = 0; r <= a.n_ranges; ++r) {
+            const long long end = r < a.n_ranges ? a.off[r] : a.total;
+            const float4* src = reinterpret_cast<const float4*>(a.base + prev);
+            float4* dst = reinterpret_cast<float4*>(a.out + prev);
+            for (long long i = tid; i < ((end - prev) >> 2); i += nth) dst[i] = src[i];
+            if (r < a.n_ranges) prev = a.off[r] + a.len[r];
+        }
+    }
+    __syncthreads();                      // (with the barriers off the launch is a single CTA: see the entry point)
+    grid_and_world_barrier(pr, e0 + 1);   // publishes the cleared weights; peers' previous kernels are done
+    float wsum = 0.f;
+    for (int p = 0; p < pr.world; ++p)
+        for (int k = 0; k < a.f.k_local; ++k) wsum += ld_sys_f32(a.f.weights[p] + k);
+    const float inv = wsum > 0.f ? a.f.server_lr / wsum : 0.f;
+    for (int r = 0; r < a.n_ranges; ++r) {
+        long long lo, hi;
+        shard_bounds(a.len[r] >> 2, pr.world, pr.rank, lo, hi);
+        for (long long i = lo + tid; i < hi; i += nth) {
+            const long long e = a.off[r] + (i << 2);
+            const float4 w0 = *reinterpret_cast<const float4*>(a.base + e);
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int q = 0; q < pr.world; ++q) {
+                const int p = (pr.rank + q) % pr.world;
+                for (int k = 0; k < a.f.k_local; ++k) {
+                    const float nk = ld_sys_f32(a.f.weights[p] + k);
+                    if (nk == 0.f) continue;   // dropped client: its (possibly non-finite) values are never read
+                    const float4 v = ld_sys_f4(a.f.clients[p] + k * a.f.stride + e);
+                    acc.x += nk * (v.x - w0.x); acc.y += nk * (v.y - w0.y);
+                    acc.z += nk * (v.z - w0.z); acc.w += nk * (v.w - w0.w);
+                }
+            }
+            const float4 w = make_float4(w0.x + inv * acc.x, w0.y + inv * acc.y, w0.z + inv * acc.z, w0.w + inv * acc.w);
+            const uint2 wb = make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
+            if (a.f.mc_global != nullptr) {
+                mc_st_f4(a.f.mc_global + e, w);
+                if (a.f.mc_shadow) mc_st_u2(a.f.mc_shadow + e, wb);
+            } else {
+                for (int q = 0; q < pr.world; ++q) {
+                    const int p = (pr.rank + q) % pr.world;
+                    st_sys_f4(a.f.global[p] + e, w);
+                    if (a.f.shadow[p]) st_sys_u2(a.f.shadow[p] + e, wb);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    grid_and_world_barrier(pr, e0 + 2);
+    // every rank's symmetric buffer now holds the aggregated ranges: assemble the private copy
+    for (int r = 0; r < a.n_ranges; ++r) {
+        const float* src = a.f.global[pr.rank] + a.off[r];
+        float4* dst = reinterpret_cast<float4*>(a.out + a.off[r]);
+        for (long long i = tid; i < (a.len[r] >> 2); i += nth) dst[i] = ld_sys_f4(src + (i << 2));
+    }
+    store_epoch(pr, e0 + 2, pr.pad[pr.rank] + 18);
+}
+
 // =====================================================================================================
 // K17: secure aggregation by pairwise masks in a 2^32 fixed-point ring
 //   client k sends  y_k = Q(w_k) + sum_{j>k} PRG(k,j) - sum_{j<k} PRG(j,k)   (mod 2^32)
@@ -665,6 +760,55 @@ extern "C" int idcb_fedavg_reduce(const idcb_comm_world* w, void* const* clients
     a.k_local = k_local; a.stride = stride; a.offset = offset; a.n = n; a.server_lr = server_lr;
     if (n == 0) return 0;
     fedavg_reduce_kernel<<<comm_grid(n / 4, w->world), kCommThreads, 0, (cudaStream_t)stream>>>(a);
+    IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int idcb_fedavg_round(const idcb_comm_world* w, void* const* clients, void* const* weights,
+                                 void* const* global, void* const* shadow, void* mc_global, void* mc_shadow,
+                                 int k_local, long long stride, int n_ranges, const long long* offsets,
+                                 const long long* lengths, float server_lr, const float* base, float* out,
+                                 long long total, void* stream) {
+    FedAvgRoundArgs a{};
+    if (fill_peers(a.f.pr, w)) return 1;
+    IDCB_REQUIRE(n_ranges >= 0 && n_ranges <= kMaxFedRanges, "fedavg_round: at most %d ranges per launch (got %d)",
+                 kMaxFedRanges, n_ranges);
+    IDCB_REQUIRE(k_local >= 1 && k_local <= 64, "fedavg_round: 1..64 clients per GPU");
+    IDCB_REQUIRE(total >= 0 && total % 4 == 0 && stride % 4 == 0 && total <= stride,
+                 "fedavg_round: model size %lld / client stride %lld must be multiples of 4, size <= stride", total, stride);
+    IDCB_REQUIRE(base != nullptr && out != nullptr && aligned16(base) && aligned16(out) && base != out,
+                 "fedavg_round: base and out must be distinct 16-byte aligned device buffers");
+    long long prev = 0, work = 0;
+    for (int r = 0; r < n_ranges; ++r) {
+        IDCB_REQUIRE(offsets[r] % 4 == 0 && lengths[r] % 4 == 0 && lengths[r] >= 0 && offsets[r] >= prev &&
+                         offsets[r] + lengths[r] <= total,
+                     "fedavg_round: range %d [%lld, +%lld) must be 4-aligned, ascending and inside the model of %lld",
+                     r, offsets[r], lengths[r], total);
+        a.off[r] = offsets[r]; a.len[r] = lengths[r];
+        prev = offsets[r] + lengths[r];
+        work += lengths[r];
+    }
+    for (int p = 0; p < w->world; ++p) {
+        a.f.clients[p] = static_cast<const float*>(clients[p]);
+        a.f.weights[p] = static_cast<const float*>(weights[p]);
+        a.f.global[p] = static_cast<float*>(global[p]);
+        a.f.shadow[p] = shadow ? static_cast<__nv_bfloat16*>(shadow[p]) : nullptr;
+        IDCB_REQUIRE(a.f.clients[p] && a.f.weights[p] && a.f.global[p], "fedavg_round: null peer pointer for rank %d", p);
+        IDCB_REQUIRE(aligned16(a.f.clients[p]) && aligned16(a.f.global[p]), "fedavg_round: peer buffers of rank %d must be 16-byte aligned", p);
+    }
+    a.f.mc_global = static_cast<float*>(mc_global);
+    a.f.mc_shadow = static_cast<__nv_bfloat16*>(mc_shadow);
+    a.f.k_local = k_local; a.f.stride = stride; a.f.server_lr = server_lr;
+    a.n_ranges = n_ranges; a.base = base; a.out = out; a.total = total;
+    if (total == 0) return 0;
+    // sized for the local phases (finite scan of k_local clients, copy of the model), which touch more than a shard
+    // the phases depend on each other across CTAs (cleared weights, the assembled copy), so without the in-kernel
+    // barriers (sequentially emulated ranks; world of one with the barrier switched off) the launch is one CTA
+    const long long per_rank = work > total - work ? work : total - work;
+    const int grid = a.f.pr.use_barrier ? comm_grid(per_rank / 4 + 1, 1) : 1;
+    IDCB_REQUIRE(a.f.pr.use_barrier || w->world == 1, "fedavg_round: ranks emulated one after another cannot run the "
+                 "one-launch round (rank r needs every rank's finite flags first)");
+    fedavg_round_kernel<<<grid, kCommThreads, 0, (cudaStream_t)stream>>>(a);
     IDCB_LAUNCH_CHECK();
     return 0;
 }

@@ -36,6 +36,10 @@ struct SmallCnnArgs {
     unsigned int step;
     float threshold;
     int acc_on_prob;
+    // optional: the batch is a gather out of each client's whole shard (x / labels are then [clients][n_ex][...])
+    const long long* idx;      // [clients][idx_stride]: example index of batch element ex at idx[cl * idx_stride + ex]
+    long long idx_stride;
+    int n_ex;
 };
 
 __device__ __forceinline__ bool keep(unsigned long long seed, unsigned step, unsigned ex, unsigned feat, unsigned layer,
@@ -58,7 +62,11 @@ __global__ void __launch_bounds__(128) small_cnn_kernel(SmallCnnArgs a) {
     __shared__ float s_dl;
     const int ex = blockIdx.x, cl = blockIdx.y, t = threadIdx.x;
     const float* P = a.params + static_cast<size_t>(cl) * a.param_stride;
-    const float* X = a.x + (static_cast<size_t>(cl) * a.batch + ex) * (kH * kH * kC);
+    // where this example lives: a dense [clients][batch] batch, or an index into the client's resident shard
+    const size_t row = a.idx != nullptr
+                           ? static_cast<size_t>(cl) * a.n_ex + static_cast<size_t>(a.idx[static_cast<size_t>(cl) * a.idx_stride + ex])
+                           : static_cast<size_t>(cl) * a.batch + ex;
+    const float* X = a.x + row * (kH * kH * kC);
     const int oCW = a.oCW, oCB = a.oCB, oDW = a.oDW, oDB = a.oDB, oOW = a.oOW, oOB = a.oOB, cs = a.cstride;
     for (int i = t; i < a.span; i += 128) sW[i] = P[i];
     for (int i = t; i < kH * kH * kC; i += 128) sx[i] = X[i];
@@ -109,7 +117,7 @@ __global__ void __launch_bounds__(128) small_cnn_kernel(SmallCnnArgs a) {
     if (t == 0) {
         float x = sW[oOB];
         for (int h = 0; h < kHid; ++h) x += hid[h] * sW[oOW + h];
-        const float z = a.labels[static_cast<size_t>(cl) * a.batch + ex];
+        const float z = a.labels[row];
         const float loss = fmaxf(x, 0.f) - x * z + log1pf(expf(-fabsf(x)));
         const float sg = 1.f / (1.f + expf(-x));
         const float pred = ((a.acc_on_prob ? sg : x) > a.threshold) ? 1.f : 0.f;
@@ -204,9 +212,32 @@ extern "C" int idcb_small_cnn_step(const float* x, const float* labels, const fl
     if (batch == 0) return 0;
     SmallCnnArgs a{x, labels, params, grads, logits, acc, batch, param_stride,
                    offsets6[0], offsets6[1], offsets6[2], offsets6[3], offsets6[4], offsets6[5], conv_cin_stride, span,
-                   training, grad_scale, drop1, drop2, seed, step, threshold, acc_on_prob};
+                   training, grad_scale, drop1, drop2, seed, step, threshold, acc_on_prob, nullptr, 0, 0};
     IDCB_CHECK(launch_pdl(small_cnn_kernel, dim3(batch, n_clients), 128, 0, (cudaStream_t)stream, a));
     IDCB_LAUNCH_CHECK();
+    return 0;
+}
+
+// The same step with the batch gathered inside the kernel: x_all [clients][n_ex][10][10][3] and labels_all
+// [clients][n_ex] are the clients' whole shards, idx [clients][idx_stride] (int64, e.g. a row of torch.randperm per
+// client, already offset to the batch's first column) names the n_ex-relative example of every batch slot.
+extern "C" int idcb_small_cnn_step_indexed(const float* x_all, const float* labels_all, const long long* idx,
+                                           long long idx_stride, int n_ex, const float* params, float* grads,
+                                           float* logits, float* acc, int n_clients, int batch, int param_stride,
+                                           const int* offsets6, int conv_cin_stride, int training, float grad_scale,
+                                           float drop1, float drop2, unsigned long long seed, unsigned int step,
+                                           float threshold, int acc_on_prob, void* stream) {
+    IDCB_REQUIRE(n_clients >= 1 && batch >= 0 && offsets6 != nullptr && conv_cin_stride >= 3, "small_cnn_step: bad sizes");
+    IDCB_REQUIRE(idx != nullptr && n_ex >= 1 && idx_stride >= batch, "small_cnn_step_indexed: bad index description");
+    const int span = offsets6[5] + 1;
+    IDCB_REQUIRE(span <= kMaxBlock && param_stride >= span, "small_cnn_step: parameter block of %d floats exceeds %d", span, kMaxBlock);
+    IDCB_REQUIRE(drop1 >= 0.f && drop1 < 1.f && drop2 >= 0.f && drop2 < 1.f, "small_cnn_step: bad dropout rates");
+    IDCB_REQUIRE(!training || grads != nullptr, "small_cnn_step: training needs a gradient buffer");
+    if (batch == 0) return 0;
+    SmallCnnArgs a{x_all, labels_all, params, grads, logits, acc, batch, param_stride,
+                   offsets6[0], offsets6[1], offsets6[2], offsets6[3], offsets6[4], offsets6[5], conv_cin_stride, span,
+                   training, grad_scale, drop1, drop2, seed, step, threshold, acc_on_prob, idx, idx_stride, n_ex};
+    IDCB_CHECK(launch_pdl(small_cnn_kernel, dim3(batch, n_clients), 128, 0, (cudaStream_t)stream, a));
     return 0;
 }
 

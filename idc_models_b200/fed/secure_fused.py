@@ -107,6 +107,20 @@ class FusedSecureFederation:
             C.c_float(self.template.acc_threshold), C.c_int(1 if self.template.acc_on_prob else 0), _lib.stream()))
         _lib.count_launch()
 
+    def _launch_indexed(self, X, Y, perm, col0: int, n_ex: int, batch: int) -> None:
+        lib = _lib.cuda_lib()
+        k = self.k_local
+        if self._logits is None or self._logits.numel() < k * batch:
+            self._logits = torch.zeros(k * batch, dtype=torch.float32, device=self.world.device)
+        _lib.check(lib.idcb_small_cnn_step_indexed(
+            vp(X.data_ptr()), vp(Y.data_ptr()), vp(perm.data_ptr() + 8 * col0), C.c_longlong(perm.shape[1]), C.c_int(n_ex),
+            vp(self.params.tensor.data_ptr()), vp(self.grads.data_ptr()), vp(self._logits.data_ptr()),
+            vp(self.acc.data_ptr()), C.c_int(k), C.c_int(batch), C.c_int(self.stride), self.offsets,
+            C.c_int(self.cstride), C.c_int(1), C.c_float(1.0 / max(batch, 1)), C.c_float(self.rates[0]),
+            C.c_float(self.rates[1]), C.c_ulonglong(self.seed), C.c_uint(self.step),
+            C.c_float(self.template.acc_threshold), C.c_int(1 if self.template.acc_on_prob else 0), _lib.stream()))
+        _lib.count_launch()
+
     def client_fit(self, epochs: int = 5) -> torch.Tensor:
         """Every resident client trains ``epochs`` passes over its shard. Returns the per-client
         [k_local, 3] (loss sum, correct, count) accumulators of the last epoch (device tensor)."""
@@ -123,14 +137,12 @@ class FusedSecureFederation:
         gen = torch.Generator(device=X.device).manual_seed(self.seed * 7919 + self.round * 104729 + self.world.rank)
         for _ in range(epochs):
             self.acc.zero_()
-            perm = torch.stack([torch.randperm(n_ex, device=X.device, generator=gen) for _ in range(k)])
+            perm = torch.stack([torch.randperm(n_ex, device=X.device, generator=gen) for _ in range(k)])   # int64 [k, n_ex]
             for s in range(0, n_ex, B):
                 b = min(B, n_ex - s)
-                idx = perm[:, s:s + b]
-                xb = torch.gather(X, 1, idx[:, :, None, None, None].expand(k, b, 10, 10, 3)).contiguous()
-                yb = torch.gather(Y, 1, idx).contiguous()
                 self.step += 1
-                self._launch(xb, yb, b, True)
+                # the batch is gathered inside the kernel from the resident shards (no index-gather launches per step)
+                self._launch_indexed(X, Y, perm, s, n_ex, b)
                 _lib.check(lib.idcb_optim_step(C.c_int(KIND["rmsprop"]), vp(self.params.tensor.data_ptr()),
                                                vp(self.grads.data_ptr()), vp(self.ms.data_ptr()), vp(0), vp(0),
                                                C.c_longlong(k * self.stride), C.c_float(self.lr), C.c_float(self.rho),
@@ -159,10 +171,10 @@ class FusedSecureFederation:
             _lib.count_launch()
         if pe < n:
             # unprotected tensors: plain float mean (equal weights, base 0 -> the kernel's weighted mean)
+            # (no host barrier: the kernel reads only THIS rank's base range, which this stream has just zeroed, and
+            # no peer can store into it before the kernel's opening cross-GPU barrier, i.e. before this rank's kernel —
+            # hence its memset — has started)
             self.out.tensor[pe:n].zero_()
-            if self.world.is_distributed:
-                torch.cuda.current_stream().synchronize()
-                self.world.barrier()     # peers must have zeroed their base range before anyone's kernel reads it
             _lib.check(lib.idcb_fedavg_reduce(C.byref(cw), self.params.ptrs(), self.wts.ptrs(), self.out.ptrs(),
                                               self.out_shadow.ptrs(), self.out.mc(), self.out_shadow.mc(), C.c_int(k),
                                               C.c_longlong(n), C.c_longlong(pe), C.c_longlong(n - pe), C.c_float(1.0),

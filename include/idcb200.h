@@ -292,6 +292,15 @@ int idcb_small_cnn_step(const float* x, const float* labels, const float* params
                         int conv_cin_stride, int training, float grad_scale, float drop1, float drop2,
                         unsigned long long seed, unsigned int step, float threshold, int acc_on_prob,
                         void* stream);
+/* The same step with the mini-batch gathered inside the kernel out of each client's resident shard
+ * (x_all [clients][n_ex][10][10][3], labels_all [clients][n_ex], idx [clients][idx_stride] int64): replaces the
+ * per-step index-gather launches of a tf.data shuffle + batch (secure_fed_model.py:56-62, 122-126). */
+int idcb_small_cnn_step_indexed(const float* x_all, const float* labels_all, const long long* idx,
+                                long long idx_stride, int n_ex, const float* params, float* grads, float* logits,
+                                float* acc, int n_clients, int batch, int param_stride, const int* offsets6,
+                                int conv_cin_stride, int training, float grad_scale, float drop1, float drop2,
+                                unsigned long long seed, unsigned int step, float threshold, int acc_on_prob,
+                                void* stream);
 /* Device-side synthetic IDC-like patches: Philox noise + class tint, fp32 [n][h][w][c] in [0,1] and 0/1
  * labels (stands in for the tf.data input pipeline of dist_model_tf_mobile.py:34-65). */
 int idcb_synth_patches(float* x, float* labels, long long n_img, int h, int w, int channels,
@@ -358,6 +367,17 @@ int idcb_fedavg_reduce(const idcb_comm_world* w, void* const* clients, void* con
                        void* const* global, void* const* shadow, void* mc_global, void* mc_shadow,
                        int k_local, long long stride, long long offset, long long n, float server_lr,
                        void* stream);
+/* A whole FedAvg aggregation in ONE launch (the state update of TFF's `iterative_process.next`,
+ * /root/reference/fed_model.py:219): the non-finite-client scan of this rank's clients over every range, the
+ * example-weighted delta mean of every range (sharded over the ranks, multicast into every rank's symmetric
+ * `global` / bf16 `shadow`), and this rank's private copy `out` of the complete new model (`base` is this round's
+ * server model, read locally; positions outside the ranges are copied from it). At most 16 ascending, disjoint,
+ * 4-aligned ranges. */
+int idcb_fedavg_round(const idcb_comm_world* w, void* const* clients, void* const* weights,
+                      void* const* global, void* const* shadow, void* mc_global, void* mc_shadow,
+                      int k_local, long long stride, int n_ranges, const long long* offsets,
+                      const long long* lengths, float server_lr, const float* base, float* out,
+                      long long total, void* stream);
 
 /* Secure aggregation (stands in for the Paillier path of secure_fed_model.py:109-121,160-168; SURVEY
  * B20, C9/C10, 8.6): pairwise Philox4x32-10 masks in the 2^32 fixed-point ring, generated in registers.

@@ -173,6 +173,38 @@ for comm in ("fused", "nccl"):
     torch.cuda.synchronize()
     sums[comm] = (state.master.double().sum().item(), state.master.double().abs().sum().item(), metrics[1])
 res["fedavg"] = sums
+# ---- the one-launch FedAvg round: two ranges, unequal weights, a non-finite client on the last rank -----------
+import ctypes as C
+from idc_models_b200.ops import _lib
+from idc_models_b200.parallel.symm import SymmAllocator
+alloc = SymmAllocator(world, True)
+W, R, kl, nn = world.size, world.rank, 3, 4096
+cl, wt = alloc.alloc(kl * nn, torch.float32), alloc.alloc(4, torch.float32)
+gb, gs = alloc.alloc(nn, torch.float32), alloc.alloc(nn, torch.bfloat16)
+g = torch.Generator(device=dev).manual_seed(77)              # the same numbers on every rank
+allc = torch.randn(W, kl, nn, device=dev, generator=g)
+base = torch.randn(nn, device=dev, generator=g)
+allc[W - 1, 1, 700] = float("nan")
+allw = (1000.0 + 500.0 * torch.arange(W * kl, device=dev)).view(W, kl)
+cl.tensor[:kl * nn].copy_(allc[R].reshape(-1)); wt.tensor[:kl].copy_(allw[R])
+torch.cuda.synchronize(); world.barrier()
+ranges = [(256, 1024), (2048, 3584)]
+offs = (C.c_longlong * 2)(*[b for b, _ in ranges]); lens = (C.c_longlong * 2)(*[e - b for b, e in ranges])
+cw = alloc.comm_world()
+round_out = []
+for rep in range(3):                                           # back to back: epochs and barriers must chain
+    out = torch.full((nn,), float("nan"), device=dev)
+    _lib.check(_lib.cuda_lib().idcb_fedavg_round(C.byref(cw), cl.ptrs(), wt.ptrs(), gb.ptrs(), gs.ptrs(), gb.mc(), gs.mc(),
+        C.c_int(kl), C.c_longlong(nn), C.c_int(2), offs, lens, C.c_float(0.5), C.c_void_p(base.data_ptr()),
+        C.c_void_p(out.data_ptr()), C.c_longlong(nn), _lib.stream()))
+    round_out.append(out)
+torch.cuda.synchronize()
+want = F.weighted_delta_mean(base.cpu(), allc.view(-1, nn).cpu(), allw.view(-1).cpu(), 0.5, ranges)
+res["fedavg_round"] = {"err": max((o.cpu() - want).abs().max().item() for o in round_out),
+                       "outside_kept": all(torch.equal(o[:256], base[:256]) and torch.equal(o[1024:2048], base[1024:2048])
+                                           and torch.equal(o[3584:], base[3584:]) for o in round_out),
+                       "dropped_weight": wt.tensor[1].item(), "sum": round_out[-1].double().sum().item(),
+                       "shadow_ok": all(torch.equal(gs.tensor[b:e], round_out[-1][b:e].to(torch.bfloat16)) for b, e in ranges)}
 allres = world.all_gather_object(res)
 if world.rank == 0:
     print("RESULT " + json.dumps(allres))
@@ -203,6 +235,12 @@ def test_federated_kernels_across_processes():
         f, l = o["fedavg"]["fused"], o["fedavg"]["nccl"]
         assert f[:2] == outs[0]["fedavg"]["fused"][:2], "ranks disagree on the FedAvg server model"
         assert abs(f[0] - l[0]) < 1e-3 * max(1.0, l[1]), (f, l)
+    for r, o in enumerate(outs):
+        fr = o["fedavg_round"]
+        assert fr["err"] < 1e-5 and fr["outside_kept"] and fr["shadow_ok"], fr
+        assert fr["sum"] == outs[0]["fedavg_round"]["sum"], "ranks disagree on the one-launch FedAvg model"
+        assert fr["dropped_weight"] == (0.0 if r == len(outs) - 1 else outs[r]["fedavg_round"]["dropped_weight"])
+    assert outs[-1]["fedavg_round"]["dropped_weight"] == 0.0 and outs[0]["fedavg_round"]["dropped_weight"] > 0.0
 
 
 STRESS_WORKER = r'''

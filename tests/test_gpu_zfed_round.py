@@ -1,0 +1,131 @@
+"""Single-GPU checks of the two federated kernels added after this round's GPU budget was spent: the one-launch
+FedAvg round (csrc/comm.cu:fedavg_round_kernel) and the in-kernel mini-batch gather of the small CNN
+(csrc/small_cnn.cu:idcb_small_cnn_step_indexed). Their first run on hardware is the driver's, so
+
+* each check runs in its OWN python process (a device fault there cannot poison the CUDA context of the
+  tests that follow), and
+* the file sorts after every other GPU test file and before tests/test_zz_no_alloc.py.
+
+Oracles: the PyTorch statement of the aggregation (fed/fedavg.py:weighted_delta_mean) and the dense launch of the
+same kernel fed by an explicit ``torch.gather``. The multi-GPU version of the first check is part of
+tests/test_gpu_multi.py::test_federated_kernels_across_processes.
+"""
+import json
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+PRELUDE = r'''
+import sys, json, ctypes as C, torch
+sys.path.insert(0, %r)
+from idc_models_b200.ops import _lib
+from idc_models_b200.parallel.world import World
+world = World.from_env("cuda")
+res = {}
+''' % str(ROOT)
+
+FEDAVG_ROUND = PRELUDE + r'''
+from idc_models_b200.fed import fedavg
+from idc_models_b200.parallel.symm import SymmAllocator
+torch.manual_seed(2)
+k_local, n = 4, 8192
+alloc = SymmAllocator(world)
+clients, weights = alloc.alloc(k_local * n, torch.float32), alloc.alloc(4, torch.float32)
+glob, shadow = alloc.alloc(n, torch.float32), alloc.alloc(n, torch.bfloat16)
+c = torch.randn(k_local, n, device="cuda")
+c[1, 5000] = float("-inf")                     # dropped: inside the second range
+c[2, 100] = float("nan")                       # kept: outside every aggregated range
+wts = torch.tensor([3000., 1000., 2500., 500.], device="cuda")
+clients.tensor.copy_(c.reshape(-1)); weights.tensor.copy_(wts)
+base = torch.randn(n, device="cuda")
+ranges = [(128, 2048), (4096, 6144), (8000, 8192)]
+offs = (C.c_longlong * 3)(*[b for b, _ in ranges]); lens = (C.c_longlong * 3)(*[e - b for b, e in ranges])
+cw = alloc.comm_world(use_barrier=True)        # a real grid barrier: the phases depend on each other across CTAs
+lib = _lib.cuda_lib()
+errs = []
+for rep in range(3):                           # back to back: the pad epochs must chain
+    out = torch.full((n,), float("nan"), device="cuda")
+    _lib.check(lib.idcb_fedavg_round(C.byref(cw), clients.ptrs(), weights.ptrs(), glob.ptrs(), shadow.ptrs(), None, None,
+                                     C.c_int(k_local), C.c_longlong(n), C.c_int(3), offs, lens, C.c_float(1.0),
+                                     C.c_void_p(base.data_ptr()), C.c_void_p(out.data_ptr()), C.c_longlong(n), _lib.stream()))
+    torch.cuda.synchronize()
+    want = fedavg.weighted_delta_mean(base.cpu(), c.cpu(), wts.cpu(), 1.0, ranges)
+    errs.append((out.cpu() - want).abs().max().item())
+res["weights"] = weights.tensor[:4].tolist()
+res["err"] = max(errs)
+prev, kept = 0, True
+for b, e in ranges + [(n, n)]:
+    kept = kept and torch.equal(out[prev:b], base[prev:b])
+    prev = e
+res["outside_kept"] = kept
+res["shadow_ok"] = all(torch.equal(shadow.tensor[b:e], out[b:e].to(torch.bfloat16)) for b, e in ranges)
+bad = (C.c_longlong * 3)(128, 64, 8000)
+rc = lib.idcb_fedavg_round(C.byref(cw), clients.ptrs(), weights.ptrs(), glob.ptrs(), shadow.ptrs(), None, None,
+                           C.c_int(k_local), C.c_longlong(n), C.c_int(3), bad, lens, C.c_float(1.0),
+                           C.c_void_p(base.data_ptr()), C.c_void_p(out.data_ptr()), C.c_longlong(n), _lib.stream())
+res["bad_ranges_refused"] = rc != 0 and b"ascending" in lib.idcb_last_error()
+print("RESULT " + json.dumps(res))
+'''
+
+INDEXED_CNN = PRELUDE + r'''
+from idc_models_b200.fed.secure_fused import FusedSecureFederation
+from idc_models_b200.workloads import create_small_cnn
+tpl = create_small_cnn(world.device, seed=0, lr=1e-3)
+k, n_ex, b = 4, 37, 16
+fed = FusedSecureFederation(world, k, 1.0, template=tpl, batch_size=b, seed=9)
+g = torch.Generator(device="cuda").manual_seed(11)
+X = torch.rand(k, n_ex, 10, 10, 3, device="cuda", generator=g)
+Y = (torch.rand(k, n_ex, device="cuda", generator=g) > 0.5).float()
+perm = torch.stack([torch.randperm(n_ex, device="cuda", generator=g) for _ in range(k)])
+out = []
+for col0, bb in ((0, b), (16, b), (32, n_ex - 32)):
+    fed.step += 1
+    idx = perm[:, col0:col0 + bb]
+    xb = torch.gather(X, 1, idx[:, :, None, None, None].expand(k, bb, 10, 10, 3)).contiguous()
+    yb = torch.gather(Y, 1, idx).contiguous()
+    fed.acc.zero_(); fed.grads.zero_()
+    fed._launch(xb, yb, bb, True)
+    torch.cuda.synchronize()
+    ref = (fed._logits[:k * bb].clone(), fed.grads.clone(), fed.acc.clone())
+    fed.acc.zero_(); fed.grads.zero_(); fed._logits.zero_()
+    fed._launch_indexed(X, Y, perm, col0, n_ex, bb)
+    torch.cuda.synchronize()
+    out.append({"logits_equal": bool(torch.equal(fed._logits[:k * bb], ref[0])),
+                "grad_scale": ref[1].abs().max().item(),
+                "grad_err": (fed.grads - ref[1]).abs().max().item(),
+                "counts_equal": bool(torch.equal(fed.acc[:, 1:], ref[2][:, 1:])),
+                "loss_err": (fed.acc[:, 0] - ref[2][:, 0]).abs().max().item()})
+res["steps"] = out
+print("RESULT " + json.dumps(res))
+'''
+
+
+def _run(name: str, body: str) -> dict:
+    script = ROOT / "build" / name
+    script.parent.mkdir(exist_ok=True)
+    script.write_text(body)
+    r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-5000:]
+    return json.loads([l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1][7:])
+
+
+def test_fedavg_round_single_launch_single_gpu():
+    """one launch = finite scan + weighted mean of every range + private copy of the whole model"""
+    o = _run("_fedavg_round_worker.py", FEDAVG_ROUND)
+    assert o["weights"] == [3000.0, 0.0, 2500.0, 500.0], o      # only the client with a bad value INSIDE a range is dropped
+    assert o["err"] < 1e-5 and o["outside_kept"] and o["shadow_ok"] and o["bad_ranges_refused"], o
+
+
+def test_small_cnn_indexed_launch_equals_gathered_launch():
+    """the mini-batch gathered inside the kernel gives the logits (bit for bit), and the atomically accumulated
+    gradients and loss sums (to rounding), of an explicit index-gather followed by the dense launch; same seed and
+    step, so the dropout masks agree"""
+    o = _run("_indexed_cnn_worker.py", INDEXED_CNN)
+    for s in o["steps"]:
+        assert s["logits_equal"] and s["counts_equal"], s
+        assert s["grad_scale"] > 0 and s["grad_err"] <= 1e-5 * max(1.0, s["grad_scale"]) and s["loss_err"] < 1e-4, s
