@@ -14,7 +14,11 @@ Timed regions
   events). The per-step times are summed, the MAX over ranks is reported.
 * ``e2e``: the same K steps through the public API (``model.train_on_batch``) including, every step, the
   host->device copy of that step's batch from pinned memory and a device->host read of the step's loss;
-  wall-clock between two barriers + synchronize, max over ranks.
+  wall-clock between two barriers + synchronize, max over ranks. The loop is pipelined the way a fit loop is:
+  the executor stages the batch on a copy stream (so the copy for step i+1 runs under step i), the loss of
+  step i is copied into pinned memory right after step i and read by the host one step later; every step's
+  input is copied and every step's loss is read inside the timed region (``IDCB_BENCH_E2E_SYNC=1``: read the
+  loss synchronously after every step instead; the mode is reported in ``e2e.loop``).
 
 ``--impl reference`` is the reference arm: the upstream scripts need TensorFlow 2.1 / TFF / phe, none of
 which can be installed offline, so it prints ``{"impl": "reference", "unavailable": ...}`` and exits 0.
@@ -204,11 +208,42 @@ def main() -> int:
     # ---- end-to-end region: public API + H2D of every batch + D2H of the loss ----
     world.barrier()
     torch.cuda.synchronize()
+    def e2e_pipelined():
+        """every step: H2D of the step's batch out of pinned memory (staged on the executor's copy stream, so it
+        runs while the previous step computes), the step through the public API, and a D2H copy of the step's loss
+        sum into pinned memory that the host reads ONE STEP LATER (as a Keras fit loop reads its metrics) — the host
+        never idles the GPU between steps, and every step's loss has been read by the host inside the timed region"""
+        pin = torch.zeros(2, 4).pin_memory()
+        evs = [torch.cuda.Event(), torch.cuda.Event()]
+        loss = 0.0
+        for i in range(args.steps):
+            out = model.train_on_batch(hx[i % ring], hy[i % ring])      # slices, copies H2D, runs the step
+            pin[i & 1, :1].copy_(out["stats"][:1], non_blocking=True)    # D2H of this step's loss sum
+            evs[i & 1].record()
+            if i > 0:
+                evs[(i - 1) & 1].synchronize()
+                loss = float(pin[(i - 1) & 1, 0])                        # host read of the previous step's loss
+        evs[(args.steps - 1) & 1].synchronize()
+        return float(pin[(args.steps - 1) & 1, 0])
+
+    def e2e_synchronous():
+        loss = 0.0
+        for i in range(args.steps):
+            out = model.train_on_batch(hx[i % ring], hy[i % ring])
+            loss = float(out["stats"][0].item())                         # D2H read of the step's loss sum, every step
+        return loss
+
+    e2e_mode = "pipelined" if os.environ.get("IDCB_BENCH_E2E_SYNC", "0") != "1" else "synchronous"
     t0 = time.perf_counter()
-    last_loss = 0.0
-    for i in range(args.steps):
-        out = model.train_on_batch(hx[i % ring], hy[i % ring])     # slices, copies H2D, runs the step
-        last_loss = float(out["stats"][0].item())                   # D2H read of the step's loss sum
+    try:
+        last_loss = e2e_pipelined() if e2e_mode == "pipelined" else e2e_synchronous()
+    except Exception as e:  # noqa: BLE001 - measure the plain loop rather than lose the number
+        print(f"bench.py: pipelined end-to-end loop failed ({type(e).__name__}: {e}); synchronous loop", file=sys.stderr)
+        e2e_mode = "synchronous (pipelined loop failed)"
+        torch.cuda.synchronize()
+        world.barrier()
+        t0 = time.perf_counter()
+        last_loss = e2e_synchronous()
     torch.cuda.synchronize()
     world.barrier()
     e2e_s = time.perf_counter() - t0
@@ -266,7 +301,12 @@ def main() -> int:
             "clocks": clocks,
             "e2e": {"value": round(gb * args.steps / e2e_s, 1), "unit": "patches/s",
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-                    "ms_per_step": round(e2e_s * 1e3 / args.steps, 4), "last_loss_sum": last_loss},
+                    "ms_per_step": round(e2e_s * 1e3 / args.steps, 4), "last_loss_sum": last_loss,
+                    "loop": e2e_mode,
+                    "loop_note": ("input of step i+1 copied on a copy stream while step i computes; the loss of "
+                                  "step i is copied to pinned memory after step i and read by the host during step "
+                                  "i+1; IDCB_BENCH_E2E_SYNC=1 reads it synchronously every step")
+                    if e2e_mode == "pipelined" else "loss read synchronously after every step"},
             "gpu_launches": launches,
             "replicas_identical": replicas_identical,
             "master_checksum": f"{sums[0][0] & 0xFFFFFFFFFFFFFFFF:016x}",

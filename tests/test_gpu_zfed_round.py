@@ -1,6 +1,7 @@
-"""Single-GPU checks of the two federated kernels added after this round's GPU budget was spent: the one-launch
-FedAvg round (csrc/comm.cu:fedavg_round_kernel) and the in-kernel mini-batch gather of the small CNN
-(csrc/small_cnn.cu:idcb_small_cnn_step_indexed). Their first run on hardware is the driver's, so
+"""Single-GPU checks of what was added after this round's GPU budget was spent: the one-launch FedAvg round
+(csrc/comm.cu:fedavg_round_kernel), the in-kernel mini-batch gather of the small CNN
+(csrc/small_cnn.cu:idcb_small_cnn_step_indexed) and the copy-stream input stager of the fused executors
+(models/fused/common.py:InputStager). Their first run on hardware is the driver's, so
 
 * each check runs in its OWN python process (a device fault there cannot poison the CUDA context of the
   tests that follow), and
@@ -105,6 +106,41 @@ print("RESULT " + json.dumps(res))
 '''
 
 
+ASYNC_STAGE = PRELUDE + r'''
+from idc_models_b200.models import applications as apps
+from idc_models_b200.models.applications import build_transfer_model
+from idc_models_b200.optim.optimizers import SGD
+torch.manual_seed(0)
+out = {}
+for name in ("small_cnn", "mobilenet_v2_tiny"):
+    if name == "small_cnn":
+        m = apps.Sequential([apps.Conv2D(32, (3, 3), activation="relu", input_shape=(10, 10, 3), strides=2),
+                             apps.MaxPooling2D((2, 2)), apps.Dropout(0.0), apps.Flatten(),
+                             apps.Dense(8, activation="relu"), apps.Dropout(0.0), apps.Dense(1)],
+                            device="cuda", seed=3, executor="fused")
+        shape = (32, 10, 10, 3)
+    else:
+        m = build_transfer_model(name, (50, 50, 3), 1, device="cuda", seed=0)
+        shape = (16, 50, 50, 3)
+    m.compile(optimizer=SGD(0.0), loss="bce", metrics=["accuracy"])
+    ex = m.executor
+    ex.use_graphs = name != "small_cnn"
+    xs = [torch.rand(*shape).pin_memory() for _ in range(7)]
+    y = (torch.rand(shape[0]) > 0.5).float().pin_memory()
+    assert ex.async_stage
+    got = [ex.eval_batch(x, y)[1] for x in xs]            # back to back, no synchronisation: both staging buffers cycle
+    torch.cuda.synchronize()
+    staged = hasattr(ex._get_plan(shape[0]), "_stager")
+    want = [ex.eval_batch(x.cuda(), y.cuda())[1] for x in xs]
+    torch.cuda.synchronize()
+    err = max((a - b).abs().max().item() for a, b in zip(got, want))
+    spread = (want[0] - want[1]).abs().max().item()       # different batches do give different logits
+    out[name] = {"staged": staged, "err": err, "spread": spread, "scale": max(w.abs().max().item() for w in want)}
+res["models"] = out
+print("RESULT " + json.dumps(res))
+'''
+
+
 def _run(name: str, body: str) -> dict:
     script = ROOT / "build" / name
     script.parent.mkdir(exist_ok=True)
@@ -129,3 +165,14 @@ def test_small_cnn_indexed_launch_equals_gathered_launch():
     for s in o["steps"]:
         assert s["logits_equal"] and s["counts_equal"], s
         assert s["grad_scale"] > 0 and s["grad_err"] <= 1e-5 * max(1.0, s["grad_scale"]) and s["loss_err"] < 1e-4, s
+
+
+def test_pinned_host_input_through_the_copy_stream_stager():
+    """a pinned host batch staged on the copy stream (double-buffered, moved into the graph's input buffer by a
+    device-to-device copy) gives the logits of the same batch passed as a device tensor, for a run of different
+    batches issued back to back, eagerly and under CUDA-graph replay"""
+    o = _run("_async_stage_worker.py", ASYNC_STAGE)
+    for name, r in o["models"].items():
+        assert r["staged"], name
+        assert r["spread"] > 0, (name, r)
+        assert r["err"] <= 1e-5 * max(1.0, r["scale"]), (name, r)
