@@ -22,6 +22,7 @@
 #include <vector>
 
 #include "host_common.h"
+#include "idcb200_host.h"
 
 namespace {
 

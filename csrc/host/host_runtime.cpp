@@ -5,6 +5,7 @@
 #include <cstring>
 
 #include "host_common.h"
+#include "idcb200_host.h"
 
 namespace idcbh {
 static thread_local char g_err[1024] = "";

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "host_common.h"
+#include "idcb200_host.h"
 
 extern "C" int idcbh_schedule_clients(int n_clients, const long long* cost, int n_ranks, int* rank_of_client,
                                       long long* load_of_rank) {

@@ -9,6 +9,7 @@
 
 #include "../philox.cuh"
 #include "host_common.h"
+#include "idcb200_host.h"
 
 extern "C" {
 
