@@ -1,4 +1,4 @@
-/* idc_models_b200 — C ABI of the host-only library (idc_models_b200/_native/libidcb200_host.so, csrc/host/*.cpp).
+/* idc_models_b200 — C ABI of the host-only library (idc_models_b200/_native/libidcb200_host.so, the sources under csrc/host).
  *
  * No CUDA dependency: loadable on a CPU-only box. Everything the reference gets from native code inside
  * TensorFlow / h5py / phe on the HOST side lives here: the tf.data runtime (shuffle buffer, batching,
