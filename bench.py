@@ -42,7 +42,8 @@ def _reference_arm() -> int:
         why = "tensorflow imports, but the reference scripts still need tensorflow_federated / tfds / phe"
     except Exception:
         pass
-    print(json.dumps({"impl": "reference", "unavailable": why}))
+    if int(os.environ.get("RANK", "0")) == 0:      # one line, also when launched as N ranks
+        print(json.dumps({"impl": "reference", "unavailable": why}))
     return 0
 
 
