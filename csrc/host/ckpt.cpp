@@ -104,6 +104,13 @@ long long idcbh_ckpt_header(const char* path, char* buf, long long buflen) {
     if (fread(magic, 1, 8, f) != 8 || memcmp(magic, "IDCBCKP1", 8) != 0 || fread(&hl, 8, 1, f) != 1) {
         fclose(f); idcbh::set_error("ckpt: %s is not an idcb checkpoint", path); return -1;
     }
+    // the length comes from the file: it has to fit in the file (and in a long long) before it sizes anything
+    fseek(f, 0, SEEK_END);
+    const long fsize = ftell(f);
+    fseek(f, 16, SEEK_SET);
+    if (fsize < 16 || hl > static_cast<unsigned long long>(fsize - 16)) {
+        fclose(f); idcbh::set_error("ckpt: header length of %s exceeds the file", path); return -1;
+    }
     if (buf == nullptr || buflen < static_cast<long long>(hl) + 1) { fclose(f); return static_cast<long long>(hl) + 1; }
     if (fread(buf, 1, hl, f) != hl) { fclose(f); idcbh::set_error("ckpt: truncated header in %s", path); return -1; }
     buf[hl] = 0;
@@ -115,6 +122,10 @@ int idcbh_ckpt_read(const char* path, unsigned long long header_len, unsigned lo
                     unsigned long long nbytes) {
     FILE* f = fopen(path, "rb");
     if (!f) { idcbh::set_error("ckpt: cannot open %s", path); return 1; }
+    const unsigned long long kMax = 1ull << 62;     // keeps the sum below inside a long
+    if (header_len > kMax || offset > kMax || nbytes > kMax || dst == nullptr) {
+        fclose(f); idcbh::set_error("ckpt: bad read range for %s", path); return 1;
+    }
     if (fseek(f, static_cast<long>(16 + header_len + offset), SEEK_SET) != 0 || fread(dst, 1, nbytes, f) != nbytes) {
         fclose(f); idcbh::set_error("ckpt: truncated payload in %s", path); return 1;
     }

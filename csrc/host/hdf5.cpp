@@ -270,21 +270,38 @@ struct Reader {
     std::map<std::string, RDataset> datasets;
     std::map<std::string, std::vector<RAttr>> attrs;   // by object path ("" = root)
     std::string err;
+    int visited = 0;
 };
 
 uint64_t rd(const Reader& r, size_t off, int n) {
     uint64_t v = 0;
-    if (off + n > r.f.size()) return UNDEF;
+    if (off > r.f.size() || static_cast<size_t>(n) > r.f.size() - off) return UNDEF;   // (off + n may wrap)
     memcpy(&v, r.f.data() + off, n);
     if (n == 8) return v;
     return (v == ((uint64_t(1) << (8 * n)) - 1)) ? UNDEF : v;
 }
 uint64_t rdraw(const Reader& r, size_t off, int n) {
     uint64_t v = 0;
-    if (off + n > r.f.size()) return 0;
+    if (off > r.f.size() || static_cast<size_t>(n) > r.f.size() - off) return 0;
     memcpy(&v, r.f.data() + off, n);
     return v;
 }
+
+// Every byte the reader looks at goes through these: an offset or a length taken from the file is never trusted
+// (a damaged or hostile .h5 must end in an error message, not in a read outside the buffer).
+inline uint8_t u8(const Reader& r, size_t off) { return off < r.f.size() ? r.f[off] : 0; }
+inline bool in_file(const Reader& r, size_t off, size_t n) { return off <= r.f.size() && n <= r.f.size() - off; }
+inline bool tag_at(const Reader& r, size_t off, const char* tag) { return in_file(r, off, 4) && memcmp(&r.f[off], tag, 4) == 0; }
+// at most maxn bytes starting at off, cut at the first NUL and at the end of the file
+inline std::string str_at(const Reader& r, size_t off, size_t maxn) {
+    if (off >= r.f.size()) return "";
+    maxn = std::min(maxn, r.f.size() - off);
+    const char* s = reinterpret_cast<const char*>(&r.f[off]);
+    return std::string(s, strnlen(s, maxn));
+}
+constexpr size_t kMaxBlocks = 4096;          // continuation blocks of one object header
+constexpr uint64_t kMaxAttrValues = 1 << 20;  // elements of one attribute
+constexpr int kMaxObjects = 1 << 20;          // objects visited in one file (cycles in a damaged file end here)
 
 struct Message {
     uint16_t type;
@@ -294,10 +311,10 @@ struct Message {
 
 bool collect_messages(Reader& r, uint64_t addr, std::vector<Message>& out) {
     const size_t a = static_cast<size_t>(addr + r.base);
-    if (a + 16 > r.f.size()) { r.err = "object header outside the file"; return false; }
-    if (memcmp(&r.f[a], "OHDR", 4) == 0) {
+    if (!in_file(r, a, 16)) { r.err = "object header outside the file"; return false; }
+    if (tag_at(r, a, "OHDR")) {
         // version 2 object header
-        const uint8_t flags = r.f[a + 5];
+        const uint8_t flags = u8(r, a + 5);
         size_t p = a + 6;
         if (flags & 0x20) p += 16;
         if (flags & 0x10) p += 4;
@@ -307,16 +324,18 @@ bool collect_messages(Reader& r, uint64_t addr, std::vector<Message>& out) {
         std::vector<std::pair<size_t, size_t>> blocks{{p, static_cast<size_t>(chunk0)}};
         const bool track = flags & 0x04;
         for (size_t bi = 0; bi < blocks.size(); ++bi) {
+            if (!in_file(r, blocks[bi].first, blocks[bi].second)) { r.err = "object header block outside the file"; return false; }
             size_t q = blocks[bi].first, end = blocks[bi].first + blocks[bi].second;
             while (q + 4 + (track ? 2 : 0) <= end) {
-                const uint8_t type = r.f[q];
+                const uint8_t type = u8(r, q);
                 const uint16_t sz = static_cast<uint16_t>(rdraw(r, q + 1, 2));
-                const uint8_t mf = r.f[q + 3];
+                const uint8_t mf = u8(r, q + 3);
                 q += 4 + (track ? 2 : 0);
                 if (q + sz > end) break;
                 if (type == 0x10) {
                     const uint64_t co = rd(r, q, r.so), cl = rdraw(r, q + r.so, r.sl);
                     // continuation block: "OCHK" + messages + checksum
+                    if (co == UNDEF || cl < 8 || blocks.size() >= kMaxBlocks) { r.err = "bad object header continuation"; return false; }
                     blocks.push_back({static_cast<size_t>(co + r.base) + 4, static_cast<size_t>(cl) - 8});
                 } else if (type != 0) {
                     out.push_back(Message{type, q, sz, mf});
@@ -326,22 +345,24 @@ bool collect_messages(Reader& r, uint64_t addr, std::vector<Message>& out) {
         }
         return true;
     }
-    if (r.f[a] != 1) { r.err = "unsupported object header version"; return false; }
+    if (u8(r, a) != 1) { r.err = "unsupported object header version"; return false; }
     const uint16_t nmsg = static_cast<uint16_t>(rdraw(r, a + 2, 2));
     const uint32_t hsize = static_cast<uint32_t>(rdraw(r, a + 8, 4));
     std::vector<std::pair<size_t, size_t>> blocks{{a + 16, hsize}};
     size_t seen = 0;
     for (size_t bi = 0; bi < blocks.size() && seen < nmsg; ++bi) {
+        if (!in_file(r, blocks[bi].first, blocks[bi].second)) { r.err = "object header block outside the file"; return false; }
         size_t q = blocks[bi].first, end = blocks[bi].first + blocks[bi].second;
         while (q + 8 <= end && seen < nmsg) {
             const uint16_t type = static_cast<uint16_t>(rdraw(r, q, 2));
             const uint16_t sz = static_cast<uint16_t>(rdraw(r, q + 2, 2));
-            const uint8_t mf = r.f[q + 4];
+            const uint8_t mf = u8(r, q + 4);
             q += 8;
-            if (q + sz > r.f.size()) { r.err = "message outside the file"; return false; }
+            if (!in_file(r, q, sz)) { r.err = "message outside the file"; return false; }
             ++seen;
             if (type == 0x0010) {
                 const uint64_t co = rd(r, q, r.so), cl = rdraw(r, q + r.so, r.sl);
+                if (co == UNDEF || blocks.size() >= kMaxBlocks) { r.err = "bad object header continuation"; return false; }
                 blocks.push_back({static_cast<size_t>(co + r.base), static_cast<size_t>(cl)});
             } else if (type != 0) {
                 out.push_back(Message{type, q, sz, mf});
@@ -360,19 +381,19 @@ struct DType {
 };
 DType parse_dtype(const Reader& r, size_t off) {
     DType d;
-    d.cls = r.f[off] & 0x0F;
+    d.cls = u8(r, off) & 0x0F;
     d.size = static_cast<uint32_t>(rdraw(r, off + 4, 4));
     d.consumed = 8;
     if (d.cls == 0) d.consumed += 4;
     else if (d.cls == 1) d.consumed += 12;
     else if (d.cls == 9) {   // variable length: bit field type 1 = string
-        d.vlen_str = (r.f[off + 1] & 0x0F) == 1;
+        d.vlen_str = (u8(r, off + 1) & 0x0F) == 1;
         d.consumed += 8 + 4;  // base type (char) is an 8+4 byte integer type; not needed further
     }
     return d;
 }
 size_t parse_dataspace(const Reader& r, size_t off, std::vector<uint64_t>& dims) {
-    const uint8_t ver = r.f[off], rank = r.f[off + 1], flags = r.f[off + 2];
+    const uint8_t ver = u8(r, off), rank = u8(r, off + 1), flags = u8(r, off + 2);
     size_t p = off + (ver == 1 ? 8 : 4);
     dims.clear();
     for (int i = 0; i < rank; ++i) dims.push_back(rdraw(r, p + size_t(r.sl) * i, r.sl));
@@ -383,7 +404,7 @@ size_t parse_dataspace(const Reader& r, size_t off, std::vector<uint64_t>& dims)
 
 std::string global_heap_string(const Reader& r, uint64_t coll, uint32_t index) {
     const size_t a = static_cast<size_t>(coll + r.base);
-    if (a + 16 > r.f.size() || memcmp(&r.f[a], "GCOL", 4) != 0) return "";
+    if (!in_file(r, a, 16) || !tag_at(r, a, "GCOL")) return "";
     const uint64_t csize = rdraw(r, a + 8, r.sl);
     size_t q = a + 8 + r.sl;
     const size_t end = a + static_cast<size_t>(csize);
@@ -393,9 +414,10 @@ std::string global_heap_string(const Reader& r, uint64_t coll, uint32_t index) {
         const size_t data = q + 8 + r.sl;
         if (idx == 0) break;
         if (idx == index) {
-            if (data + osz > r.f.size()) return "";
+            if (!in_file(r, data, static_cast<size_t>(osz)) || osz > (1u << 24)) return "";
             return std::string(reinterpret_cast<const char*>(&r.f[data]), static_cast<size_t>(osz));
         }
+        if (osz > r.f.size()) return "";
         q = data + ((static_cast<size_t>(osz) + 7) & ~size_t(7));
     }
     return "";
@@ -403,7 +425,7 @@ std::string global_heap_string(const Reader& r, uint64_t coll, uint32_t index) {
 
 void parse_attr(Reader& r, const Message& m, std::vector<RAttr>& out) {
     const size_t o = m.off;
-    const uint8_t ver = r.f[o];
+    const uint8_t ver = u8(r, o);
     if (ver < 1 || ver > 3) return;
     const uint16_t nsz = static_cast<uint16_t>(rdraw(r, o + 2, 2));
     const uint16_t dtsz = static_cast<uint16_t>(rdraw(r, o + 4, 2));
@@ -411,7 +433,7 @@ void parse_attr(Reader& r, const Message& m, std::vector<RAttr>& out) {
     size_t p = o + 8 + (ver == 3 ? 1 : 0);
     auto adv = [&](size_t n) { return ver == 1 ? pad8(n) : n; };
     RAttr a;
-    a.name = std::string(reinterpret_cast<const char*>(&r.f[p]), strnlen(reinterpret_cast<const char*>(&r.f[p]), nsz));
+    a.name = str_at(r, p, nsz);
     p += adv(nsz);
     const DType dt = parse_dtype(r, p);
     p += adv(dtsz);
@@ -419,15 +441,17 @@ void parse_attr(Reader& r, const Message& m, std::vector<RAttr>& out) {
     parse_dataspace(r, p, dims);
     p += adv(dssz);
     uint64_t count = 1;
-    for (uint64_t d : dims) count *= d;
+    for (uint64_t d : dims) {
+        if (d != 0 && count > kMaxAttrValues / d) return;      // not an attribute a weight file carries
+        count *= d;
+    }
     if (dt.cls == 3) {
         a.is_str = true;
-        for (uint64_t i = 0; i < count; ++i) {
-            const char* s = reinterpret_cast<const char*>(&r.f[p + i * dt.size]);
-            a.strs.push_back(std::string(s, strnlen(s, dt.size)));
-        }
+        if (dt.size == 0 || !in_file(r, p, static_cast<size_t>(count) * dt.size)) return;
+        for (uint64_t i = 0; i < count; ++i) a.strs.push_back(str_at(r, p + i * dt.size, dt.size));
     } else if (dt.cls == 9 && dt.vlen_str) {
         a.is_str = true;
+        if (!in_file(r, p, static_cast<size_t>(count) * (4 + r.so + 4))) return;
         for (uint64_t i = 0; i < count; ++i) {
             const size_t e = p + i * (4 + r.so + 4);
             const uint64_t coll = rd(r, e + 4, r.so);
@@ -437,6 +461,7 @@ void parse_attr(Reader& r, const Message& m, std::vector<RAttr>& out) {
     } else if (dt.cls == 1 || dt.cls == 0) {
         for (uint64_t i = 0; i < count && i < 64; ++i) {
             const size_t e = p + i * dt.size;
+            if (dt.size == 0 || !in_file(r, e, std::max<uint32_t>(dt.size, 8))) break;
             double v = 0;
             if (dt.cls == 1 && dt.size == 4) { float f; memcpy(&f, &r.f[e], 4); v = f; }
             else if (dt.cls == 1 && dt.size == 8) memcpy(&v, &r.f[e], 8);
@@ -449,10 +474,11 @@ void parse_attr(Reader& r, const Message& m, std::vector<RAttr>& out) {
 
 bool walk(Reader& r, uint64_t header, const std::string& path, int depth);
 
-bool walk_btree(Reader& r, uint64_t bt, uint64_t heap_data, const std::string& path, int depth) {
+bool walk_btree(Reader& r, uint64_t bt, uint64_t heap_data, const std::string& path, int depth, int tree_depth = 0) {
     const size_t a = static_cast<size_t>(bt + r.base);
-    if (a + 24 > r.f.size() || memcmp(&r.f[a], "TREE", 4) != 0) { r.err = "bad group B-tree node"; return false; }
-    const uint8_t level = r.f[a + 5];
+    if (bt == UNDEF || !in_file(r, a, 24) || !tag_at(r, a, "TREE")) { r.err = "bad group B-tree node"; return false; }
+    if (tree_depth > 16) { r.err = "group B-tree too deep"; return false; }
+    const uint8_t level = u8(r, a + 5);
     const uint16_t used = static_cast<uint16_t>(rdraw(r, a + 6, 2));
     size_t p = a + 8 + 2 * r.so;
     for (int i = 0; i < used; ++i) {
@@ -460,18 +486,19 @@ bool walk_btree(Reader& r, uint64_t bt, uint64_t heap_data, const std::string& p
         const uint64_t child = rd(r, p, r.so);
         p += r.so;
         if (level > 0) {
-            if (!walk_btree(r, child, heap_data, path, depth)) return false;
+            if (!walk_btree(r, child, heap_data, path, depth, tree_depth + 1)) return false;
             continue;
         }
         const size_t s = static_cast<size_t>(child + r.base);
-        if (s + 8 > r.f.size() || memcmp(&r.f[s], "SNOD", 4) != 0) { r.err = "bad symbol node"; return false; }
+        if (child == UNDEF || !in_file(r, s, 8) || !tag_at(r, s, "SNOD")) { r.err = "bad symbol node"; return false; }
         const uint16_t nsym = static_cast<uint16_t>(rdraw(r, s + 6, 2));
         for (int k = 0; k < nsym; ++k) {
             const size_t e = s + 8 + size_t(k) * (2 * r.so + 24);
             const uint64_t noff = rdraw(r, e, r.so);
             const uint64_t oh = rd(r, e + r.so, r.so);
-            const char* nm = reinterpret_cast<const char*>(&r.f[static_cast<size_t>(heap_data + r.base + noff)]);
-            const std::string child_path = path.empty() ? std::string(nm) : path + "/" + nm;
+            if (heap_data == UNDEF || noff >= r.f.size()) { r.err = "symbol name outside the local heap"; return false; }
+            const std::string nm = str_at(r, static_cast<size_t>(heap_data + r.base + noff), 4096);
+            const std::string child_path = path.empty() ? nm : path + "/" + nm;
             if (!walk(r, oh, child_path, depth + 1)) return false;
         }
     }
@@ -480,6 +507,8 @@ bool walk_btree(Reader& r, uint64_t bt, uint64_t heap_data, const std::string& p
 
 bool walk(Reader& r, uint64_t header, const std::string& path, int depth) {
     if (depth > 32) { r.err = "group nesting too deep"; return false; }
+    if (header == UNDEF) { r.err = "link to an undefined object header"; return false; }
+    if (++r.visited > kMaxObjects) { r.err = "too many objects (a cycle in the link structure?)"; return false; }
     std::vector<Message> msgs;
     if (!collect_messages(r, header, msgs)) return false;
     bool is_group = false;
@@ -491,14 +520,14 @@ bool walk(Reader& r, uint64_t header, const std::string& path, int depth) {
                 is_group = true;
                 const uint64_t bt = rd(r, m.off, r.so), hp = rd(r, m.off + r.so, r.so);
                 const size_t h = static_cast<size_t>(hp + r.base);
-                if (h + 8 + 2 * r.sl + r.so > r.f.size() || memcmp(&r.f[h], "HEAP", 4) != 0) { r.err = "bad local heap"; return false; }
+                if (hp == UNDEF || !in_file(r, h, 8 + 2 * r.sl + r.so) || !tag_at(r, h, "HEAP")) { r.err = "bad local heap"; return false; }
                 const uint64_t seg = rd(r, h + 8 + 2 * r.sl, r.so);
                 if (!walk_btree(r, bt, seg, path, depth)) return false;
                 break;
             }
             case 0x0002:     // link info
                 is_group = true;
-                if (rd(r, m.off + 2 + ((r.f[m.off + 1] & 1) ? 8 : 0), r.so) != UNDEF) {
+                if (rd(r, m.off + 2 + ((u8(r, m.off + 1) & 1) ? 8 : 0), r.so) != UNDEF) {
                     r.err = "group '" + path + "' uses dense link storage (fractal heap), which is outside the supported subset";
                     return false;
                 }
@@ -506,15 +535,16 @@ bool walk(Reader& r, uint64_t header, const std::string& path, int depth) {
             case 0x0006: {   // link message (compact new-style group)
                 is_group = true;
                 size_t p = m.off;
-                const uint8_t lf = r.f[p + 1];
+                const uint8_t lf = u8(r, p + 1);
                 p += 2;
                 uint8_t ltype = 0;
-                if (lf & 0x08) ltype = r.f[p++];
+                if (lf & 0x08) ltype = u8(r, p++);
                 if (lf & 0x04) p += 8;
                 if (lf & 0x10) p += 1;
                 const int lsz = 1 << (lf & 3);
                 const uint64_t nlen = rdraw(r, p, lsz);
                 p += lsz;
+                if (nlen > 4096 || !in_file(r, p, static_cast<size_t>(nlen))) { r.err = "link name outside the file"; return false; }
                 const std::string nm(reinterpret_cast<const char*>(&r.f[p]), static_cast<size_t>(nlen));
                 p += static_cast<size_t>(nlen);
                 if (ltype == 0) {
@@ -527,16 +557,17 @@ bool walk(Reader& r, uint64_t header, const std::string& path, int depth) {
             case 0x0003: { DType dt = parse_dtype(r, m.off); ds.cls = dt.cls; ds.elem = dt.size; has_type = true; break; }
             case 0x0008: {
                 has_layout = true;
-                const uint8_t ver = r.f[m.off];
+                const uint8_t ver = u8(r, m.off);
                 if (ver == 3 || ver == 4) {
-                    const uint8_t cls = r.f[m.off + 1];
+                    const uint8_t cls = u8(r, m.off + 1);
                     if (cls == 1) { ds.addr = rd(r, m.off + 2, r.so); ds.size = rdraw(r, m.off + 2 + r.so, r.sl); ds.ok = true; }
                     else if (cls == 0) {
                         const uint16_t sz = static_cast<uint16_t>(rdraw(r, m.off + 2, 2));
-                        ds.compact.assign(&r.f[m.off + 4], &r.f[m.off + 4] + sz); ds.size = sz; ds.ok = true;
+                        if (!in_file(r, m.off + 4, sz)) { r.err = "compact dataset outside the file"; return false; }
+                        ds.compact.assign(r.f.begin() + (m.off + 4), r.f.begin() + (m.off + 4 + sz)); ds.size = sz; ds.ok = true;
                     } else ds.why = "chunked/compressed storage is outside the supported subset";
                 } else if (ver == 1 || ver == 2) {
-                    const uint8_t rank = r.f[m.off + 1], cls = r.f[m.off + 2];
+                    const uint8_t rank = u8(r, m.off + 1), cls = u8(r, m.off + 2);
                     if (cls == 1) {
                         ds.addr = rd(r, m.off + 8, r.so);
                         ds.ok = true;   // size derived from dims below
@@ -659,9 +690,11 @@ void* idcbh_h5r_open(const char* path) {
     if (!found) { idcbh::set_error("h5r: %s is not an HDF5 file", path); return nullptr; }
     const uint8_t ver = r->f[sb + 8];
     uint64_t root_header = UNDEF;
+    const char* only8 = "h5r: only 8-byte offsets/lengths are supported";
     if (ver == 0 || ver == 1) {
         r->so = r->f[sb + 13];
         r->sl = r->f[sb + 14];
+        if (r->so != 8 || r->sl != 8) { idcbh::set_error("%s", only8); return nullptr; }   // before any sized read
         size_t p = sb + 24 + (ver == 1 ? 4 : 0);
         r->base = rdraw(*r, p, r->so);
         p += 4 * size_t(r->so);
@@ -669,10 +702,11 @@ void* idcbh_h5r_open(const char* path) {
     } else if (ver == 2 || ver == 3) {
         r->so = r->f[sb + 9];
         r->sl = r->f[sb + 10];
+        if (r->so != 8 || r->sl != 8) { idcbh::set_error("%s", only8); return nullptr; }
         r->base = rdraw(*r, sb + 12, r->so);
         root_header = rd(*r, sb + 12 + 3 * size_t(r->so), r->so);
     } else { idcbh::set_error("h5r: unsupported superblock version %d", ver); return nullptr; }
-    if (r->so != 8 || r->sl != 8) { idcbh::set_error("h5r: only 8-byte offsets/lengths are supported"); return nullptr; }
+    if (r->base > r->f.size()) { idcbh::set_error("h5r: base address outside the file"); return nullptr; }
     if (!walk(*r, root_header, "", 0)) { idcbh::set_error("h5r: %s", r->err.c_str()); return nullptr; }
     return r.release();
 }
@@ -714,13 +748,18 @@ int idcbh_h5r_read_f32(void* h, const char* path, float* dst, long long n) {
     if (!d.ok) { idcbh::set_error("h5r: dataset '%s': %s", path, d.why.c_str()); return 1; }
     if (d.cls != 1 || (d.elem != 4 && d.elem != 8)) { idcbh::set_error("h5r: dataset '%s' is not float32/float64", path); return 1; }
     uint64_t cnt = 1;
-    for (uint64_t v : d.dims) cnt *= v;
-    if (static_cast<uint64_t>(n) != cnt) { idcbh::set_error("h5r: dataset '%s' has %llu elements, caller expects %lld", path, (unsigned long long)cnt, n); return 1; }
+    for (uint64_t v : d.dims) {
+        if (v != 0 && cnt > (uint64_t(1) << 40) / v) { idcbh::set_error("h5r: dataset '%s' has an absurd shape", path); return 1; }
+        cnt *= v;
+    }
+    if (n < 0 || static_cast<uint64_t>(n) != cnt) { idcbh::set_error("h5r: dataset '%s' has %llu elements, caller expects %lld", path, (unsigned long long)cnt, n); return 1; }
     const uint8_t* src = d.compact.empty() ? nullptr : d.compact.data();
+    if (src && d.compact.size() < cnt * d.elem) { idcbh::set_error("h5r: compact dataset '%s' is shorter than its shape", path); return 1; }
     if (!src) {
         if (d.addr == UNDEF) { memset(dst, 0, cnt * 4); return 0; }   // never written: fill value
         const size_t a = static_cast<size_t>(d.addr + r->base);
-        if (a + cnt * d.elem > r->f.size()) { idcbh::set_error("h5r: dataset '%s' points outside the file", path); return 1; }
+        if (!in_file(*r, a, static_cast<size_t>(cnt * d.elem))) { idcbh::set_error("h5r: dataset '%s' points outside the file", path); return 1; }
+        if (cnt == 0) return 0;
         src = &r->f[a];
     }
     if (d.elem == 4) memcpy(dst, src, cnt * 4);

@@ -59,6 +59,8 @@ def read_checkpoint(path: str) -> dict:
     out = {}
     for t in meta["tensors"]:
         a = np.empty(t["shape"], dtype=np.float32)
+        if int(t["nbytes"]) != a.nbytes or int(t["offset"]) < 0:       # the header is file content: never trusted
+            raise IOError(f"checkpoint {path}: tensor {t['name']!r} declares {t['nbytes']} bytes for shape {t['shape']}")
         if lib.idcbh_ckpt_read(path.encode(), C.c_ulonglong(hl), C.c_ulonglong(t["offset"]),
                                a.ctypes.data_as(C.c_void_p), C.c_ulonglong(t["nbytes"])) != 0:
             raise IOError(lib.idcbh_last_error().decode())

@@ -248,3 +248,86 @@ def test_reader_names_the_unsupported_feature_of_a_dense_storage_group(tmp_path)
     path.write_bytes(raw)
     with pytest.raises(IOError, match="dense link storage"):
         keras_h5.read_h5(str(path))
+
+
+def test_h5_and_checkpoint_readers_under_sanitizers(tmp_path):
+    """tests/native/fuzz_h5.cpp: truncations, bit flips, saturated bytes and random damage of a file from our writer
+    and of the hand-built version-2 file; every mutation is opened, listed and every listed dataset read, with the
+    readers compiled under -fsanitize=address,undefined. A length or offset taken from the file and
+    trusted shows up as a sanitizer abort. (This harness found the unchecked header / name / attribute reads that the
+    checked accessors of csrc/host/hdf5.cpp now guard.)"""
+    import shutil
+    import subprocess
+    from pathlib import Path
+    from idc_models_b200.io import keras_h5
+    root = Path(__file__).resolve().parent.parent
+    cxx = shutil.which("g++")
+    if cxx is None:
+        pytest.skip("no g++")
+    exe = tmp_path / "fuzz_h5"
+    host = root / "csrc" / "host"
+    cmd = [cxx, "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined", "-pthread",
+           "-I", str(root / "include"), "-I", str(host), str(host / "hdf5.cpp"), str(host / "ckpt.cpp"),
+           str(host / "host_runtime.cpp"), str(root / "tests" / "native" / "fuzz_h5.cpp"), "-o", str(exe)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0 and "sanitize" in r.stderr:
+        pytest.skip("this g++ has no sanitizer runtime")
+    assert r.returncode == 0, r.stderr[-3000:]
+    rng = np.random.default_rng(0)
+    ours = tmp_path / "w.h5"
+    keras_h5.write_h5(str(ours), {"conv1/conv1/kernel:0": rng.normal(size=(3, 3, 3, 8)).astype(np.float32),
+                                  "conv1/conv1/bias:0": np.zeros(8, np.float32), "bn/bn/gamma:0": np.ones(8, np.float32)},
+                      [("/", "layer_names", ["conv1", "bn"], False), ("/", "backend", ["tensorflow"], True),
+                       ("conv1", "weight_names", ["conv1/kernel:0", "conv1/bias:0"], False),
+                       ("bn", "weight_names", ["bn/gamma:0"], False)])
+    blob = _build_v2_file()
+    v2 = tmp_path / "v2.h5"
+    v2.write_bytes(blob[0] if isinstance(blob, tuple) else blob)
+    # a checkpoint container too (the harness pushes every mutated file through both readers)
+    import ctypes as C
+    from idc_models_b200.ops import _lib
+    hl = _lib.host_lib()
+    hl.idcbh_ckpt_begin.restype = C.c_void_p
+    ck = tmp_path / "w.ckpt"
+    h = C.c_void_p(hl.idcbh_ckpt_begin(str(ck).encode()))
+    w = rng.normal(size=(4, 6)).astype(np.float32)
+    assert hl.idcbh_ckpt_add_f32(h, b"dense/kernel", w.ctypes.data_as(C.c_void_p), (C.c_longlong * 2)(4, 6), 2) == 0
+    assert hl.idcbh_ckpt_end(h) == 0
+    r = subprocess.run([str(exe), "2", str(tmp_path / "mut.h5"), str(ours), str(v2), str(ck)], capture_output=True,
+                       text=True, timeout=900)
+    assert r.returncode == 0, (r.stdout[-300:], r.stderr[-3000:])
+    files, opened, reads = [int(t) for t in r.stdout.split() if t.isdigit()]
+    assert files > 5000 and 0 < opened < files and reads > opened
+
+
+def test_checkpoint_with_a_lying_header_is_refused(tmp_path):
+    """a header length larger than the file, and a tensor whose declared byte count disagrees with its shape, are
+    errors (they used to size a read)"""
+    import ctypes as C
+    import struct
+    from idc_models_b200.io import checkpoint
+    from idc_models_b200.ops import _lib
+    hl = _lib.host_lib()
+    hl.idcbh_ckpt_begin.restype = C.c_void_p
+    ck = tmp_path / "w.ckpt"
+    h = C.c_void_p(hl.idcbh_ckpt_begin(str(ck).encode()))
+    w = np.arange(24, dtype=np.float32).reshape(4, 6)
+    assert hl.idcbh_ckpt_add_f32(h, b"dense/kernel", w.ctypes.data_as(C.c_void_p), (C.c_longlong * 2)(4, 6), 2) == 0
+    assert hl.idcbh_ckpt_end(h) == 0
+    good = ck.read_bytes()
+    assert np.array_equal(checkpoint.read_checkpoint(str(ck))["dense/kernel"], w)
+    for lie in (0xFFFFFFFFFFFFFFFF, 0x7FFFFFFFFFFFFFFF, len(good)):
+        bad = tmp_path / "bad.ckpt"
+        bad.write_bytes(good[:8] + struct.pack("<Q", lie) + good[16:])
+        with pytest.raises(IOError, match="exceeds the file"):
+            checkpoint.read_checkpoint(str(bad))
+    (hdr_len,) = struct.unpack("<Q", good[8:16])
+    header = good[16:16 + hdr_len].decode()
+    assert '"nbytes"' in header
+    lying = header.replace('"nbytes": 96', '"nbytes": 960').replace('"nbytes":96', '"nbytes":960')
+    assert lying != header
+    pad = lying.encode()
+    bad = tmp_path / "bad2.ckpt"
+    bad.write_bytes(good[:8] + struct.pack("<Q", len(pad)) + pad + good[16 + hdr_len:])
+    with pytest.raises(IOError, match="declares"):
+        checkpoint.read_checkpoint(str(bad))

@@ -142,3 +142,136 @@ def test_map_fast_path_equals_per_file_mapping(tmp_path):
     for (a, la), (b, lb) in zip(fast, slow):
         assert la == lb and np.array_equal(a, b)
     assert sorted({l for _, l in fast}) == [0, 1]
+
+
+def _chunk(tag: bytes, body: bytes) -> bytes:
+    import struct
+    import zlib
+    return struct.pack(">I", len(body)) + tag + body + struct.pack(">I", zlib.crc32(tag + body) & 0xFFFFFFFF)
+
+
+def _filter_rows(img: np.ndarray, filters) -> bytes:
+    """PNG-filter an [h, w, c] uint8 image with the given per-row filter types (the encoder side of the five filters,
+    written from the specification)"""
+    h, w, c = img.shape
+    rows = img.reshape(h, w * c).astype(np.int32)
+    out = bytearray()
+    prev = np.zeros(w * c, np.int32)
+    for y in range(h):
+        cur = rows[y]
+        left = np.concatenate([np.zeros(c, np.int32), cur[:-c]])
+        upleft = np.concatenate([np.zeros(c, np.int32), prev[:-c]])
+        ft = filters[y % len(filters)]
+        if ft == 0:
+            f = cur
+        elif ft == 1:
+            f = cur - left
+        elif ft == 2:
+            f = cur - prev
+        elif ft == 3:
+            f = cur - ((left + prev) >> 1)
+        else:
+            p = left + prev - upleft
+            pa, pb, pc = np.abs(p - left), np.abs(p - prev), np.abs(p - upleft)
+            pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, upleft))
+            f = cur - pred
+        out.append(ft)
+        out += (f & 0xFF).astype(np.uint8).tobytes()
+        prev = cur
+    return bytes(out)
+
+
+@pytest.mark.parametrize("strategy", ["default", "fixed", "rle", "huffman_only", "stored"])
+def test_hand_built_pngs_every_filter_every_deflate_block_type(strategy):
+    """PNG files assembled by hand: each of the five row filters forced, zlib told to emit fixed-Huffman, RLE,
+    Huffman-only, stored and ordinary dynamic blocks, the compressed stream cut into many IDAT chunks, long
+    back-references (image larger than the 32 KiB window)"""
+    import struct
+    import zlib
+    lib = _lib()
+    rng = np.random.default_rng(17)
+    strat = {"default": zlib.Z_DEFAULT_STRATEGY, "fixed": zlib.Z_FIXED, "rle": zlib.Z_RLE,
+             "huffman_only": zlib.Z_HUFFMAN_ONLY, "stored": zlib.Z_DEFAULT_STRATEGY}[strategy]
+    level = 0 if strategy == "stored" else 6
+    for (h, w, c), filters in [((40, 31, 3), [0]), ((40, 31, 3), [1]), ((40, 31, 3), [2]), ((40, 31, 3), [3]),
+                               ((40, 31, 3), [4]), ((130, 150, 3), [4, 3, 2, 1, 0]), ((64, 64, 4), [1, 4]),
+                               ((33, 17, 1), [3, 4, 0]), ((200, 200, 3), [0, 4])]:
+        img = _smooth(rng, h, w, c)
+        if (h, w) == (200, 200):
+            img[100:] = img[:100]                     # matches at distances up to the full window
+        co = zlib.compressobj(level, zlib.DEFLATED, 15, 9, strat)
+        z = co.compress(_filter_rows(img, filters)) + co.flush()
+        ctype = {1: 0, 3: 2, 4: 6}[c]
+        png = b"\x89PNG\r\n\x1a\n" + _chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, ctype, 0, 0, 0))
+        png += _chunk(b"tEXt", b"Comment\0hand built")
+        step = max(1, len(z) // 7)
+        for i in range(0, len(z), step):                   # several IDAT chunks, boundaries anywhere in the stream
+            png += _chunk(b"IDAT", z[i:i + step])
+        png += _chunk(b"IEND", b"")
+        rc, out, size = _native(lib, png, h, w)
+        assert rc == 0, (strategy, (h, w, c), filters, lib.idcbh_last_error())
+        want = img[:, :, :3] if c >= 3 else np.repeat(img, 3, axis=2)
+        assert size == (w, h) and np.array_equal(out, want.astype(np.float32) / 255.0), (strategy, (h, w, c), filters)
+        assert np.array_equal(out, _pil(png))              # and Pillow reads the hand-built file the same way
+
+
+def test_truncations_and_bit_flips_never_crash_or_decode_silently():
+    """every prefix of a valid file and a sweep of single-bit flips inside the compressed stream: the decoder either
+    rejects the file (status 2) or — when the flip hits a byte that does not matter (padding after the final block) or
+    still yields a stream whose adler32 checks — returns exactly what Pillow returns; it never reads out of bounds"""
+    lib = _lib()
+    rng = np.random.default_rng(23)
+    data = _png(Image.fromarray(_smooth(rng, 24, 24, 3), "RGB"))
+    full = _pil(data)
+    n_rejected = 0
+    for cut in range(0, len(data) - 1, 3):
+        rc, out, _ = _native(lib, data[:cut] if cut else b"\0", 24, 24)
+        assert rc in (0, 2), cut
+        if rc == 0:                        # only the trailer (IEND, or the last chunk's CRC) is missing
+            assert cut > data.index(b"IEND") - 8 and np.array_equal(out, full), cut
+        n_rejected += rc == 2
+    assert n_rejected > len(data) // 3 - 10
+    idat = data.index(b"IDAT")
+    for pos in range(idat + 4, len(data) - 16):
+        for bit in (0, 3, 7):
+            bad = bytearray(data)
+            bad[pos] ^= 1 << bit
+            rc, out, _ = _native(lib, bytes(bad), 24, 24)
+            assert rc in (0, 2)
+            if rc == 0:
+                assert np.array_equal(out, _pil(data)), (pos, bit)
+
+
+def test_decoder_under_address_and_undefined_behaviour_sanitizers(tmp_path):
+    """tests/native/fuzz_png.cpp: prefixes, bit flips and random damage of four files, from exact-size heap copies,
+    with the decoder compiled under -fsanitize=address,undefined (what a sanitizer can check on the
+    host side of this code base). Any out-of-bounds access or undefined shift aborts the harness."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    cxx = shutil.which("g++")
+    if cxx is None:
+        pytest.skip("no g++")
+    exe = tmp_path / "fuzz_png"
+    cmd = [cxx, "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined", "-pthread",
+           "-I", str(root / "include"), "-I", str(root / "csrc" / "host"), str(root / "csrc" / "host" / "png.cpp"),
+           str(root / "csrc" / "host" / "host_runtime.cpp"), str(root / "tests" / "native" / "fuzz_png.cpp"), "-o", str(exe)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0 and "sanitize" in r.stderr:
+        pytest.skip("this g++ has no sanitizer runtime")
+    assert r.returncode == 0, r.stderr[-3000:]
+    rng = np.random.default_rng(1)
+    files = []
+    for i, mode in enumerate(("RGB", "RGBA", "L", "P")):
+        a = _smooth(rng, 40, 37, 4)
+        im = {"RGB": lambda: Image.fromarray(a[:, :, :3], "RGB"), "RGBA": lambda: Image.fromarray(a, "RGBA"),
+              "L": lambda: Image.fromarray(a[:, :, 0], "L"),
+              "P": lambda: Image.fromarray(a[:, :, :3], "RGB").quantize(16)}[mode]()
+        p = tmp_path / f"f{i}.png"
+        im.save(p)
+        files.append(str(p))
+    r = subprocess.run([str(exe), "3", *files], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-500:], r.stderr[-3000:])
+    calls, decoded = [int(t) for t in r.stdout.split() if t.isdigit()]
+    assert calls > 5000 and 0 < decoded < calls // 10
