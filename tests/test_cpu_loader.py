@@ -79,3 +79,31 @@ def test_from_dataset_matches_python_pipeline_contents():
     ids, labels, sizes = _epoch(ld)
     assert sizes == [16, 16, 8] and sorted(ids) == list(range(40))
     assert labels == [float(i % 2) for i in ids]
+
+
+def test_loader_ring_protocol_under_thread_sanitizer(tmp_path):
+    """tests/native/tsan_loader.cpp: 4 worker threads against a consumer that holds two slots at a time, six epochs
+    (two abandoned half way), destruction with workers waiting and filling — compiled with -fsanitize=thread, so a
+    data race in the slot protocol is a report and a non-zero exit (host side)."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+    import pytest
+    root = Path(__file__).resolve().parent.parent
+    cxx = shutil.which("g++")
+    if cxx is None:
+        pytest.skip("no g++")
+    exe = tmp_path / "tsan_loader"
+    host = root / "csrc" / "host"
+    cmd = [cxx, "-O1", "-g", "-std=c++17", "-fsanitize=thread", "-pthread", "-I", str(root / "include"), "-I", str(host),
+           str(host / "loader.cpp"), str(host / "host_runtime.cpp"), str(root / "tests" / "native" / "tsan_loader.cpp"),
+           "-o", str(exe)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0 and ("sanitize" in r.stderr or "tsan" in r.stderr):
+        pytest.skip("this g++ has no thread-sanitizer runtime")
+    assert r.returncode == 0, r.stderr[-3000:]
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)
+    if "FATAL: ThreadSanitizer" in r.stderr and "memory layout" in r.stderr:
+        pytest.skip("thread sanitizer cannot map its shadow memory on this kernel")
+    assert r.returncode == 0 and "loader ok" in r.stdout and "WARNING: ThreadSanitizer" not in r.stderr, \
+        (r.stdout[-500:], r.stderr[-3000:])
