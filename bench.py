@@ -235,6 +235,11 @@ def main() -> int:
         return loss
 
     e2e_mode = "pipelined" if os.environ.get("IDCB_BENCH_E2E_SYNC", "0") != "1" else "synchronous"
+    # one untimed step through the same call: creates the executor's staging buffers / copy stream (one-time set-up,
+    # like the graph capture during warm-up), then the timed K steps start from an idle device
+    model.train_on_batch(hx[(ring - 1) % ring], hy[(ring - 1) % ring])
+    torch.cuda.synchronize()
+    world.barrier()
     t0 = time.perf_counter()
     try:
         last_loss = e2e_pipelined() if e2e_mode == "pipelined" else e2e_synchronous()
