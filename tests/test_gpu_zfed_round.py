@@ -128,13 +128,19 @@ for name in ("small_cnn", "mobilenet_v2_tiny"):
     xs = [torch.rand(*shape).pin_memory() for _ in range(7)]
     y = (torch.rand(shape[0]) > 0.5).float().pin_memory()
     assert ex.async_stage
-    got = [ex.eval_batch(x, y)[1] for x in xs]            # back to back, no synchronisation: both staging buffers cycle
+    if name == "small_cnn":
+        run = lambda x, yy: ex.eval_batch(x, yy)[1]                      # eager inference (returns a copy)
+    else:
+        # the captured training step (learning rate 0, so every call sees the same weights); its BatchNorm sums are
+        # accumulated atomically, hence the comparison below is relative to the batch-to-batch spread
+        run = lambda x, yy: ex.train_batch(x, yy, shape[0])[1].clone()
+    got = [run(x, y) for x in xs]                         # back to back, no synchronisation: both staging buffers cycle
     torch.cuda.synchronize()
     staged = hasattr(ex._get_plan(shape[0]), "_stager")
-    want = [ex.eval_batch(x.cuda(), y.cuda())[1] for x in xs]
+    want = [run(x.cuda(), y.cuda()) for x in xs]
     torch.cuda.synchronize()
     err = max((a - b).abs().max().item() for a, b in zip(got, want))
-    spread = (want[0] - want[1]).abs().max().item()       # different batches do give different logits
+    spread = min((want[i] - want[i + 1]).abs().max().item() for i in range(6))   # different batches, different logits
     out[name] = {"staged": staged, "err": err, "spread": spread, "scale": max(w.abs().max().item() for w in want)}
 res["models"] = out
 print("RESULT " + json.dumps(res))
@@ -175,4 +181,4 @@ def test_pinned_host_input_through_the_copy_stream_stager():
     for name, r in o["models"].items():
         assert r["staged"], name
         assert r["spread"] > 0, (name, r)
-        assert r["err"] <= 1e-5 * max(1.0, r["scale"]), (name, r)
+        assert r["err"] <= 0.02 * r["spread"] + 1e-5 * max(1.0, r["scale"]), (name, r)
