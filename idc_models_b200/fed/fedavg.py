@@ -229,23 +229,34 @@ class FederatedAveragingProcess:
                 cl = torch.cat([b[0] for b in blocks]); wt = torch.cat([b[1] for b in blocks])
             return weighted_delta_mean(state.master, cl, wt, self.server_lr, ranges)
         lib = _lib.cuda_lib()
-        cw = self._symm.comm_world()
         base = state.master
-        cw_round = self._symm.comm_world(use_barrier=True)     # a world of one GPU still needs the grid barrier
-        if len(ranges) <= 16 and base.dtype == torch.float32 and base.is_contiguous() and base.is_cuda \
-                and all(b % 4 == 0 and (e - b) % 4 == 0 for b, e in ranges):
+        # everything that does not change from round to round is marshalled once (the launch below is the whole
+        # aggregation, so the Python in front of it is what the GPU waits for)
+        key = (tuple(sorted(ranges)), n, k_local, id(clients), id(weights), id(gbuf), id(gshadow))
+        ra = getattr(self, "_round_args", None)
+        if ra is None or ra["key"] != key:
+            rs = sorted(ranges)
+            ra = self._round_args = {
+                "key": key, "keep": (clients, weights, gbuf, gshadow),
+                "ok": len(rs) <= 16 and all(b % 4 == 0 and (e - b) % 4 == 0 for b, e in rs),
+                "cw": self._symm.comm_world(use_barrier=True),     # a world of one GPU still needs the grid barrier
+                "n_ranges": C.c_int(len(rs)),
+                "offs": (C.c_longlong * max(len(rs), 1))(*[b for b, _ in rs]),
+                "lens": (C.c_longlong * max(len(rs), 1))(*[e - b for b, e in rs]),
+                "ptrs": (clients.ptrs(), weights.ptrs(), gbuf.ptrs(), gshadow.ptrs(), gbuf.mc(), gshadow.mc()),
+            }
+        if ra["ok"] and base.dtype == torch.float32 and base.is_contiguous() and base.is_cuda:
             # one launch: finite scan of the local clients, every range's weighted mean (multicast into every rank),
             # and this rank's private copy of the complete new model
-            rs = sorted(ranges)
-            offs = (C.c_longlong * max(len(rs), 1))(*[b for b, _ in rs])
-            lens = (C.c_longlong * max(len(rs), 1))(*[e - b for b, e in rs])
             out = torch.empty_like(base)
-            _lib.check(lib.idcb_fedavg_round(C.byref(cw_round), clients.ptrs(), weights.ptrs(), gbuf.ptrs(), gshadow.ptrs(),
-                                             gbuf.mc(), gshadow.mc(), C.c_int(k_local), C.c_longlong(n), C.c_int(len(rs)),
-                                             offs, lens, C.c_float(self.server_lr), C.c_void_p(base.data_ptr()),
+            cp, wp, gp, sp, gmc, smc = ra["ptrs"]
+            _lib.check(lib.idcb_fedavg_round(C.byref(ra["cw"]), cp, wp, gp, sp, gmc, smc, C.c_int(k_local),
+                                             C.c_longlong(n), ra["n_ranges"], ra["offs"], ra["lens"],
+                                             C.c_float(self.server_lr), C.c_void_p(base.data_ptr()),
                                              C.c_void_p(out.data_ptr()), C.c_longlong(n), _lib.stream()))
             _lib.count_launch()
             return out
+        cw = self._symm.comm_world()
         gbuf.tensor[:n].copy_(base)
         for b, e in ranges:
             _lib.check(lib.idcb_fedavg_finite_flags(C.c_void_p(clients.tensor.data_ptr()), C.c_longlong(n),
