@@ -101,9 +101,41 @@ def Dense(units, activation=None, **kw):
     return _L("dense", units=units, activation=activation)
 
 
-def Sequential(items, name: str = "sequential", device=None, seed: int = 0, executor: str = "auto",
-               input_shape=None) -> Network:
-    """Chain an optional application base and single layers into one :class:`Network`."""
+class _GrowingSequential:
+    """``model = Sequential(); model.add(layer); ...`` (/root/reference/secure_fed_model.py:85-94): layers are
+    collected until the model is first used (``compile``, ``summary``, ``get_weights``, ...); from then on the object
+    is the built :class:`Network` in every respect (attribute access is forwarded to it)."""
+
+    def __init__(self, **kw):
+        object.__setattr__(self, "_items", [])
+        object.__setattr__(self, "_kw", kw)
+        object.__setattr__(self, "_net", None)
+
+    def add(self, layer) -> None:
+        if self._net is not None:
+            raise RuntimeError("Sequential.add after the model has been built (compile / summary / weights were used)")
+        self._items.append(layer)
+
+    def build(self) -> Network:
+        if self._net is None:
+            if not self._items:
+                raise ValueError("Sequential has no layers")
+            object.__setattr__(self, "_net", Sequential(list(self._items), **self._kw))
+        return self._net
+
+    def __getattr__(self, name):
+        return getattr(self.build(), name)
+
+    def __setattr__(self, name, value):
+        setattr(self.build(), name, value)
+
+
+def Sequential(items=None, name: str = "sequential", device=None, seed: int = 0, executor: str = "auto",
+               input_shape=None):
+    """Chain an optional application base and single layers into one :class:`Network`. Without ``items`` the
+    incremental Keras form is returned: ``model = Sequential(); model.add(Conv2D(...)); ...; model.compile(...)``."""
+    if items is None:
+        return _GrowingSequential(name=name, device=device, seed=seed, executor=executor, input_shape=input_shape)
     base: BaseSpec | None = None
     rest = list(items)
     if rest and isinstance(rest[0], BaseSpec):

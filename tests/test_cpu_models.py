@@ -100,3 +100,34 @@ def test_densenet201_cifar_fine_tune_set_matches_survey():
     tw = m.trainable_weights
     assert len(tw) == 479
     assert sum(t.numel() for t in tw) == 16611530
+
+
+def test_incremental_sequential_add_builds_the_same_model():
+    """``model = Sequential(); model.add(...)`` (the form of /root/reference/secure_fed_model.py:85-94) builds the
+    network of the list form, lazily at first use; adding afterwards is refused"""
+    import numpy as np
+    import pytest
+    import torch
+    from idc_models_b200.models import applications as apps
+    from idc_models_b200.models.network import clone_model
+
+    def layers():
+        return [apps.Conv2D(32, kernel_size=(3, 3), activation="relu", input_shape=(10, 10, 3), strides=2),
+                apps.MaxPooling2D(pool_size=(2, 2)), apps.Dropout(0.25), apps.Flatten(),
+                apps.Dense(8, activation="relu"), apps.Dropout(0.5), apps.Dense(1)]
+    m = apps.Sequential(device="cpu", seed=3)
+    for l in layers():
+        m.add(l)
+    ref = apps.Sequential(layers(), device="cpu", seed=3)
+    m.compile(optimizer="rmsprop", loss="bce", metrics=["accuracy"])
+    assert m.count_params() == ref.count_params() == 1937
+    assert all(np.array_equal(a, b) for a, b in zip(m.get_weights(), ref.get_weights()))
+    x, y = torch.rand(8, 10, 10, 3), (torch.rand(8) > 0.5).float()
+    h = m.fit([(x, y)] * 2, epochs=1, verbose=0)
+    assert len(h.history["loss"]) == 1
+    with pytest.raises(RuntimeError, match="after the model has been built"):
+        m.add(apps.Dense(1))
+    c = clone_model(m.build())
+    assert c.count_params() == 1937
+    with pytest.raises(ValueError, match="no layers"):
+        apps.Sequential(device="cpu").compile(optimizer="sgd", loss="bce")
