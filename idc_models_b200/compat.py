@@ -1,0 +1,123 @@
+"""Name-for-name front door for code written against the reference's imports.
+
+The five upstream scripts use a small, fixed part of TensorFlow / Keras, TensorFlow Federated, ``phe`` and
+scikit-learn. This module lays this framework's implementations out under the same dotted names, so a
+script written the way the reference's are ports by changing its import lines::
+
+    # was:  import tensorflow as tf; import tensorflow_federated as tff; from phe import paillier
+    from idc_models_b200.compat import tf, tff, paillier, roc_auc_score
+
+    strategy = tf.distribute.MirroredStrategy()
+    with strategy.scope():
+        base_model = tf.keras.applications.MobileNetV2(input_shape=(50, 50, 3), include_top=False, weights=None)
+        base_model.trainable = False
+        model = tf.keras.Sequential([base_model, tf.keras.layers.GlobalAveragePooling2D(), tf.keras.layers.Dense(1)])
+        model.compile(optimizer=tf.keras.optimizers.RMSprop(lr=1e-4),
+                      loss=tf.keras.losses.BinaryCrossentropy(from_logits=True), metrics=['accuracy'])
+
+Only what the reference touches is here (/root/reference/dist_model_tf_mobile.py:1-20,105-170, fed_model.py:1-30,
+186-236, secure_fed_model.py:1-20,85-121); it is a map of names, not an emulation of TensorFlow. Tensors are
+``torch.Tensor`` / ``numpy.ndarray``, datasets are :class:`idc_models_b200.data.dataset.Dataset`.
+"""
+from __future__ import annotations
+
+import types as _types
+
+from .data import dataset as _dataset
+from .fed import client_data as _client_data
+from .fed import fedavg as _fedavg
+from .fed import paillier as _paillier
+from .models import applications as _apps
+from .models import network as _network
+from .optim import optimizers as _optim
+from .parallel import strategy as _strategy
+from .train import engine as _engine
+from .train import losses as _losses
+from .train import metrics as _metrics
+
+
+def _ns(**kw) -> _types.SimpleNamespace:
+    return _types.SimpleNamespace(**kw)
+
+
+def _read_file(path: str) -> bytes:
+    """tf.io.read_file"""
+    with open(path, "rb") as f:
+        return f.read()
+
+
+def _decode_png(data: bytes, channels: int = 3):
+    """tf.image.decode_png(channels=3) followed by convert_image_dtype(float32): float32 [H, W, 3] in [0, 1] at the
+    image's own size (the two reference calls are one step here; ``convert_image_dtype`` is then the identity)."""
+    import numpy as np
+    from PIL import Image
+    import io
+    if channels != 3:
+        raise ValueError("only channels=3 is supported (what the reference uses)")
+    lib = _dataset._native_png()
+    if lib:
+        import ctypes as C
+        w, h = C.c_int(), C.c_int()
+        probe = np.empty((1, 1, 3), np.float32)
+        # first call only learns the size (the 1x1 output is discarded), second decodes at native resolution
+        if lib.idcbh_png_decode_f32(data, len(data), probe.ctypes.data, 1, 1, C.byref(w), C.byref(h)) == 0:
+            out = np.empty((h.value, w.value, 3), np.float32)
+            if lib.idcbh_png_decode_f32(data, len(data), out.ctypes.data, h.value, w.value, None, None) == 0:
+                return out
+    return np.asarray(Image.open(io.BytesIO(data)).convert("RGB"), dtype=np.float32) / 255.0
+
+
+def _convert_image_dtype(img, dtype=None):
+    import numpy as np
+    a = np.asarray(img)
+    return a.astype(np.float32) / 255.0 if a.dtype == np.uint8 else a.astype(np.float32)
+
+
+def _resize(img, size):
+    """tf.image.resize (bilinear, half-pixel centres, no antialias) of one [H, W, C] float image"""
+    import numpy as np
+    import torch
+    a = np.asarray(img, dtype=np.float32)
+    if a.shape[0] == size[0] and a.shape[1] == size[1]:
+        return a
+    t = torch.from_numpy(a).permute(2, 0, 1).unsqueeze(0)
+    t = torch.nn.functional.interpolate(t, size=tuple(size), mode="bilinear", align_corners=False)
+    return t.squeeze(0).permute(1, 2, 0).contiguous().numpy()
+
+
+tf = _ns(
+    keras=_ns(
+        Sequential=_apps.Sequential,
+        applications=_ns(MobileNetV2=_apps.MobileNetV2, VGG16=_apps.VGG16, DenseNet121=_apps.DenseNet121,
+                         DenseNet169=_apps.DenseNet169, DenseNet201=_apps.DenseNet201,
+                         vgg16=_ns(VGG16=_apps.VGG16)),
+        layers=_ns(Conv2D=_apps.Conv2D, MaxPooling2D=_apps.MaxPooling2D, AveragePooling2D=_apps.AveragePooling2D,
+                   Dropout=_apps.Dropout, Flatten=_apps.Flatten, GlobalAveragePooling2D=_apps.GlobalAveragePooling2D,
+                   Dense=_apps.Dense),
+        models=_ns(Sequential=_apps.Sequential, clone_model=lambda m, **kw: _network.clone_model(
+            m.build() if hasattr(m, "build") and not isinstance(m, _network.Network) else m, **kw)),
+        optimizers=_ns(RMSprop=_optim.RMSprop, SGD=_optim.SGD, Adam=_optim.Adam),
+        losses=_ns(BinaryCrossentropy=_losses.BinaryCrossentropy, CategoricalCrossentropy=_losses.CategoricalCrossentropy),
+        metrics=_ns(BinaryAccuracy=_metrics.BinaryAccuracy, CategoricalAccuracy=_metrics.CategoricalAccuracy),
+        callbacks=_ns(ModelCheckpoint=_engine.ModelCheckpoint, Callback=_engine.Callback, History=_engine.History),
+    ),
+    distribute=_ns(MirroredStrategy=_strategy.MirroredStrategy, get_strategy=_strategy.get_strategy,
+                   experimental=_ns(CentralStorageStrategy=_strategy.CentralStorageStrategy)),
+    data=_ns(Dataset=_dataset.Dataset, experimental=_ns(AUTOTUNE=_dataset.AUTOTUNE)),
+    io=_ns(read_file=_read_file),
+    image=_ns(decode_png=_decode_png, convert_image_dtype=_convert_image_dtype, resize=_resize),
+)
+
+tff = _ns(
+    learning=_ns(from_keras_model=_fedavg.from_keras_model,
+                 build_federated_averaging_process=_fedavg.build_federated_averaging_process,
+                 build_federated_evaluation=_fedavg.build_federated_evaluation,
+                 state_with_new_model_weights=_fedavg.state_with_new_model_weights,
+                 ModelWeights=_fedavg.ModelWeights),
+    simulation=_ns(ClientData=_client_data.ClientData),
+)
+
+paillier = _ns(generate_paillier_keypair=_paillier.generate_paillier_keypair, EncryptedNumber=_paillier.EncryptedNumber,
+               PaillierPublicKey=_paillier.PaillierPublicKey, PaillierPrivateKey=_paillier.PaillierPrivateKey)
+
+roc_auc_score = _metrics.roc_auc_score
