@@ -5,7 +5,7 @@ scikit-learn. This module lays this framework's implementations 
 script written the way the reference's are ports by changing its import lines::
 
     # was:  import tensorflow as tf; import tensorflow_federated as tff; from phe import paillier
-    from idc_models_b200.compat import tf, tff, paillier, roc_auc_score
+    from idc_models_b200.compat import tf, tff, tfds, paillier, roc_auc_score
 
     strategy = tf.distribute.MirroredStrategy()
     with strategy.scope():
@@ -85,12 +85,73 @@ def _resize(img, size):
     return t.squeeze(0).permute(1, 2, 0).contiguous().numpy()
 
 
+def _strings_split(s, sep=None):
+    """tf.strings.split of ONE string: the list of parts (``parts[-2] == '1'`` is the reference's label rule)"""
+    return str(s).split(sep)
+
+
+def _cast(x, dtype):
+    import numpy as np
+    import torch
+    if isinstance(x, torch.Tensor):
+        return x.to(torch.float64 if dtype in (np.float64, float) else torch.float32 if dtype is np.float32 else dtype)
+    return np.asarray(x).astype(dtype)
+
+
+def _map_structure(fn, *structures):
+    """tf.nest.map_structure over nested lists / tuples / dicts"""
+    first = structures[0]
+    if isinstance(first, dict):
+        return {k: _map_structure(fn, *[s[k] for s in structures]) for k in first}
+    if isinstance(first, (list, tuple)):
+        out = [_map_structure(fn, *parts) for parts in zip(*structures)]
+        return type(first)(out) if not hasattr(first, "_fields") else type(first)(*out)
+    return fn(*structures)
+
+
+def _py_func(func, inp, Tout=None, **kw):
+    """tf.compat.v1.py_func: there is no graph here, so it is the call itself"""
+    return func(*inp)
+
+
+def _tfds_load(name="cifar10", split=None, data_dir=None, with_info=False, as_supervised=True, n_synthetic=50000, seed=0):
+    """tfds.load('cifar10', with_info=True, as_supervised=True) of /root/reference/dist_model_tf_dense.py:120: an
+    on-disk copy under ``data_dir`` (``cifar-10-batches-bin`` / ``-py``, searched like the dense script does) or,
+    without one, the synthetic stand-in of the same shape (there is nothing to download from here). uint8 images."""
+    if name != "cifar10":
+        raise ValueError("only 'cifar10' (the dataset the reference loads) is available")
+    from .data import cifar, synthetic
+    found = cifar.find_cifar10(data_dir) if data_dir else None
+    if found is not None:
+        (xtr, ytr), (xte, yte) = cifar.load_cifar10(found)
+        ds = {"train": _dataset.Dataset.from_tensor_slices((xtr, ytr)), "test": _dataset.Dataset.from_tensor_slices((xte, yte))}
+        sizes = {"train": len(xtr), "test": len(xte)}
+    else:
+        n_test = max(n_synthetic // 5, 1)
+        ds = {"train": synthetic.synthetic_cifar10(n_synthetic, seed), "test": synthetic.synthetic_cifar10(n_test, seed + 1)}
+        sizes = {"train": n_synthetic, "test": n_test}
+    out = ds if split is None else (ds[split] if isinstance(split, str) else [ds[s] for s in split])
+    if with_info:
+        info = _ns(name="cifar10", splits={k: _ns(num_examples=v) for k, v in sizes.items()},
+                   features=_ns(image_shape=(32, 32, 3), num_classes=10), source="disk" if found else "synthetic")
+        return out, info
+    return out
+
+
+import numpy as _np
+
 tf = _ns(
+    float32=_np.float32, double=_np.float64, float64=_np.float64, cast=_cast,
+    strings=_ns(split=_strings_split),
+    nest=_ns(map_structure=_map_structure),
+    compat=_ns(v1=_ns(enable_v2_behavior=lambda: None, py_func=_py_func)),
     keras=_ns(
         Sequential=_apps.Sequential,
         applications=_ns(MobileNetV2=_apps.MobileNetV2, VGG16=_apps.VGG16, DenseNet121=_apps.DenseNet121,
                          DenseNet169=_apps.DenseNet169, DenseNet201=_apps.DenseNet201,
-                         vgg16=_ns(VGG16=_apps.VGG16)),
+                         vgg16=_ns(VGG16=_apps.VGG16), mobilenet_v2=_ns(MobileNetV2=_apps.MobileNetV2),
+                         densenet=_ns(DenseNet121=_apps.DenseNet121, DenseNet169=_apps.DenseNet169,
+                                      DenseNet201=_apps.DenseNet201)),
         layers=_ns(Conv2D=_apps.Conv2D, MaxPooling2D=_apps.MaxPooling2D, AveragePooling2D=_apps.AveragePooling2D,
                    Dropout=_apps.Dropout, Flatten=_apps.Flatten, GlobalAveragePooling2D=_apps.GlobalAveragePooling2D,
                    Dense=_apps.Dense),
@@ -116,6 +177,8 @@ tff = _ns(
                  ModelWeights=_fedavg.ModelWeights),
     simulation=_ns(ClientData=_client_data.ClientData),
 )
+
+tfds = _ns(load=_tfds_load)
 
 paillier = _ns(generate_paillier_keypair=_paillier.generate_paillier_keypair, EncryptedNumber=_paillier.EncryptedNumber,
                PaillierPublicKey=_paillier.PaillierPublicKey, PaillierPrivateKey=_paillier.PaillierPrivateKey)

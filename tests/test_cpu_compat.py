@@ -98,3 +98,24 @@ def test_image_functions_match_the_dataset_pipeline(tmp_path):
     assert img.shape == (61, 47, 3) and np.array_equal(img, a.astype(np.float32) / 255.0)
     out = tf.image.resize(img, [50, 50])
     assert np.abs(out - decode_img(str(p), (50, 50))).max() < 5e-6
+
+
+def test_remaining_reference_names():
+    """everything else the five scripts call on tf / tff / tfds (grep of /root/reference/*.py)"""
+    import os
+    from idc_models_b200.compat import tfds
+    tf.compat.v1.enable_v2_behavior()
+    parts = tf.strings.split(os.path.join("data", "1", "patch.png"), os.path.sep)
+    assert (parts[-2] == "1") is True
+    assert tf.cast(np.arange(3), tf.float32).dtype == np.float32 and tf.cast(torch.ones(2), tf.double).dtype == torch.float64
+    assert tf.nest.map_structure(lambda a, b: a + b, {"x": [1, 2], "y": (3,)}, {"x": [10, 20], "y": (30,)}) == \
+        {"x": [11, 22], "y": (33,)}
+    assert tf.compat.v1.py_func(lambda a, b: a * b, [3, 4], tf.double) == 12
+    assert tf.keras.applications.densenet.DenseNet201 is tf.keras.applications.DenseNet201
+    datasets, info = tfds.load(name="cifar10", with_info=True, as_supervised=True, n_synthetic=40)
+    image, label = next(iter(datasets["train"]))
+    assert np.asarray(image).shape == (32, 32, 3) and 0 <= int(label) < 10
+    assert info.splits["train"].num_examples == 40 and info.source == "synthetic"
+    cd = tff.simulation.ClientData.from_clients_and_fn(list(range(10)), lambda c: c)
+    train, test = tff.simulation.ClientData.train_test_client_split(cd, 2)
+    assert len(train.client_ids) == 8 and len(test.client_ids) == 2
