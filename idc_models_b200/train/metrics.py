@@ -119,6 +119,25 @@ def auroc(y_true=None, y_pred=None):
     return roc_auc_score(np.asarray(y_true), np.asarray(y_pred))
 
 
+class FunctionMetric(Metric):
+    """A plain ``fn(y_true, y_pred)`` passed in ``metrics=[...]`` (Keras calls it per batch and averages the values
+    over the batches; the reference's own ``auroc`` py_func wrapper is one, secure_fed_model.py:81-82,97). A batch
+    on which the function raises ``ValueError`` (AUROC of a single-class batch) is left out of the average."""
+
+    def __init__(self, fn):
+        super().__init__()
+        self.fn = fn
+        self.name = getattr(fn, "__name__", "metric")
+
+    def batch_stats(self, logits, labels):
+        y = labels.detach().cpu().numpy().reshape(logits.shape[0], -1)
+        s = logits.detach().float().cpu().numpy().reshape(logits.shape[0], -1)
+        try:
+            return float(np.mean(np.asarray(self.fn(y, s), dtype=np.float64))), 1.0
+        except ValueError:
+            return 0.0, 0.0
+
+
 def get(m, n_outputs: int) -> Metric:
     if isinstance(m, Metric):
         return m
@@ -132,7 +151,16 @@ def get(m, n_outputs: int) -> Metric:
         if m in ("auroc", "auc"):
             return AUROC()
     if callable(m):
-        r = m()
-        if isinstance(r, Metric):
-            return r
+        import inspect
+        try:
+            required = [p for p in inspect.signature(m).parameters.values()
+                        if p.default is p.empty and p.kind in (p.POSITIONAL_ONLY, p.POSITIONAL_OR_KEYWORD)]
+        except (TypeError, ValueError):
+            required = []
+        if not required:                       # a metric class / factory
+            r = m()
+            if isinstance(r, Metric):
+                return r
+        elif len(required) == 2:               # fn(y_true, y_pred)
+            return FunctionMetric(m)
     raise ValueError(f"unknown metric {m!r}")

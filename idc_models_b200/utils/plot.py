@@ -105,3 +105,31 @@ def log(path: str, history, history_fine, num_devices: int, initial_epochs: int 
     printer(history.history)
     printer(history_fine.history)
     return out
+
+
+def write_panels_png(path: str, panels: list, size: int = 800) -> str:
+    """Render recorded pyplot-style panels (``{"lines": [(xs, ys, label), ...], "ylim": (lo, hi) | None}``), stacked
+    vertically, with the built-in rasteriser. Used by the ``matplotlib.pyplot`` stand-in of
+    ``idc_models_b200.run_reference`` when matplotlib is not installed."""
+    img = np.full((size, size, 3), 255, dtype=np.uint8)
+    n_p = max(len(panels), 1)
+    height = (size - 80) // n_p - 40
+    colors = [(31, 119, 180), (255, 127, 14), (44, 160, 44), (214, 39, 40)]
+    for pi, p in enumerate(panels):
+        top = 40 + pi * (height + 80)
+        left, right, bottom = 60, size - 20, top + height
+        _line(img, left, top, left, bottom, (0, 0, 0))
+        _line(img, left, bottom, right, bottom, (0, 0, 0))
+        xs_all = [x for xs, _, _ in p["lines"] for x in xs] or [0.0, 1.0]
+        ys_all = [y for _, ys, _ in p["lines"] for y in ys] or [0.0, 1.0]
+        lo, hi = p.get("ylim") or (min(ys_all), max(ys_all))
+        x_lo, x_hi = min(xs_all), max(xs_all)
+        xs_span, ys_span = max(x_hi - x_lo, 1e-12), max(hi - lo, 1e-12)
+        for li, (xs, ys, _) in enumerate(p["lines"]):
+            pts = [(left + (right - left) * ((x - x_lo) / xs_span),
+                    bottom - (bottom - top) * ((min(max(y, lo), hi) - lo) / ys_span)) for x, y in zip(xs, ys)]
+            for (x0, y0), (x1, y1) in zip(pts[:-1], pts[1:]):
+                _line(img, x0, y0, x1, y1, colors[li % len(colors)])
+    with open(path, "wb") as f:
+        f.write(_png_bytes(img))
+    return path
