@@ -114,13 +114,17 @@ def _py_func(func, inp, Tout=None, **kw):
     return func(*inp)
 
 
-def _tfds_load(name="cifar10", split=None, data_dir=None, with_info=False, as_supervised=True, n_synthetic=50000, seed=0):
+def _tfds_load(name="cifar10", split=None, data_dir=None, with_info=False, as_supervised=True, n_synthetic=None, seed=0):
     """tfds.load('cifar10', with_info=True, as_supervised=True) of /root/reference/dist_model_tf_dense.py:120: an
     on-disk copy under ``data_dir`` (``cifar-10-batches-bin`` / ``-py``, searched like the dense script does) or,
     without one, the synthetic stand-in of the same shape (there is nothing to download from here). uint8 images."""
     if name != "cifar10":
         raise ValueError("only 'cifar10' (the dataset the reference loads) is available")
+    import os
     from .data import cifar, synthetic
+    if n_synthetic is None:
+        n_synthetic = int(os.environ.get("IDCB_TFDS_SYNTHETIC_N", "50000"))
+    data_dir = data_dir or os.environ.get("TFDS_DATA_DIR")
     found = cifar.find_cifar10(data_dir) if data_dir else None
     if found is not None:
         (xtr, ytr), (xte, yte) = cifar.load_cifar10(found)

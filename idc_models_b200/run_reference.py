@@ -12,8 +12,9 @@ The modules those scripts import (``tensorflow``, ``tensorflow_federated``, ``te
 
 This is a convenience for users switching over, not the benchmark's reference arm: every model, kernel and
 collective that runs is this framework's (``bench.py --impl reference`` stays "unavailable").
-Known limits, all in the scripts themselves: ``fed_model.py`` calls ``sys.path.exists`` (an AttributeError upstream
-too), and ``secure_fed_model.py`` with ``percent > 0`` builds a ragged ``np.array`` that NumPy >= 1.24 refuses.
+``fed_model.py`` calls ``sys.path.exists`` (an AttributeError upstream); the runner gives ``sys.path`` that method
+(= ``os.path.exists``, what the author meant) so the script runs. One limit is the script's own: ``secure_fed_model.py``
+with ``percent > 0`` builds a ragged ``np.array`` that NumPy >= 1.24 refuses.
 """
 from __future__ import annotations
 
@@ -106,6 +107,14 @@ def install_shims(device: str | None = None) -> None:
             return seq(items, **kw)
         for ns in (compat.tf.keras, compat.tf.keras.models):
             ns.Sequential = Sequential
+    # fed_model.py asks ``sys.path.exists(...)`` where it means os.path.exists (an AttributeError upstream): give the
+    # module search path that method, so that the script does what its author meant
+    if not hasattr(sys.path, "exists"):
+        class _SearchPath(list):
+            exists = staticmethod(os.path.exists)
+        sys.path = _SearchPath(sys.path)
+    from .fed.client_data import ClientData
+    ClientData.strict_ids = False        # the TFF of the reference's time did not check ids (see client_data.py)
     tf = _from_namespace("tensorflow", compat.tf)
     tf.__version__ = "2.1.0 (idc_models_b200.compat)"
     sys.modules["tensorflow"] = tf

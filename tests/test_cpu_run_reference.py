@@ -54,3 +54,16 @@ def test_unmodified_reference_secure_script_runs(tmp_path):
     assert out.count("Training for client 0 took") == 2 and out.count("Training for client 1 took") == 2
     assert "Secure fed model took" in out
     assert "binary_accuracy" in out and "auroc" in out    # the script's own py_func AUROC metric was accepted
+
+
+def test_unmodified_reference_fedavg_script_runs_twice(tmp_path):
+    """fed_model.py: first run pre-trains and writes <path>/pretrained/cp.ckpt (the script's ``sys.path.exists`` is
+    given its intended meaning by the runner), the second run loads it; non-IID listing on the second run"""
+    _folder(tmp_path, "data/balanced_IDC_30k", 96, 50)
+    out = _run("fed_model.py", str(tmp_path), "1", "iid", timeout=1500)
+    assert "Pre-training took" in out and "saving model to" in out and "Federated training took" in out
+    assert (tmp_path / "pretrained" / "cp.ckpt").exists()
+    out = _run("fed_model.py", str(tmp_path), "2", "noniid", timeout=1500)
+    assert "Loading pretrained model" in out and "Pre-training took" not in out
+    rounds = [l for l in out.splitlines() if l.strip().startswith(("0,", "1,"))]
+    assert len(rounds) == 2 and all(len(l.split(",")) == 5 for l in rounds)
