@@ -13,8 +13,9 @@ The modules those scripts import (``tensorflow``, ``tensorflow_federated``, ``te
 This is a convenience for users switching over, not the benchmark's reference arm: every model, kernel and
 collective that runs is this framework's (``bench.py --impl reference`` stays "unavailable").
 ``fed_model.py`` calls ``sys.path.exists`` (an AttributeError upstream); the runner gives ``sys.path`` that method
-(= ``os.path.exists``, what the author meant) so the script runs. One limit is the script's own: ``secure_fed_model.py``
-with ``percent > 0`` builds a ragged ``np.array`` that NumPy >= 1.24 refuses.
+(= ``os.path.exists``, what the author meant) so the script runs; ``secure_fed_model.py`` with ``percent > 0`` builds ragged
+``np.array``s, which NumPy >= 1.24 refuses: inside this process that one error case gets the old object-array result.
+``IDCB_PAILLIER_BITS`` shortens the key the script generates at import (pure-Python big integers are slow at 2048).
 """
 from __future__ import annotations
 
@@ -92,6 +93,27 @@ class _Plt:
         P.write_panels_png(path, self.panels)
 
 
+def _legacy_ragged_arrays() -> None:
+    """``np.array(list_of_arrays_with_different_shapes)`` gave a 1-D object array (with a deprecation warning) in the
+    NumPy the reference ran on; NumPy >= 1.24 raises. secure_fed_model.py relies on the old behaviour
+    (``np.array(self.model.get_weights())``, ``np.array(ave_weights)``), so within a run_reference process the old
+    result is restored for exactly that error case."""
+    import numpy as np
+    real = np.array
+    if getattr(real, "_idcb_legacy", False):
+        return
+
+    def array(obj, *args, **kw):
+        try:
+            return real(obj, *args, **kw)
+        except ValueError as e:
+            if "inhomogeneous" not in str(e) or args or "dtype" in kw:
+                raise
+            return real(obj, dtype=object, **kw)
+    array._idcb_legacy = True
+    np.array = array
+
+
 def install_shims(device: str | None = None) -> None:
     """Register the stand-in modules. ``device`` (or ``IDCB_DEVICE``) picks where models are built (default: cuda when
     available)."""
@@ -115,6 +137,13 @@ def install_shims(device: str | None = None) -> None:
         sys.path = _SearchPath(sys.path)
     from .fed.client_data import ClientData
     ClientData.strict_ids = False        # the TFF of the reference's time did not check ids (see client_data.py)
+    _legacy_ragged_arrays()
+    bits = os.environ.get("IDCB_PAILLIER_BITS")
+    if bits:
+        # ``paillier.generate_paillier_keypair()`` is called without arguments at import time by secure_fed_model.py;
+        # a smaller modulus makes a demonstration run of the encrypted path practical on pure-Python big integers
+        gen = compat.paillier.generate_paillier_keypair
+        compat.paillier.generate_paillier_keypair = lambda n_length=int(bits), **kw: gen(n_length=n_length, **kw)
     tf = _from_namespace("tensorflow", compat.tf)
     tf.__version__ = "2.1.0 (idc_models_b200.compat)"
     sys.modules["tensorflow"] = tf

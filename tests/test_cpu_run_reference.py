@@ -27,8 +27,8 @@ def _folder(root: Path, sub: str, n: int, size: int) -> None:
         Image.fromarray(a, "RGB").save(root / sub / str(c) / f"p{i:04d}.png")
 
 
-def _run(script: str, *args: str, timeout: int = 900) -> str:
-    env = dict(os.environ, PYTHONPATH=str(ROOT), IDCB_DEVICE="cpu")
+def _run(script: str, *args: str, timeout: int = 900, **extra_env) -> str:
+    env = dict(os.environ, PYTHONPATH=str(ROOT), IDCB_DEVICE="cpu", **extra_env)
     r = subprocess.run([sys.executable, "-m", "idc_models_b200.run_reference", str(REF / script), *args],
                        capture_output=True, text=True, timeout=timeout, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
@@ -67,3 +67,14 @@ def test_unmodified_reference_fedavg_script_runs_twice(tmp_path):
     assert "Loading pretrained model" in out and "Pre-training took" not in out
     rounds = [l for l in out.splitlines() if l.strip().startswith(("0,", "1,"))]
     assert len(rounds) == 2 and all(len(l.split(",")) == 5 for l in rounds)
+
+
+def test_unmodified_reference_secure_script_encrypted_path(tmp_path):
+    """percent = 0.2: the first weight tensor of every client is Paillier-encrypted scalar by scalar, averaged under
+    encryption by the script's Server.aggregate and decrypted by its clients (short key for the test; the ragged
+    ``np.array`` calls of the script get the object-array result of the NumPy it was written for)"""
+    _folder(tmp_path, "data/balanced_IDC_30k", 120, 12)
+    out = _run("secure_fed_model.py", str(tmp_path), "1", "0.2", IDCB_PAILLIER_BITS="256")
+    for c in (0, 1):
+        assert f"Encryption for client {c} took" in out and f"Decryption for client {c} took" in out
+    assert "Secure fed model took" in out
