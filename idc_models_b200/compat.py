@@ -142,6 +142,20 @@ def _tfds_load(name="cifar10", split=None, data_dir=None, with_info=False, as_su
     return out
 
 
+def _strategy_ctor(cls):
+    """``tf.distribute.MirroredStrategy()`` takes no arguments in the scripts; launched with torchrun (one process per
+    GPU, ``WORLD_SIZE`` > 1) the strategy has to join that job instead of standing alone."""
+    def ctor(*args, **kw):
+        import os
+        if "world" not in kw and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+            from .parallel.world import World
+            kw["world"] = World.from_env(os.environ.get("IDCB_DEVICE"))
+        return cls(*args, **kw)
+    ctor.__name__ = cls.__name__
+    ctor.__doc__ = cls.__doc__
+    return ctor
+
+
 import numpy as _np
 
 tf = _ns(
@@ -166,8 +180,8 @@ tf = _ns(
         metrics=_ns(BinaryAccuracy=_metrics.BinaryAccuracy, CategoricalAccuracy=_metrics.CategoricalAccuracy),
         callbacks=_ns(ModelCheckpoint=_engine.ModelCheckpoint, Callback=_engine.Callback, History=_engine.History),
     ),
-    distribute=_ns(MirroredStrategy=_strategy.MirroredStrategy, get_strategy=_strategy.get_strategy,
-                   experimental=_ns(CentralStorageStrategy=_strategy.CentralStorageStrategy)),
+    distribute=_ns(MirroredStrategy=_strategy_ctor(_strategy.MirroredStrategy), get_strategy=_strategy.get_strategy,
+                   experimental=_ns(CentralStorageStrategy=_strategy_ctor(_strategy.CentralStorageStrategy))),
     data=_ns(Dataset=_dataset.Dataset, experimental=_ns(AUTOTUNE=_dataset.AUTOTUNE)),
     io=_ns(read_file=_read_file),
     image=_ns(decode_png=_decode_png, convert_image_dtype=_convert_image_dtype, resize=_resize),

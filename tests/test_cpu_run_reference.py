@@ -78,3 +78,23 @@ def test_unmodified_reference_secure_script_encrypted_path(tmp_path):
     for c in (0, 1):
         assert f"Encryption for client {c} took" in out and f"Decryption for client {c} took" in out
     assert "Secure fed model took" in out
+
+
+def test_unmodified_reference_transfer_script_as_two_ranks(tmp_path):
+    """launched with torchrun, the script's argument-less ``tf.distribute.MirroredStrategy()`` joins the job: two
+    data-parallel CPU replicas (gloo), ``num_replicas_in_sync`` = 2 in the script's own Timer lines"""
+    import socket
+    _folder(tmp_path, "data/IDC_regular_ps50_idx5/100", 48, 50)
+    (tmp_path / "logs").mkdir()
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    env = dict(os.environ, PYTHONPATH=str(ROOT), IDCB_DEVICE="cpu")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", str(port), "-m", "idc_models_b200.run_reference",
+                        str(REF / "dist_model_tf_mobile.py"), str(tmp_path)],
+                       capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert r.stdout.count("Pre-training with 2 devices took") == 2
+    assert r.stdout.count("Fine-tuning with 2 devices took") == 2
+    assert (tmp_path / "logs" / "plot_dev2.png").exists()
