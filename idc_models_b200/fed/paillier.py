@@ -127,11 +127,26 @@ class PaillierPrivateKey:
         n = public_key.n
         self.lam = (p - 1) * (q - 1)
         self.mu = pow(self.lam, -1, n)
+        # Chinese-remainder decryption (what phe does too): two exponentiations with half-length exponents modulo
+        # p^2 and q^2 instead of one with a full-length exponent modulo n^2 — about 3-4x less work.
+        # With g = n + 1:  L_p(g^(p-1) mod p^2) = (p-1) q mod p, hence h_p = ((p-1) q)^-1 mod p (likewise for q).
+        self.p, self.q = p, q
+        self.psquare, self.qsquare = p * p, q * q
+        self.hp = pow((p - 1) * q % p, -1, p)
+        self.hq = pow((q - 1) * p % q, -1, q)
+        self.p_inverse = pow(p, -1, q)
 
-    def raw_decrypt(self, c: int) -> int:
+    def raw_decrypt_plain(self, c: int) -> int:
+        """the textbook form: L(c^lambda mod n^2) * mu mod n (kept as the cross-check of the CRT path)"""
         n, n2 = self.public_key.n, self.public_key.nsquare
         u = pow(c, self.lam, n2)
         return (u - 1) // n * self.mu % n
+
+    def raw_decrypt(self, c: int) -> int:
+        p, q = self.p, self.q
+        mp = (pow(c % self.psquare, p - 1, self.psquare) - 1) // p * self.hp % p
+        mq = (pow(c % self.qsquare, q - 1, self.qsquare) - 1) // q * self.hq % q
+        return mp + (mq - mp) * self.p_inverse % q * p
 
     def decrypt(self, enc: EncryptedNumber) -> float:
         n = self.public_key.n

@@ -151,3 +151,20 @@ def test_client_scheduler_balances_and_is_deterministic():
     assert plan == assign_clients(costs, 2)
     assert sorted(clients_of_rank(costs, 2, 0) + clients_of_rank(costs, 2, 1)) == list(range(8))
     assert assign_clients([5, 3], 1) == [0, 0]
+
+
+def test_paillier_crt_decryption_equals_the_textbook_form():
+    """the Chinese-remainder decryption (two half-length exponentiations) against L(c^lambda mod n^2) * mu mod n"""
+    import random
+    from idc_models_b200.fed import paillier
+    for bits in (256, 512, 1024):
+        pk, sk = paillier.generate_paillier_keypair(n_length=bits, seed=bits)
+        rng = random.Random(bits)
+        for _ in range(12):
+            m = rng.randrange(0, pk.n)
+            c = pk.raw_encrypt(m)
+            assert sk.raw_decrypt(c) == sk.raw_decrypt_plain(c) == m
+        for edge in (0, 1, pk.n - 1):
+            assert sk.raw_decrypt(pk.raw_encrypt(edge)) == edge
+        mean = (pk.encrypt(3.0) + pk.encrypt(-5.5) + pk.encrypt(0.25)) / 3
+        assert abs(sk.decrypt(mean) - (3.0 - 5.5 + 0.25) / 3) < 1e-6
