@@ -55,14 +55,11 @@ def _decode_png(data: bytes, channels: int = 3):
     if channels != 3:
         raise ValueError("only channels=3 is supported (what the reference uses)")
     lib = _dataset._native_png()
-    if lib:
-        import ctypes as C
-        w, h = C.c_int(), C.c_int()
-        probe = np.empty((1, 1, 3), np.float32)
-        # first call only learns the size (the 1x1 output is discarded), second decodes at native resolution
-        if lib.idcbh_png_decode_f32(data, len(data), probe.ctypes.data, 1, 1, C.byref(w), C.byref(h)) == 0:
-            out = np.empty((h.value, w.value, 3), np.float32)
-            if lib.idcbh_png_decode_f32(data, len(data), out.ctypes.data, h.value, w.value, None, None) == 0:
+    if lib and len(data) >= 24 and data[:8] == b"\x89PNG\r\n\x1a\n" and data[12:16] == b"IHDR":
+        w, h = int.from_bytes(data[16:20], "big"), int.from_bytes(data[20:24], "big")   # the image's own size
+        if 0 < w <= 16384 and 0 < h <= 16384:
+            out = np.empty((h, w, 3), np.float32)
+            if lib.idcbh_png_decode_f32(bytes(data), len(data), out.ctypes.data, h, w, None, None) == 0:
                 return out
     return np.asarray(Image.open(io.BytesIO(data)).convert("RGB"), dtype=np.float32) / 255.0
 
