@@ -9,6 +9,12 @@ read in either of the two layouts the dataset is distributed in:
 * ``cifar-10-batches-py``: ``data_batch_{1..5}`` + ``test_batch``, pickled dicts with ``data`` (N x 3072 uint8,
   same plane order) and ``labels``.
 
+* a ``tensorflow_datasets`` cache, which is what running the reference once leaves behind:
+  ``<data_dir>/cifar10/<version>/cifar10-{train,test}.tfrecord-*`` — TFRecord files of ``tf.train.Example`` protos
+  with a PNG-encoded ``image`` and an int64 ``label`` (data/tfrecord.py reads the framing and the protos, the native
+  PNG decoder the images). Looked for under ``<path>/data``, ``<path>``, ``<path>/tensorflow_datasets``,
+  ``$TFDS_DATA_DIR`` and ``~/tensorflow_datasets``.
+
 Images come back as uint8 NHWC arrays (what tfds yields), labels as int64.
 """
 from __future__ import annotations
@@ -22,14 +28,53 @@ _BIN, _PY = "cifar-10-batches-bin", "cifar-10-batches-py"
 _RECORD = 1 + 3 * 32 * 32
 
 
+def _tfds_dir(root: str) -> str | None:
+    """``<root>/cifar10/<version>`` holding train and test TFRecord shards (the newest version if several)"""
+    import glob
+    base = os.path.join(root, "cifar10")
+    if not os.path.isdir(base):
+        return None
+    for d in sorted((d for d in glob.glob(os.path.join(base, "*")) if os.path.isdir(d)), reverse=True):
+        if glob.glob(os.path.join(d, "cifar10-train.tfrecord*")) and glob.glob(os.path.join(d, "cifar10-test.tfrecord*")):
+            return d
+    return None
+
+
 def find_cifar10(path: str) -> str | None:
-    """Directory of an on-disk CIFAR-10 copy under ``path`` (or ``path/data``), or None."""
+    """Directory of an on-disk CIFAR-10 copy under ``path`` (or ``path/data``), or None: the binary / python batch
+    directories first, then a tensorflow_datasets cache (also under $TFDS_DATA_DIR and ~/tensorflow_datasets)."""
     for root in (os.path.join(path, "data"), path):
         for name in (_BIN, _PY):
             for d in (os.path.join(root, name), os.path.join(root, "cifar10", name)):
                 if os.path.isdir(d):
                     return d
+    roots = [os.path.join(path, "data"), path, os.path.join(path, "tensorflow_datasets")]
+    if os.environ.get("TFDS_DATA_DIR"):
+        roots.append(os.environ["TFDS_DATA_DIR"])
+    roots.append(os.path.join(os.path.expanduser("~"), "tensorflow_datasets"))
+    for root in roots:
+        d = _tfds_dir(root)
+        if d is not None:
+            return d
     return None
+
+
+def _read_tfds(files):
+    """``cifar10-<split>.tfrecord-*`` shards -> (uint8 [N, 32, 32, 3], int64 [N])"""
+    from . import tfrecord
+    from .dataset import decode_img
+    xs, ys = [], []
+    for f in sorted(files):
+        for rec in tfrecord.read_records(f):
+            ex = tfrecord.parse_example(rec)
+            if not ex.get("image") or not ex.get("label"):
+                raise ValueError(f"{f}: a record without image / label features (found {sorted(ex)})")
+            img = decode_img(ex["image"][0], (32, 32))                 # float32 in [0, 1], exact multiples of 1/255
+            xs.append(np.rint(img * 255.0).astype(np.uint8))
+            ys.append(int(ex["label"][0]))
+    if not xs:
+        raise ValueError("no records in " + ", ".join(files))
+    return np.stack(xs), np.asarray(ys, dtype=np.int64)
 
 
 def _planes_to_nhwc(flat: np.ndarray) -> np.ndarray:
@@ -61,7 +106,11 @@ def _read_py(files):
 
 
 def load_cifar10(directory: str):
-    """((x_train, y_train), (x_test, y_test)) from a ``cifar-10-batches-{bin,py}`` directory."""
+    """((x_train, y_train), (x_test, y_test)) from a ``cifar-10-batches-{bin,py}`` directory or a tfds cache directory."""
+    import glob
+    shards = glob.glob(os.path.join(directory, "cifar10-train.tfrecord*"))
+    if shards:
+        return _read_tfds(shards), _read_tfds(glob.glob(os.path.join(directory, "cifar10-test.tfrecord*")))
     is_bin = os.path.basename(os.path.normpath(directory)) == _BIN or os.path.exists(os.path.join(directory, "test_batch.bin"))
     ext = ".bin" if is_bin else ""
     train = [os.path.join(directory, f"data_batch_{i}{ext}") for i in range(1, 6)]
