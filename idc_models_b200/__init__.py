@@ -16,4 +16,4 @@ Layout::
     io/        Keras .h5 import/export (own HDF5 subset), checkpoints
     utils/     Timer, logging, plotting
 """
-__version__ = "0.1.0"
+__version__ = "0.2.0"
