@@ -15,5 +15,7 @@ Layout::
     fed/       ClientData, FedAvg process, secure (pairwise-mask) aggregation
     io/        Keras .h5 import/export (own HDF5 subset), checkpoints
     utils/     Timer, logging, plotting
+    compat     the reference's import surface (tf / tff / tfds / paillier names) over the modules above
+    run_reference   executes a reference-style script, incl. the upstream ones unmodified, on this framework
 """
 __version__ = "0.2.0"
