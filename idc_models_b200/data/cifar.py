@@ -93,11 +93,24 @@ def _read_bin(files):
     return np.concatenate(xs), np.concatenate(ys)
 
 
+class _BatchUnpickler(pickle.Unpickler):
+    """The python-version batches are pickles of a dict of bytes / lists / one numpy array. A pickle can name any
+    callable, so only the handful of globals such a file needs are resolvable; anything else is refused."""
+    _ALLOWED = {("numpy.core.multiarray", "_reconstruct"), ("numpy._core.multiarray", "_reconstruct"),
+                ("numpy", "ndarray"), ("numpy", "dtype"), ("copy_reg", "_reconstructor"), ("copyreg", "_reconstructor"),
+                ("__builtin__", "object"), ("builtins", "object")}
+
+    def find_class(self, module, name):
+        if (module, name) not in self._ALLOWED:
+            raise pickle.UnpicklingError(f"CIFAR-10 batch refers to {module}.{name}: not something a dataset file needs")
+        return super().find_class(module, name)
+
+
 def _read_py(files):
     xs, ys = [], []
     for f in files:
         with open(f, "rb") as fh:
-            d = pickle.load(fh, encoding="bytes")
+            d = _BatchUnpickler(fh, encoding="bytes").load()
         data = d[b"data"] if b"data" in d else d["data"]
         labels = d.get(b"labels", d.get("labels"))
         xs.append(_planes_to_nhwc(np.asarray(data, dtype=np.uint8)))

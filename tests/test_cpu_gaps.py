@@ -155,3 +155,20 @@ def test_mobile_script_honours_dtype_and_split_flags(tmp_path):
                                      "--train-split", "0.5", "--val-split", "0.25", "--shuffle-buffer", "16"])
     assert type(out["model"].executor).__name__ == "RefExecutor"
     assert np.isfinite(out["history_fine"].history["loss"][-1])
+
+
+def test_cifar_python_batches_cannot_name_arbitrary_callables(tmp_path):
+    """a 'dataset file' whose pickle refers to os.system (or anything else a batch does not need) is refused"""
+    import pickle
+    d = tmp_path / "data" / "cifar-10-batches-py"
+    d.mkdir(parents=True)
+
+    class Evil:
+        def __reduce__(self):
+            import os
+            return (os.system, ("echo pwned > /dev/null",))
+    for name in ["data_batch_%d" % i for i in range(1, 6)] + ["test_batch"]:
+        with open(d / name, "wb") as f:
+            pickle.dump({b"data": Evil(), b"labels": [0]}, f, protocol=2)
+    with pytest.raises(pickle.UnpicklingError, match="not something a dataset file needs"):
+        cifar.load_cifar10(str(d))
