@@ -175,7 +175,9 @@ tf = _ns(
         optimizers=_ns(RMSprop=_optim.RMSprop, SGD=_optim.SGD, Adam=_optim.Adam),
         losses=_ns(BinaryCrossentropy=_losses.BinaryCrossentropy, CategoricalCrossentropy=_losses.CategoricalCrossentropy),
         metrics=_ns(BinaryAccuracy=_metrics.BinaryAccuracy, CategoricalAccuracy=_metrics.CategoricalAccuracy),
-        callbacks=_ns(ModelCheckpoint=_engine.ModelCheckpoint, Callback=_engine.Callback, History=_engine.History),
+        callbacks=_ns(ModelCheckpoint=_engine.ModelCheckpoint, Callback=_engine.Callback, History=_engine.History,
+                      EarlyStopping=_engine.EarlyStopping, LearningRateScheduler=_engine.LearningRateScheduler,
+                      ReduceLROnPlateau=_engine.ReduceLROnPlateau, CSVLogger=_engine.CSVLogger),
     ),
     distribute=_ns(MirroredStrategy=_strategy_ctor(_strategy.MirroredStrategy), get_strategy=_strategy.get_strategy,
                    experimental=_ns(CentralStorageStrategy=_strategy_ctor(_strategy.CentralStorageStrategy))),

@@ -61,6 +61,127 @@ class ModelCheckpoint(Callback):
         self.model.save_weights(path)
 
 
+class EarlyStopping(Callback):
+    """``tf.keras.callbacks.EarlyStopping``: stop when ``monitor`` has not improved by ``min_delta`` for ``patience``
+    epochs; optionally put the best weights back."""
+
+    def __init__(self, monitor: str = "val_loss", min_delta: float = 0.0, patience: int = 0, mode: str = "auto",
+                 restore_best_weights: bool = False, verbose: int = 0, **kw):
+        self.monitor, self.min_delta, self.patience = monitor, abs(float(min_delta)), int(patience)
+        self.restore_best_weights, self.verbose = restore_best_weights, verbose
+        self.larger_is_better = mode == "max" or (mode == "auto" and ("acc" in monitor or "auc" in monitor))
+
+    def on_train_begin(self, logs=None):
+        self.best, self.wait, self.stopped_epoch, self.best_weights = None, 0, None, None
+
+    def on_epoch_end(self, epoch, logs=None):
+        cur = (logs or {}).get(self.monitor)
+        if cur is None:
+            return
+        better = self.best is None or (cur > self.best + self.min_delta if self.larger_is_better
+                                       else cur < self.best - self.min_delta)
+        if better:
+            self.best, self.wait = cur, 0
+            if self.restore_best_weights:
+                self.best_weights = self.model.get_weights()
+            return
+        self.wait += 1
+        if self.wait >= self.patience:
+            self.stopped_epoch = epoch
+            self.model.stop_training = True
+            if self.restore_best_weights and self.best_weights is not None:
+                self.model.set_weights(self.best_weights)
+            if self.verbose:
+                print(f"Epoch {epoch + 1:05d}: early stopping")
+
+
+class LearningRateScheduler(Callback):
+    """``tf.keras.callbacks.LearningRateScheduler(schedule)``: ``schedule(epoch, lr) -> lr`` (or ``schedule(epoch)``)
+    at the start of every epoch. The optimizer reads its learning rate when a step is launched, so no re-compile is
+    needed (a data-parallel step whose all-reduce is captured in a CUDA graph re-captures once per new value)."""
+
+    def __init__(self, schedule, verbose: int = 0):
+        self.schedule, self.verbose = schedule, verbose
+
+    def on_epoch_begin(self, epoch, logs=None):
+        opt = self.model.optimizer
+        try:
+            lr = self.schedule(epoch, opt.learning_rate)
+        except TypeError:
+            lr = self.schedule(epoch)
+        opt.learning_rate = float(lr)
+        if self.verbose:
+            print(f"\nEpoch {epoch + 1:05d}: LearningRateScheduler setting learning rate to {opt.learning_rate}.")
+
+    def on_epoch_end(self, epoch, logs=None):
+        if logs is not None:
+            logs["lr"] = self.model.optimizer.learning_rate
+
+
+class ReduceLROnPlateau(Callback):
+    """``tf.keras.callbacks.ReduceLROnPlateau``: multiply the learning rate by ``factor`` after ``patience`` epochs
+    without improvement of ``monitor`` (then wait ``cooldown`` epochs), never below ``min_lr``."""
+
+    def __init__(self, monitor: str = "val_loss", factor: float = 0.1, patience: int = 10, min_delta: float = 1e-4,
+                 cooldown: int = 0, min_lr: float = 0.0, mode: str = "auto", verbose: int = 0, **kw):
+        if factor >= 1.0:
+            raise ValueError("ReduceLROnPlateau does not support a factor >= 1.0")
+        self.monitor, self.factor, self.patience, self.min_delta = monitor, float(factor), int(patience), abs(float(min_delta))
+        self.cooldown, self.min_lr, self.verbose = int(cooldown), float(min_lr), verbose
+        self.larger_is_better = mode == "max" or (mode == "auto" and ("acc" in monitor or "auc" in monitor))
+
+    def on_train_begin(self, logs=None):
+        self.best, self.wait, self.cooldown_counter = None, 0, 0
+
+    def on_epoch_end(self, epoch, logs=None):
+        opt = self.model.optimizer
+        if logs is not None:
+            logs["lr"] = opt.learning_rate
+        cur = (logs or {}).get(self.monitor)
+        if cur is None:
+            return
+        if self.cooldown_counter > 0:
+            self.cooldown_counter -= 1
+            self.wait = 0
+        better = self.best is None or (cur > self.best + self.min_delta if self.larger_is_better
+                                       else cur < self.best - self.min_delta)
+        if better:
+            self.best, self.wait = cur, 0
+        elif self.cooldown_counter <= 0:
+            self.wait += 1
+            if self.wait >= self.patience and opt.learning_rate > self.min_lr:
+                opt.learning_rate = max(opt.learning_rate * self.factor, self.min_lr)
+                self.cooldown_counter, self.wait = self.cooldown, 0
+                if self.verbose:
+                    print(f"\nEpoch {epoch + 1:05d}: ReduceLROnPlateau reducing learning rate to {opt.learning_rate}.")
+
+
+class CSVLogger(Callback):
+    """``tf.keras.callbacks.CSVLogger(filename, separator=',', append=False)``: one row per epoch."""
+
+    def __init__(self, filename: str, separator: str = ",", append: bool = False):
+        self.filename, self.sep, self.append = filename, separator, append
+        self.keys = None
+
+    def on_train_begin(self, logs=None):
+        import os
+        self._fh = open(self.filename, "a" if self.append else "w")
+        self.keys = None
+        self._header = not (self.append and os.path.getsize(self.filename) > 0)
+
+    def on_epoch_end(self, epoch, logs=None):
+        logs = logs or {}
+        if self.keys is None:
+            self.keys = sorted(logs)
+            if self._header:
+                self._fh.write(self.sep.join(["epoch"] + self.keys) + "\n")
+        self._fh.write(self.sep.join([str(epoch)] + [repr(float(logs.get(k, float("nan")))) for k in self.keys]) + "\n")
+        self._fh.flush()
+
+    def on_train_end(self, logs=None):
+        self._fh.close()
+
+
 def compile_model(net, optimizer, loss, metrics) -> None:
     net.loss = L.get(loss if loss is not None else ("bce" if net.n_outputs == 1 else "cce"))
     net.metrics = [M.get(m, net.n_outputs) for m in metrics]
@@ -185,11 +306,11 @@ def fit(net, data, epochs, initial_epoch, validation_data, callbacks, verbose, s
         dt = max(time.time() - t0, 1e-9)
         if validation_data is not None:
             logs.update(_evaluate(net, validation_data, validation_steps, prefix="val_"))
+        for cb in callbacks:
+            cb.on_epoch_end(epoch, logs)          # (a callback may add to the logs, e.g. the learning rate)
         hist._append(epoch, logs)
         jlog.log("epoch", epoch=epoch, steps=nb, examples=seen, train_seconds=round(dt, 4),
                  examples_per_s=round(seen / dt, 1), **{k: float(v) for k, v in logs.items()})
-        for cb in callbacks:
-            cb.on_epoch_end(epoch, logs)
         if verbose and net.strategy.world.rank == 0:
             body = " - ".join(f"{k}: {v:.4f}" for k, v in logs.items())
             print(f"Epoch {epoch + 1}/{epochs} - {time.time() - t0:.0f}s - {body}")

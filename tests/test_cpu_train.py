@@ -159,3 +159,49 @@ def test_prepare_for_training_batches_synthetic_idc():
     srt = synthetic.synthetic_idc(10, order="class_sorted", label_as_int=True)
     labs = [l for _, l in srt]
     assert labs == sorted(labs, reverse=True)             # all class-1 first: the non-IID listing
+
+
+def test_keras_style_callbacks(tmp_path):
+    """EarlyStopping (with restore_best_weights), LearningRateScheduler, ReduceLROnPlateau, CSVLogger"""
+    import numpy as np
+    import torch
+    from idc_models_b200.models import applications as apps
+    from idc_models_b200.train import engine as E
+
+    def model(lr=0.05):
+        m = apps.Sequential([apps.Conv2D(8, (3, 3), activation="relu", input_shape=(10, 10, 3), strides=2),
+                             apps.Flatten(), apps.Dense(1)], device="cpu", seed=1)
+        m.compile(optimizer=apps_opt(lr), loss="bce", metrics=["accuracy"])
+        return m
+    from idc_models_b200.optim.optimizers import SGD
+    apps_opt = lambda lr: SGD(lr)
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand(32, 10, 10, 3, generator=g)
+    y = (x.mean(dim=(1, 2, 3)) > 0.5).float()
+    data = [(x[i:i + 8], y[i:i + 8]) for i in range(0, 32, 8)]
+    # schedule: lr halves every epoch; the optimizer sees it and history records it
+    m = model()
+    h = m.fit(data, epochs=3, verbose=0, callbacks=[E.LearningRateScheduler(lambda epoch, lr: 0.05 * 0.5 ** epoch),
+                                                    E.CSVLogger(str(tmp_path / "log.csv"))])
+    assert h.history["lr"] == [0.05, 0.025, 0.0125] and m.optimizer.learning_rate == 0.0125
+    rows = (tmp_path / "log.csv").read_text().strip().splitlines()
+    assert rows[0].split(",")[0] == "epoch" and "loss" in rows[0] and len(rows) == 4
+    # early stopping on a metric that cannot improve (lr 0): stops after `patience` non-improving epochs
+    m = model(0.0)
+    es = E.EarlyStopping(monitor="loss", patience=2, restore_best_weights=True)
+    w0 = [w.copy() for w in m.get_weights()]
+    h = m.fit(data, epochs=10, verbose=0, callbacks=[es])
+    assert len(h.history["loss"]) == 3 and es.stopped_epoch == 2
+    assert all(np.array_equal(a, b) for a, b in zip(w0, m.get_weights()))
+    # plateau: a monitored value that never improves drives the learning rate down by `factor` every `patience`
+    # epochs, floored at min_lr
+    m = model(1.0)
+
+    class Flat(E.Callback):
+        def on_epoch_end(self, epoch, logs=None):
+            logs["flat"] = 1.0
+    rl = E.ReduceLROnPlateau(monitor="flat", factor=0.5, patience=1, min_lr=0.2, min_delta=0.0)
+    h = m.fit(data, epochs=5, verbose=0, callbacks=[Flat(), rl])
+    assert h.history["lr"] == [1.0, 1.0, 0.5, 0.25, 0.2] and m.optimizer.learning_rate == 0.2
+    with pytest.raises(ValueError):
+        E.ReduceLROnPlateau(factor=1.0)
