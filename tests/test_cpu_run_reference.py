@@ -59,7 +59,7 @@ def test_unmodified_reference_secure_script_runs(tmp_path):
 def test_unmodified_reference_fedavg_script_runs_twice(tmp_path):
     """fed_model.py: first run pre-trains and writes <path>/pretrained/cp.ckpt (the script's ``sys.path.exists`` is
     given its intended meaning by the runner), the second run loads it; non-IID listing on the second run"""
-    _folder(tmp_path, "data/balanced_IDC_30k", 64, 50)
+    _folder(tmp_path, "data/balanced_IDC_30k", 32, 50)
     out = _run("fed_model.py", str(tmp_path), "1", "iid", timeout=1500)
     assert "Pre-training took" in out and "saving model to" in out and "Federated training took" in out
     assert (tmp_path / "pretrained" / "cp.ckpt").exists()
